@@ -1,0 +1,137 @@
+/*
+ * oracle/imgops_oracle.c — TEST INFRASTRUCTURE ONLY (never on the product path).
+ *
+ * Scalar CPU restatement of the O(N) image ops on depthlib's stereo hot path:
+ *   orc_remap_u8       cv2.remap(gray, map1, map2, INTER_LINEAR)      depthlib/rectify.py:185-186
+ *   orc_bgr2gray       cv2.cvtColor(img, COLOR_BGR2GRAY)              depthlib/rectify.py:116, stereo_core.py:157-159
+ *   orc_median3_f32    cv2.medianBlur(float32, 3)                     depthlib/postprocess.py:169, stereo_core.py:173
+ *   orc_box5_mean      cv2.boxFilter(f32, -1, (5,5))                  depthlib/postprocess.py:59,63
+ *   orc_postprocess    postprocess_disparity (hole filling off)       depthlib/postprocess.py:120-171
+ *   orc_disp_to_depth  StereoCore.disparity_to_depth                  depthlib/stereo_core.py:234-272
+ * The arithmetic of the cv2 calls lives in the opencv-python wheel (not under /root/reference); it is
+ * restated from SURVEY.md Appendix B and pinned against the live cv2 binary by tests/test_oracle_vs_cv2.py.
+ * Compile with -ffp-contract=off: the float32 chain must not be fused into FMAs.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+void orc_filter_speckles(int16_t *img, int H, int W, int newVal, int maxSize, int maxDiff);
+
+/* B.1: fixed-point bilinear gather, 5 fractional bits, constant-0 border */
+void orc_remap_u8(const uint8_t *src, int sH, int sW, const float *map1, const float *map2,
+                  int H, int W, uint8_t *dst)
+{
+    for (size_t i = 0; i < (size_t)H * W; i++) {
+        int sx = (int)lrintf(map1[i] * 32.0f); /* round-half-even of the float32 product */
+        int sy = (int)lrintf(map2[i] * 32.0f);
+        int ix = sx >> 5, iy = sy >> 5, fx = sx & 31, fy = sy & 31;
+        int p00 = 0, p01 = 0, p10 = 0, p11 = 0;
+        if (iy >= 0 && iy < sH) {
+            if (ix >= 0 && ix < sW) p00 = src[(size_t)iy * sW + ix];
+            if (ix + 1 >= 0 && ix + 1 < sW) p01 = src[(size_t)iy * sW + ix + 1];
+        }
+        if (iy + 1 >= 0 && iy + 1 < sH) {
+            if (ix >= 0 && ix < sW) p10 = src[(size_t)(iy + 1) * sW + ix];
+            if (ix + 1 >= 0 && ix + 1 < sW) p11 = src[(size_t)(iy + 1) * sW + ix + 1];
+        }
+        int acc = (32 - fy) * (32 - fx) * p00 + (32 - fy) * fx * p01 + fy * (32 - fx) * p10 + fy * fx * p11;
+        dst[i] = (uint8_t)((acc * 32 + 16384) >> 15);
+    }
+}
+
+/* B.2: weights applied to the channels as stored */
+void orc_bgr2gray(const uint8_t *img, size_t npix, uint8_t *dst)
+{
+    for (size_t i = 0; i < npix; i++)
+        dst[i] = (uint8_t)((3735 * img[3 * i] + 19235 * img[3 * i + 1] + 9798 * img[3 * i + 2] + 16384) >> 15);
+}
+
+static inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+static inline void fswap(float *a, float *b) { if (*a > *b) { float t = *a; *a = *b; *b = t; } }
+
+void orc_median3_f32(const float *src, int H, int W, float *dst)
+{
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            float v[9];
+            int k = 0;
+            for (int dy = -1; dy <= 1; dy++)
+                for (int dx = -1; dx <= 1; dx++)
+                    v[k++] = src[(size_t)clampi(y + dy, 0, H - 1) * W + clampi(x + dx, 0, W - 1)];
+            for (int i = 1; i < 9; i++) { /* insertion sort: 9 elements */
+                float t = v[i];
+                int j = i - 1;
+                while (j >= 0 && v[j] > t) { v[j + 1] = v[j]; j--; }
+                v[j + 1] = t;
+            }
+            dst[(size_t)y * W + x] = v[4];
+        }
+}
+
+static inline int reflect101(int p, int n)
+{
+    if (n == 1) return 0;
+    while (p < 0 || p >= n) {
+        if (p < 0) p = -p;
+        else p = 2 * (n - 1) - p;
+    }
+    return p;
+}
+
+/* 5x5 normalised box mean, BORDER_REFLECT_101, double accumulation, one rounding to float32 */
+void orc_box5_mean(const float *src, int H, int W, float *dst)
+{
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            double s = 0.0;
+            for (int dy = -2; dy <= 2; dy++)
+                for (int dx = -2; dx <= 2; dx++)
+                    s += (double)src[(size_t)reflect101(y + dy, H) * W + reflect101(x + dx, W)];
+            dst[(size_t)y * W + x] = (float)(s * (1.0 / 25.0));
+        }
+}
+
+/* postprocess.postprocess_disparity with apply_hole_filling=False */
+void orc_postprocess(const float *disp, int H, int W, int maxSpeckle, int maxDiff16, float thr,
+                     int outliers, float *out)
+{
+    size_t N = (size_t)H * W;
+    int16_t *d16 = malloc(N * sizeof(int16_t));
+    float *d = malloc(N * sizeof(float)), *sq = malloc(N * sizeof(float));
+    float *mean = malloc(N * sizeof(float)), *msq = malloc(N * sizeof(float));
+    for (size_t i = 0; i < N; i++) d16[i] = (int16_t)(int32_t)(disp[i] * 16.0f); /* astype(int16) truncates */
+    orc_filter_speckles(d16, H, W, 0, maxSpeckle, maxDiff16);
+    for (size_t i = 0; i < N; i++) d[i] = (float)d16[i] / 16.0f;
+    if (outliers) {
+        for (size_t i = 0; i < N; i++) sq[i] = d[i] * d[i];
+        orc_box5_mean(d, H, W, mean);
+        orc_box5_mean(sq, H, W, msq);
+        for (size_t i = 0; i < N; i++) {
+            float m2 = mean[i] * mean[i];
+            float var = msq[i] - m2;
+            float sd = sqrtf(var > 0.0f ? var : 0.0f);
+            float diff = fabsf(d[i] - mean[i]);
+            float lim = thr * sd;
+            if (diff > lim && d[i] > 0.0f) sq[i] = 0.0f; else sq[i] = d[i];
+        }
+        memcpy(d, sq, N * sizeof(float));
+    }
+    orc_median3_f32(d, H, W, out);
+    free(d16); free(d); free(sq); free(mean); free(msq);
+}
+
+/* B.4 */
+void orc_disp_to_depth(const float *disp, size_t n, float fB, float doffs, float eps,
+                       float max_depth, int has_max, float *Z)
+{
+    for (size_t i = 0; i < n; i++) {
+        float adj = disp[i] + doffs;
+        float z = INFINITY;
+        if (adj > eps) z = fB / adj;
+        if (has_max && z > max_depth) z = max_depth;
+        Z[i] = z;
+    }
+}
