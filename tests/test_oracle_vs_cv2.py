@@ -1,0 +1,81 @@
+"""Pins the C restatement (oracle/*.c) bit-exact against the live cv2 binary, called exactly the
+way depthlib calls it (oracle/cv2_reference.py). Skipped where cv2 is not importable."""
+import numpy as np
+import pytest
+
+import oracle
+from oracle import cv2_reference as cr
+from depthestimation_b200.synth import make_pair, make_adversarial, make_calibration
+
+pytestmark = pytest.mark.skipif(not cr.HAVE_CV2, reason="cv2 not importable")
+
+MODES = ["sgbm", "hh", "sgbm_3way", "hh4"]
+
+
+def _check(L, R, **kw):
+    ref = cr.compute_disparity16(L, R, **kw)
+    got = oracle.sgbm_compute(L, R, oracle.make_params(**kw))
+    bad = int((ref != got).sum())
+    assert bad == 0, f"{bad} px differ for {kw}"
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("D,bs", [(64, 5), (48, 3), (32, 9), (16, 1), (40, 11), (44, 5), (62, 7)])
+def test_modes_blocks(mode, D, bs):
+    L, R, _ = make_pair(64, 180, D, seed=1000 + D + bs)
+    _check(L, R, min_disp=0, num_disp=D, block_size=bs, sgbm_mode=mode)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("mind", [-24, -8, 3, 8])
+def test_min_disp(mode, mind):
+    L, R, _ = make_pair(56, 170, 32, seed=77)
+    _check(L, R, min_disp=mind, num_disp=32, block_size=5, sgbm_mode=mode)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("uniq,d12,cap,sws", [(0, 1, 31, 0), (30, -1, 5, 50), (75, 3, 63, 20), (10, 0, 20, 100)])
+def test_filters(mode, uniq, d12, cap, sws):
+    L, R, _ = make_pair(60, 160, 40, seed=5)
+    _check(L, R, min_disp=0, num_disp=40, block_size=5, sgbm_mode=mode, uniqueness_ratio=uniq,
+           disp12_max_diff=d12, prefilter_cap=cap, speckle_window_size=sws, speckle_range=1)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("kind", ["noise", "zeros", "quantized", "periodic"])
+def test_adversarial_inputs(mode, kind):
+    L, R = make_adversarial(kind, 48, 150)
+    _check(L, R, min_disp=0, num_disp=32, block_size=5, sgbm_mode=mode)
+
+
+@pytest.mark.parametrize("mode", ["sgbm", "sgbm_3way"])
+def test_kitti_shape_defaults(mode):
+    L, R, _ = make_pair(375, 1242, 128, seed=1000)
+    _check(L, R, min_disp=0, num_disp=128, block_size=5, sgbm_mode=mode)
+
+
+def test_remap_gray_median_speckle_post_depth():
+    import cv2
+    rng = np.random.default_rng(3)
+    H, W = 90, 210
+    cal = make_calibration(H, W)
+    maps = cr.build_maps(cal, alpha=1.0)
+    img = rng.integers(0, 256, (H, W), dtype=np.uint8)
+    assert np.array_equal(oracle.remap_u8(img, maps["map1_L"], maps["map2_L"]),
+                          cv2.remap(img, maps["map1_L"], maps["map2_L"], cv2.INTER_LINEAR))
+    col = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    assert np.array_equal(oracle.bgr2gray(col), cv2.cvtColor(col, cv2.COLOR_BGR2GRAY))
+    L, R, _ = make_pair(H, W, 48, seed=9)
+    d16 = cr.compute_disparity16(L, R, num_disp=48, sgbm_mode="sgbm", speckle_window_size=0)
+    assert np.array_equal(oracle.median3_s16(d16), cv2.medianBlur(d16, 3))
+    sp = d16.copy()
+    cv2.filterSpeckles(sp, -16, 40, 16)
+    assert np.array_equal(oracle.filter_speckles(d16, -16, 40, 16), sp)
+    d = (d16.astype(np.float32) / 16.0)[:, 48:]
+    assert np.array_equal(oracle.median3_f32(d), cv2.medianBlur(d, 3))
+    assert np.array_equal(oracle.postprocess(d, 100, 1.0, 2.5), cr.postprocess_disparity(d, 100, 1.0, 2.5))
+    post = oracle.postprocess(d, 100, 1.0, 2.5)
+    for md in (None, 30.0):
+        a = oracle.disp_to_depth(post, 0.8 * W, 0.54, 1.25, eps=0, max_depth=md)
+        b = cr.disparity_to_depth(post, 0.8 * W, 0.54, 1.25, eps=0, max_depth=md)
+        assert np.array_equal(a, b)
