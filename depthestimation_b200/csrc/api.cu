@@ -1,0 +1,496 @@
+// api.cu — the C ABI of libb200stereo.so (include/b200stereo.h): handle, scratch management and
+// the stage graph  remap -> prefilter -> cost -> paths -> WTA -> median -> speckle -> post -> depth.
+// Host-side counterpart of StereoCore (depthlib/stereo_core.py:44-75, 125-200, 212-293).
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "common.cuh"
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <typename T> T* as() const { return (T*)p; }
+};
+
+struct B200sHandle {
+    int device = 0;
+    B200sParams params;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    char err[512];
+    long long launches = 0;
+    bool timing = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+    // maps
+    int mapH = 0, mapW = 0;
+    DevBuf maps;  // 4 x H x W float
+    // scratch
+    DevBuf imgL, imgR, rectL, rectR, recL, recR, C, S, Calt, raw, med, labels, sizes, f0, f1, s16c, hostio;
+    // geometry of the last sgbm call (for debug taps)
+    Eff last_eff;
+    int last_B = 0;
+    bool have_last = false;
+
+    void set_error(int code, const char* fmt, ...) {
+        (void)code;
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, sizeof(err), fmt, ap);
+        va_end(ap);
+    }
+    void release_all() {
+        DevBuf* all[] = {&maps, &imgL, &imgR, &rectL, &rectR, &recL, &recR, &C, &S, &Calt, &raw, &med,
+                         &labels, &sizes, &f0, &f1, &s16c, &hostio};
+        for (DevBuf* b : all) b->release();
+    }
+};
+
+static int validate(B200sHandle* h, const B200sParams* p) {
+    if (!p) { if (h) h->set_error(B200S_E_INVALID, "params is NULL"); return B200S_E_INVALID; }
+    auto fail = [&](const char* m) { if (h) h->set_error(B200S_E_INVALID, "%s", m); return B200S_E_INVALID; };
+    if (p->numDisparities < 1 || p->numDisparities > 256) return fail("numDisparities must be in [1, 256]");
+    int bs = p->blockSize > 0 ? p->blockSize : 5;
+    if (bs % 2 == 0 || bs > 11) return fail("blockSize must be odd and <= 11");
+    if (p->mode < 0 || p->mode > 3) return fail("mode must be one of sgbm(0), hh(1), sgbm_3way(2), hh4(3)");
+    if (p->minDisparity < -4096 || p->minDisparity > 4096) return fail("minDisparity out of range");
+    Eff e = make_eff(*p, 1, 1);
+    if (e.P2e > 16384) return fail("P2 too large for the int16 aggregation (max 16384)");
+    if ((long long)e.P2e + (long long)bs * bs * (2 * e.ftzero + 63) > 32767)
+        return fail("blockSize/preFilterCap/P2 combination can overflow the int16 cost volume");
+    if (p->mode == B200S_MODE_SGBM_3WAY && e.ue >= 100) return fail("uniquenessRatio must be < 100 in sgbm_3way mode");
+    if (e.ue > 100) return fail("uniquenessRatio must be <= 100");
+    return B200S_OK;
+}
+
+static StripePlan make_stripes(const Eff& e) {
+    StripePlan sp;
+    memset(&sp, 0, sizeof(sp));
+    if (e.mode != B200S_MODE_SGBM_3WAY) {
+        sp.n = 1; sp.a[0] = 0; sp.r0[0] = 0; sp.r1[0] = e.H; sp.alt_rows = 0;
+        return sp;
+    }
+    const int nst = 4;
+    const int sz = (e.H + nst - 1) / nst;
+    const int ov = (e.bs / 2 + 1) + (sz + 9) / 10;  // ceil(0.1 * sz)
+    sp.n = nst;
+    sp.alt_rows = e.SH2;
+    for (int n = 0; n < nst; n++) {
+        int r0 = n * sz, r1 = h_imin((n + 1) * sz, e.H);
+        if (r0 >= r1) { sp.a[n] = sp.r0[n] = sp.r1[n] = 0; continue; }
+        sp.a[n] = h_imax(h_imin(r0 - ov, e.H), 0);
+        sp.r0[n] = r0;
+        sp.r1[n] = r1;
+    }
+    return sp;
+}
+
+extern "C" {
+
+int b200s_abi_version(void) { return B200S_ABI_VERSION; }
+
+int b200s_create(int device, const B200sParams* p, B200sHandle** out) {
+    if (!out) return B200S_E_INVALID;
+    *out = nullptr;
+    int rc = validate(nullptr, p);
+    if (rc) return rc;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return B200S_E_CUDA;
+    if (cudaSetDevice(device) != cudaSuccess) return B200S_E_CUDA;
+    B200sHandle* h = new (std::nothrow) B200sHandle();
+    if (!h) return B200S_E_CUDA;
+    h->err[0] = 0;
+    h->device = device;
+    h->params = *p;
+    if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return B200S_E_CUDA; }
+    h->stream = h->own_stream;
+    cudaEventCreate(&h->ev0);
+    cudaEventCreate(&h->ev1);
+    *out = h;
+    return B200S_OK;
+}
+
+int b200s_configure(B200sHandle* h, const B200sParams* p) {
+    if (!h) return B200S_E_INVALID;
+    int rc = validate(h, p);
+    if (rc) return rc;
+    h->params = *p;
+    h->have_last = false;
+    return B200S_OK;
+}
+
+int b200s_destroy(B200sHandle* h) {
+    if (!h) return B200S_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    h->release_all();
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+    return B200S_OK;
+}
+
+const char* b200s_last_error(const B200sHandle* h) { return h ? h->err : "null handle"; }
+
+int b200s_set_stream(B200sHandle* h, void* s) {
+    if (!h) return B200S_E_INVALID;
+    h->stream = s ? (cudaStream_t)s : h->own_stream;
+    return B200S_OK;
+}
+
+int b200s_sync(B200sHandle* h) {
+    if (!h) return B200S_E_INVALID;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return B200S_OK;
+}
+
+int b200s_enable_timing(B200sHandle* h, int on) { if (!h) return B200S_E_INVALID; h->timing = on != 0; return B200S_OK; }
+float b200s_last_ms(const B200sHandle* h) { return h ? h->last_ms : 0.f; }
+long long b200s_launch_count(const B200sHandle* h) { return h ? h->launches : 0; }
+
+int b200s_geometry(const B200sHandle* h, int W, int* W1, int* minX1, int* Dp, int* INV) {
+    if (!h) return B200S_E_INVALID;
+    Eff e = make_eff(h->params, 1, W);
+    if (W1) *W1 = e.W1;
+    if (minX1) *minX1 = e.minX1;
+    if (Dp) *Dp = e.Dp;
+    if (INV) *INV = e.INV;
+    return B200S_OK;
+}
+
+int b200s_set_maps(B200sHandle* h, const float* m1L, const float* m2L, const float* m1R, const float* m2R, int H, int W) {
+    if (!h) return B200S_E_INVALID;
+    if (!m1L || !m2L || !m1R || !m2R || H <= 0 || W <= 0) { h->set_error(B200S_E_INVALID, "set_maps: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    size_t n = (size_t)H * W;
+    CUDA_TRY(h, h->maps.ensure(4 * n * sizeof(float)));
+    const float* src[4] = {m1L, m2L, m1R, m2R};
+    for (int i = 0; i < 4; i++)
+        CUDA_TRY(h, cudaMemcpyAsync(h->maps.as<float>() + i * n, src[i], n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    h->mapH = H; h->mapW = W;
+    return B200S_OK;
+}
+
+}  // extern "C"
+
+// ---- internal stage graph (device pointers) -----------------------------------------------------------
+
+static int check_launch(B200sHandle* h, const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { h->set_error(B200S_E_CUDA, "%s: %s", what, cudaGetErrorString(e)); return B200S_E_CUDA; }
+    return B200S_OK;
+}
+
+static int dev_remap(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int sH, int sW, uint8_t* oL, uint8_t* oR) {
+    if (!h->maps.p) { h->set_error(B200S_E_STATE, "remap: rectification maps not set (call b200s_set_maps)"); return B200S_E_STATE; }
+    size_t n = (size_t)h->mapH * h->mapW;
+    const float* m = h->maps.as<float>();
+    launch_remap(dL, B, sH, sW, m, m + n, h->mapH, h->mapW, oL, h->stream);
+    launch_remap(dR, B, sH, sW, m + 2 * n, m + 3 * n, h->mapH, h->mapW, oR, h->stream);
+    h->launches += 2;
+    return check_launch(h, "remap");
+}
+
+// cv2.StereoSGBM.compute on a dense device batch
+static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int H, int W, int16_t* dDisp) {
+    if (B <= 0 || H <= 0 || W <= 0) { h->set_error(B200S_E_INVALID, "sgbm: empty input"); return B200S_E_INVALID; }
+    Eff e = make_eff(h->params, H, W);
+    const size_t npx = (size_t)B * H * W;
+    h->last_eff = e; h->last_B = B; h->have_last = true;
+    if (e.W1 <= 0) {  // no column has a full disparity range: everything invalid (A.0)
+        CUDA_TRY(h, h->raw.ensure(npx * 2));
+        // rare path: host-side fill
+        int16_t* tmp = (int16_t*)malloc(npx * 2);
+        if (!tmp) { h->set_error(B200S_E_CUDA, "out of host memory"); return B200S_E_CUDA; }
+        for (size_t i = 0; i < npx; i++) tmp[i] = (int16_t)e.INV;
+        cudaError_t ce = cudaMemcpyAsync(dDisp, tmp, npx * 2, cudaMemcpyHostToDevice, h->stream);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h->raw.p, tmp, npx * 2, cudaMemcpyHostToDevice, h->stream);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(h->stream);
+        free(tmp);
+        if (ce != cudaSuccess) { h->set_error(B200S_E_CUDA, "fill: %s", cudaGetErrorString(ce)); return B200S_E_CUDA; }
+        return B200S_OK;
+    }
+    const StripePlan sp = make_stripes(e);
+    const size_t vol = (size_t)B * H * e.W1 * e.Dp * sizeof(uint16_t);
+    CUDA_TRY(h, h->recL.ensure(npx * sizeof(uint2)));
+    CUDA_TRY(h, h->recR.ensure(npx * sizeof(uint2)));
+    CUDA_TRY(h, h->C.ensure(vol));
+    CUDA_TRY(h, h->S.ensure(vol));
+    if (sp.alt_rows > 0 && sp.n > 1)
+        CUDA_TRY(h, h->Calt.ensure((size_t)B * B200S_MAX_STRIPES * sp.alt_rows * e.W1 * e.Dp * sizeof(uint16_t)));
+    CUDA_TRY(h, h->raw.ensure(npx * 2));
+    launch_prefilter(e, dL, dR, B, h->recL.as<uint2>(), h->recR.as<uint2>(), h->stream);
+    h->launches++;
+    int rc = launch_cost(e, sp, h->recL.as<uint2>(), h->recR.as<uint2>(), B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->stream);
+    if (rc) { h->set_error(B200S_E_INVALID, "cost kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
+    h->launches++;
+    rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches);
+    if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
+    launch_wta(e, B, h->S.as<uint16_t>(), h->raw.as<int16_t>(), h->stream);
+    h->launches++;
+    launch_median3_s16(h->raw.as<int16_t>(), dDisp, B, H, W, h->stream);
+    h->launches++;
+    if (e.speckleWindowSize > 0) {
+        CUDA_TRY(h, h->labels.ensure(npx * sizeof(int)));
+        CUDA_TRY(h, h->sizes.ensure(npx * sizeof(int)));
+        launch_speckle(dDisp, B, H, W, e.INV, e.speckleWindowSize, 16 * e.speckleRange, h->labels.as<int>(), h->sizes.as<int>(),
+                       h->stream, &h->launches);
+    }
+    return check_launch(h, "sgbm");
+}
+
+// postprocess_disparity (hole filling off) / fast-mode median on a dense device batch, result in `out`
+static int dev_post(B200sHandle* h, const float* dIn, int B, int H, int W, const B200sPostParams& pp, float* out) {
+    const size_t n = (size_t)B * H * W;
+    if (pp.fastMode) {
+        launch_median3_f32(dIn, out, B, H, W, h->stream);
+        h->launches++;
+        return check_launch(h, "post(fast)");
+    }
+    CUDA_TRY(h, h->s16c.ensure(n * 2));
+    CUDA_TRY(h, h->labels.ensure(n * sizeof(int)));
+    CUDA_TRY(h, h->sizes.ensure(n * sizeof(int)));
+    CUDA_TRY(h, h->f1.ensure(n * sizeof(float)));
+    int16_t* s16 = h->s16c.as<int16_t>();
+    float* t = h->f1.as<float>();
+    launch_f32_to_s16x16(dIn, n, s16, h->stream);
+    launch_speckle(s16, B, H, W, 0, pp.maxSpeckleSize, pp.maxDiff16, h->labels.as<int>(), h->sizes.as<int>(), h->stream, &h->launches);
+    h->launches += 2;
+    if (pp.applyOutlierRemoval) {
+        launch_s16_to_f32_div16(s16, n, out, h->stream);       // out used as temp
+        launch_outliers(out, t, B, H, W, pp.outlierThreshold, h->stream);
+        launch_median3_f32(t, out, B, H, W, h->stream);
+        h->launches += 2;
+    } else {
+        launch_s16_to_f32_div16(s16, n, t, h->stream);
+        launch_median3_f32(t, out, B, H, W, h->stream);
+        h->launches += 1;
+    }
+    return check_launch(h, "post");
+}
+
+static int dev_pipeline(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int H, int W, int use_maps,
+                        const B200sPostParams& pp, const B200sDepthParams& dp, float* dDisp, float* dDepth,
+                        const uint8_t** rectLout, const uint8_t** rectRout) {
+    const size_t npx = (size_t)B * H * W;
+    const uint8_t* mL = dL;
+    const uint8_t* mR = dR;
+    if (use_maps) {
+        if (h->mapH != H || h->mapW != W) {
+            h->set_error(B200S_E_INVALID, "pipeline: image size %dx%d does not match the rectification maps %dx%d", W, H, h->mapW, h->mapH);
+            return B200S_E_INVALID;
+        }
+        CUDA_TRY(h, h->rectL.ensure(npx));
+        CUDA_TRY(h, h->rectR.ensure(npx));
+        int rc = dev_remap(h, dL, dR, B, H, W, h->rectL.as<uint8_t>(), h->rectR.as<uint8_t>());
+        if (rc) return rc;
+        mL = h->rectL.as<uint8_t>();
+        mR = h->rectR.as<uint8_t>();
+    }
+    if (rectLout) *rectLout = mL;
+    if (rectRout) *rectRout = mR;
+    const int x0 = h->params.numDisparities;  // crop [:, num_disp:] (stereo_core.py:168)
+    if (x0 >= W) { h->set_error(B200S_E_INVALID, "pipeline: numDisparities >= image width"); return B200S_E_INVALID; }
+    const int Wc = W - x0;
+    CUDA_TRY(h, h->med.ensure(npx * 2));
+    int rc = dev_sgbm(h, mL, mR, B, H, W, h->med.as<int16_t>());
+    if (rc) return rc;
+    const size_t nc = (size_t)B * H * Wc;
+    CUDA_TRY(h, h->f0.ensure(nc * sizeof(float)));
+    launch_disp16_to_f32_crop(h->med.as<int16_t>(), B, H, W, x0, h->f0.as<float>(), h->stream);
+    h->launches++;
+    rc = dev_post(h, h->f0.as<float>(), B, H, Wc, pp, dDisp);
+    if (rc) return rc;
+    if (dp.enabled && dDepth) {
+        launch_depth(dDisp, nc, dp, dDepth, h->stream);
+        h->launches++;
+    }
+    return check_launch(h, "pipeline");
+}
+
+struct Timed {
+    B200sHandle* h;
+    explicit Timed(B200sHandle* h_) : h(h_) { if (h->timing) cudaEventRecord(h->ev0, h->stream); }
+    void stop() {
+        if (h->timing) {
+            cudaEventRecord(h->ev1, h->stream);
+            cudaEventSynchronize(h->ev1);
+            cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+        }
+    }
+};
+
+static int upload_u8(B200sHandle* h, DevBuf& buf, const uint8_t* src, int H, int W, size_t stride) {
+    CUDA_TRY(h, buf.ensure((size_t)H * W));
+    CUDA_TRY(h, cudaMemcpy2DAsync(buf.p, W, src, stride, W, H, cudaMemcpyHostToDevice, h->stream));
+    return B200S_OK;
+}
+
+extern "C" {
+
+int b200s_bgr2gray(B200sHandle* h, const uint8_t* img, int H, int W, size_t stride, uint8_t* gray) {
+    if (!h) return B200S_E_INVALID;
+    if (!img || !gray || H <= 0 || W <= 0 || stride < (size_t)3 * W) { h->set_error(B200S_E_INVALID, "bgr2gray: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    size_t n = (size_t)H * W;
+    CUDA_TRY(h, h->hostio.ensure(3 * n));
+    CUDA_TRY(h, h->imgL.ensure(n));
+    CUDA_TRY(h, cudaMemcpy2DAsync(h->hostio.p, 3 * (size_t)W, img, stride, 3 * (size_t)W, H, cudaMemcpyHostToDevice, h->stream));
+    launch_bgr2gray(h->hostio.as<uint8_t>(), n, h->imgL.as<uint8_t>(), h->stream);
+    h->launches++;
+    CUDA_TRY(h, cudaMemcpyAsync(gray, h->imgL.p, n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "bgr2gray");
+}
+
+int b200s_remap_u8(B200sHandle* h, const uint8_t* L, const uint8_t* R, int srcH, int srcW, size_t stride, uint8_t* outL, uint8_t* outR) {
+    if (!h) return B200S_E_INVALID;
+    if (!L || !R || !outL || !outR || srcH <= 0 || srcW <= 0 || stride < (size_t)srcW) { h->set_error(B200S_E_INVALID, "remap: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    if (!h->maps.p) { h->set_error(B200S_E_STATE, "remap: rectification maps not set (call b200s_set_maps)"); return B200S_E_STATE; }
+    int rc = upload_u8(h, h->imgL, L, srcH, srcW, stride); if (rc) return rc;
+    rc = upload_u8(h, h->imgR, R, srcH, srcW, stride); if (rc) return rc;
+    size_t n = (size_t)h->mapH * h->mapW;
+    CUDA_TRY(h, h->rectL.ensure(n));
+    CUDA_TRY(h, h->rectR.ensure(n));
+    rc = dev_remap(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), 1, srcH, srcW, h->rectL.as<uint8_t>(), h->rectR.as<uint8_t>());
+    if (rc) return rc;
+    CUDA_TRY(h, cudaMemcpyAsync(outL, h->rectL.p, n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(outR, h->rectR.p, n, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return B200S_OK;
+}
+
+int b200s_sgbm_compute(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H, int W, size_t stride, int16_t* disp16) {
+    if (!h) return B200S_E_INVALID;
+    if (!L || !R || !disp16 || H <= 0 || W <= 0 || stride < (size_t)W) { h->set_error(B200S_E_INVALID, "sgbm_compute: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    int rc = upload_u8(h, h->imgL, L, H, W, stride); if (rc) return rc;
+    rc = upload_u8(h, h->imgR, R, H, W, stride); if (rc) return rc;
+    size_t n = (size_t)H * W;
+    CUDA_TRY(h, h->med.ensure(n * 2));
+    Timed t(h);
+    rc = dev_sgbm(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), 1, H, W, h->med.as<int16_t>());
+    if (rc) return rc;
+    t.stop();
+    CUDA_TRY(h, cudaMemcpyAsync(disp16, h->med.p, n * 2, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "sgbm_compute");
+}
+
+int b200s_postprocess(B200sHandle* h, float* disp, int H, int W, const B200sPostParams* pp) {
+    if (!h) return B200S_E_INVALID;
+    if (!disp || !pp || H <= 0 || W <= 0) { h->set_error(B200S_E_INVALID, "postprocess: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    size_t n = (size_t)H * W;
+    CUDA_TRY(h, h->f0.ensure(n * sizeof(float)));
+    CUDA_TRY(h, h->hostio.ensure(n * sizeof(float)));
+    CUDA_TRY(h, cudaMemcpyAsync(h->f0.p, disp, n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    int rc = dev_post(h, h->f0.as<float>(), 1, H, W, *pp, h->hostio.as<float>());
+    if (rc) return rc;
+    CUDA_TRY(h, cudaMemcpyAsync(disp, h->hostio.p, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "postprocess");
+}
+
+int b200s_disp_to_depth(B200sHandle* h, const float* disp, size_t n, const B200sDepthParams* dp, float* depth) {
+    if (!h) return B200S_E_INVALID;
+    if (!disp || !depth || !dp || n == 0) { h->set_error(B200S_E_INVALID, "disp_to_depth: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, h->f0.ensure(n * sizeof(float)));
+    CUDA_TRY(h, h->f1.ensure(n * sizeof(float)));
+    CUDA_TRY(h, cudaMemcpyAsync(h->f0.p, disp, n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    launch_depth(h->f0.as<float>(), n, *dp, h->f1.as<float>(), h->stream);
+    h->launches++;
+    CUDA_TRY(h, cudaMemcpyAsync(depth, h->f1.p, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "disp_to_depth");
+}
+
+int b200s_pipeline(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H, int W, size_t stride, int use_maps,
+                   const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth, uint8_t* rectL, uint8_t* rectR) {
+    if (!h) return B200S_E_INVALID;
+    if (!L || !R || !pp || !dp || !disp || H <= 0 || W <= 0 || stride < (size_t)W) { h->set_error(B200S_E_INVALID, "pipeline: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    int rc = upload_u8(h, h->imgL, L, H, W, stride); if (rc) return rc;
+    rc = upload_u8(h, h->imgR, R, H, W, stride); if (rc) return rc;
+    const int Wc = W - h->params.numDisparities;
+    if (Wc <= 0) { h->set_error(B200S_E_INVALID, "pipeline: numDisparities >= image width"); return B200S_E_INVALID; }
+    size_t nc = (size_t)H * Wc;
+    CUDA_TRY(h, h->hostio.ensure(2 * nc * sizeof(float)));
+    float* dDisp = h->hostio.as<float>();
+    float* dDepth = dDisp + nc;
+    const uint8_t *rl = nullptr, *rr = nullptr;
+    Timed t(h);
+    rc = dev_pipeline(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), 1, H, W, use_maps, *pp, *dp, dDisp, dDepth, &rl, &rr);
+    if (rc) return rc;
+    t.stop();
+    CUDA_TRY(h, cudaMemcpyAsync(disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (dp->enabled && depth) CUDA_TRY(h, cudaMemcpyAsync(depth, dDepth, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (rectL) CUDA_TRY(h, cudaMemcpyAsync(rectL, rl, (size_t)H * W, cudaMemcpyDeviceToHost, h->stream));
+    if (rectR) CUDA_TRY(h, cudaMemcpyAsync(rectR, rr, (size_t)H * W, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "pipeline");
+}
+
+int b200s_sgbm_compute_batch_dev(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int H, int W, int16_t* dDisp16) {
+    if (!h) return B200S_E_INVALID;
+    if (!dL || !dR || !dDisp16) { h->set_error(B200S_E_INVALID, "sgbm_compute_batch_dev: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    Timed t(h);
+    int rc = dev_sgbm(h, dL, dR, B, H, W, dDisp16);
+    if (rc) return rc;
+    t.stop();
+    return B200S_OK;
+}
+
+int b200s_pipeline_batch_dev(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int H, int W, int use_maps,
+                             const B200sPostParams* pp, const B200sDepthParams* dp, float* dDisp, float* dDepth) {
+    if (!h) return B200S_E_INVALID;
+    if (!dL || !dR || !pp || !dp || !dDisp) { h->set_error(B200S_E_INVALID, "pipeline_batch_dev: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    Timed t(h);
+    int rc = dev_pipeline(h, dL, dR, B, H, W, use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
+    if (rc) return rc;
+    t.stop();
+    return B200S_OK;
+}
+
+int b200s_debug_stage(B200sHandle* h, int which, int b, int16_t* out) {
+    if (!h) return B200S_E_INVALID;
+    if (!h->have_last || !out || b < 0 || b >= h->last_B) { h->set_error(B200S_E_STATE, "debug_stage: no previous sgbm call / bad frame"); return B200S_E_STATE; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const Eff& e = h->last_eff;
+    if (which == 2) {
+        size_t n = (size_t)e.H * e.W;
+        CUDA_TRY(h, cudaMemcpyAsync(out, h->raw.as<int16_t>() + (size_t)b * n, n * 2, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+        return B200S_OK;
+    }
+    if (which != 0 && which != 1) { h->set_error(B200S_E_INVALID, "debug_stage: which must be 0, 1 or 2"); return B200S_E_INVALID; }
+    if (e.W1 <= 0) { h->set_error(B200S_E_STATE, "debug_stage: empty cost domain"); return B200S_E_STATE; }
+    size_t cells = (size_t)e.H * e.W1 * e.D;
+    CUDA_TRY(h, h->hostio.ensure(cells * 2));
+    const uint16_t* V = (which == 0 ? h->C.as<uint16_t>() : h->S.as<uint16_t>()) + (size_t)b * e.H * e.W1 * e.Dp;
+    launch_debug_volume(V, e.H, e.W1, e.Dp, e.D, which == 0 ? e.P2e : 0, h->hostio.as<int16_t>(), h->stream);
+    CUDA_TRY(h, cudaMemcpyAsync(out, h->hostio.p, cells * 2, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "debug_stage");
+}
+
+}  // extern "C"

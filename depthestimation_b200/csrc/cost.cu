@@ -1,0 +1,261 @@
+// cost.cu — prefilter (A.1), Birchfield–Tomasi pixel cost (A.2) and bs x bs block sum (A.3).
+//
+// Replaces the cost-volume part of cv2.StereoSGBM.compute as called at
+// depthlib/stereo_core.py:231. Output: C[b][y][xc][d] (u16, d fastest, pitch Dp), WITHOUT the
+// reference's +P2 term (the path recursion is rewritten so it is never needed, see paths.cu).
+//
+// Kernel k_cost: one CTA = a strip of XT cost columns x all disparities, marching down a row
+// segment. Thread = one disparity pair (packed 16x2). Per source row the thread slides along x
+// with a register ring of the last BS pixel costs (horizontal box sum), and keeps XT running
+// vertical sums in registers, fed by a shared-memory ring of the last BS horizontal-sum rows.
+// Everything is packed-16x2 integer SIMD (VIADD.16x2 / VIADDMNMX.S16x2.RELU / VIMNMX.S16x2).
+#include "common.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// prefilter: one thread per pixel -> 8-byte record {g, g_lo, g_hi, r, r_lo, r_hi, 0, 0}
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int sobel_clip(const uint8_t* __restrict__ c, const uint8_t* __restrict__ n,
+                                          const uint8_t* __restrict__ s, int x, int W, int ftzero) {
+    if (x <= 0 || x >= W - 1) return ftzero;  // border columns: g = ftzero
+    int v = 2 * ((int)c[x + 1] - (int)c[x - 1]) + ((int)n[x + 1] - (int)n[x - 1]) + ((int)s[x + 1] - (int)s[x - 1]);
+    return min(max(v, -ftzero), ftzero) + ftzero;
+}
+__device__ __forceinline__ int raw_px(const uint8_t* __restrict__ c, int x, int W, int ftzero) {
+    return (x <= 0 || x >= W - 1) ? ftzero : (int)c[x];  // raw channel border is ftzero too
+}
+
+__global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ L, const uint8_t* __restrict__ R,
+                                                   int H, int W, int ftzero, uint2* __restrict__ recL,
+                                                   uint2* __restrict__ recR) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    int z = blockIdx.z;  // 2*b + image
+    if (x >= W) return;
+    int b = z >> 1;
+    const uint8_t* img = ((z & 1) ? R : L) + (size_t)b * H * W;
+    uint2* rec = ((z & 1) ? recR : recL) + (size_t)b * H * W;
+    const uint8_t* c = img + (size_t)y * W;
+    const uint8_t* n = img + (size_t)max(y - 1, 0) * W;
+    const uint8_t* s = img + (size_t)min(y + 1, H - 1) * W;
+    int g0 = sobel_clip(c, n, s, x, W, ftzero);
+    int r0 = raw_px(c, x, W, ftzero);
+    int glo = g0, ghi = g0, rlo = r0, rhi = r0;
+    if (x > 0) {
+        int ga = (g0 + sobel_clip(c, n, s, x - 1, W, ftzero)) >> 1;
+        int ra = (r0 + raw_px(c, x - 1, W, ftzero)) >> 1;
+        glo = min(glo, ga); ghi = max(ghi, ga); rlo = min(rlo, ra); rhi = max(rhi, ra);
+    }
+    if (x < W - 1) {
+        int gb = (g0 + sobel_clip(c, n, s, x + 1, W, ftzero)) >> 1;
+        int rb = (r0 + raw_px(c, x + 1, W, ftzero)) >> 1;
+        glo = min(glo, gb); ghi = max(ghi, gb); rlo = min(rlo, rb); rhi = max(rhi, rb);
+    }
+    uint2 o;
+    o.x = (unsigned)g0 | ((unsigned)glo << 8) | ((unsigned)ghi << 16) | ((unsigned)r0 << 24);
+    o.y = (unsigned)rlo | ((unsigned)rhi << 8);
+    rec[(size_t)y * W + x] = o;
+}
+
+void launch_prefilter(const Eff& e, const uint8_t* L, const uint8_t* R, int B, uint2* recL, uint2* recR,
+                      cudaStream_t st) {
+    dim3 grid((e.W + 255) / 256, e.H, 2 * B);
+    k_prefilter<<<grid, 256, 0, st>>>(L, R, e.H, e.W, e.ftzero, recL, recR);
+}
+
+// ------------------------------------------------------------------------------------------------
+// block cost
+// ------------------------------------------------------------------------------------------------
+struct CostArgs {
+    const uint2* recL;
+    const uint2* recR;
+    uint16_t* C;
+    uint16_t* Calt;
+    int H, W, W1, D, Dp, minD, minX1, SH2, mode;
+    int RS, nreg;           // rows per regular segment, number of regular segments
+    StripePlan sp;          // alt segments: one per stripe >= 1 when sp.alt_rows > 0
+};
+
+// right-image arrays in shared memory, stored reversed in x so that increasing d walks forward
+enum { RA_VG = 0, RA_NVG, RA_LOG, RA_NHIG, RA_VR, RA_NVR, RA_LOR, RA_NHIR, RA_COUNT };
+
+template <int BS, int XT>
+__global__ void __launch_bounds__(128) k_cost(const CostArgs a) {
+    constexpr int NXI = XT + BS - 1;  // pixel-cost columns evaluated per row (with halo)
+    extern __shared__ __align__(16) unsigned smem[];
+    const int NT = blockDim.x;        // Dp / 2 threads, one disparity pair each
+    const int dp = threadIdx.x;
+    const int xa = blockIdx.x * XT;   // first cost column of the strip
+    const int b = blockIdx.z;
+
+    // ---- which rows does this CTA produce? -------------------------------------------------
+    int y0, y1, ylo;
+    uint16_t* out;
+    {
+        int seg = blockIdx.y;
+        if (seg < a.nreg) {
+            y0 = seg * a.RS; y1 = min(y0 + a.RS, a.H); ylo = 0;
+            out = a.C + (size_t)b * a.H * a.W1 * a.Dp;           // indexed by absolute row
+        } else {
+            int n = seg - a.nreg + 1;                              // stripe-local rows (A.7)
+            y0 = a.sp.a[n]; y1 = min(y0 + a.sp.alt_rows, a.sp.r1[n]); ylo = y0;
+            out = a.Calt + ((size_t)(b * B200S_MAX_STRIPES + n) * a.sp.alt_rows) * a.W1 * a.Dp
+                  - (size_t)y0 * a.W1 * a.Dp;                      // so that out[row y] lands at local row y - y0
+        }
+    }
+    if (y0 >= y1) return;
+
+    // ---- shared memory carve-up ---------------------------------------------------------------
+    const int xc_min = min(max(xa - BS / 2, 0), a.W1 - 1);
+    const int xc_max = min(max(xa + XT - 1 + BS / 2, 0), a.W1 - 1);
+    const int x_min = xc_min + a.minX1, x_max = xc_max + a.minX1;      // left-image columns touched
+    const int NR = (x_max - x_min) + 2 * NT + 2;                      // right-image samples (reversed)
+    const int NRW = (NR + 1) / 2 + 1;                                  // words per alignment copy
+    unsigned* ring = smem;                                             // [BS][XT][NT]
+    unsigned* sL = ring + BS * XT * NT;                                // [NXI][8]
+    unsigned* sR = sL + NXI * 8;                                       // [2][RA_COUNT][NRW]
+    unsigned short* sRh = (unsigned short*)(sR + 2 * RA_COUNT * NRW);  // staging: [RA_COUNT][NR + 2] halves
+
+    for (int i = threadIdx.x; i < BS * XT * NT; i += NT) ring[i] = 0u;
+
+    unsigned V[XT];
+#pragma unroll
+    for (int i = 0; i < XT; i++) V[i] = 0u;
+
+    const size_t frame = (size_t)b * a.H * a.W;
+    const int xr_hi = x_max - a.minD;  // right x for d index 0 at the right-most left pixel
+    const int s_begin = y0 - a.SH2, s_end = y1 - 1 + a.SH2;
+
+    for (int s = s_begin; s <= s_end; s++) {
+        const int yc = min(max(s, ylo), a.H - 1);
+        const int slot = (s - s_begin) % BS;
+        __syncthreads();  // previous row's readers are done with sL / sR
+        // -- left pixels: replicated pairs {u, -u, lo1, -hi1} for g and r, indexed by halo column
+        for (int i = threadIdx.x; i < NXI; i += NT) {
+            int xc = min(max(xa - BS / 2 + i, 0), a.W1 - 1);
+            uint2 r = a.recL[frame + (size_t)yc * a.W + xc + a.minX1];
+            unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
+            unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
+            uint4 w0, w1;
+            w0.x = pk2(g); w0.y = pk2(0u - g); w0.z = pk2(glo); w0.w = pk2(0u - ghi);
+            w1.x = pk2(rr); w1.y = pk2(0u - rr); w1.z = pk2(rlo); w1.w = pk2(0u - rhi);
+            *(uint4*)(sL + i * 8) = w0;
+            *(uint4*)(sL + i * 8 + 4) = w1;
+        }
+        // -- right pixels, reversed: half index i <-> right x = xr_hi - i
+        for (int i = threadIdx.x; i < NR + 2; i += NT) {
+            int xr = xr_hi - i;
+            unsigned g = 0, glo = 0, ghi = 0, rr = 0, rlo = 0, rhi = 0;
+            if (xr >= 0 && xr < a.W) {
+                uint2 r = a.recR[frame + (size_t)yc * a.W + xr];
+                g = r.x & 255u; glo = (r.x >> 8) & 255u; ghi = (r.x >> 16) & 255u;
+                rr = r.x >> 24; rlo = r.y & 255u; rhi = (r.y >> 8) & 255u;
+            }
+            const int P = NR + 2;
+            sRh[RA_VG * P + i] = (unsigned short)g;    sRh[RA_NVG * P + i] = (unsigned short)(0u - g);
+            sRh[RA_LOG * P + i] = (unsigned short)glo; sRh[RA_NHIG * P + i] = (unsigned short)(0u - ghi);
+            sRh[RA_VR * P + i] = (unsigned short)rr;   sRh[RA_NVR * P + i] = (unsigned short)(0u - rr);
+            sRh[RA_LOR * P + i] = (unsigned short)rlo; sRh[RA_NHIR * P + i] = (unsigned short)(0u - rhi);
+        }
+        __syncthreads();
+        // -- two alignment copies of packed pairs: copy c word k = (half[2k + c], half[2k + c + 1])
+        for (int i = threadIdx.x; i < 2 * RA_COUNT * NRW; i += NT) {
+            int k = i % NRW, arr = (i / NRW) % RA_COUNT, c = i / (NRW * RA_COUNT);
+            int h0 = 2 * k + c;
+            const int P = NR + 2;
+            unsigned lo = (h0 < P) ? sRh[arr * P + h0] : 0u;
+            unsigned hi = (h0 + 1 < P) ? sRh[arr * P + h0 + 1] : 0u;
+            sR[i] = lo | (hi << 16);
+        }
+        __syncthreads();
+
+        // -- slide along the strip: pixel cost -> horizontal box sum -> vertical running sum
+        unsigned pr[BS];
+#pragma unroll
+        for (int j = 0; j < BS; j++) pr[j] = 0u;
+        unsigned hs = 0u;
+#pragma unroll
+        for (int i = 0; i < NXI; i++) {
+            const int xc = min(max(xa - BS / 2 + i, 0), a.W1 - 1);
+            const int e = x_max - (xc + a.minX1);            // uniform
+            const unsigned* base = sR + (e & 1) * RA_COUNT * NRW + (e >> 1) + dp;
+            const uint4 l0 = *(const uint4*)(sL + i * 8);     // {u, -u, lo1, -hi1} gradient channel
+            const uint4 l1 = *(const uint4*)(sL + i * 8 + 4); // raw channel
+            unsigned vg = base[RA_VG * NRW], nvg = base[RA_NVG * NRW], log2_ = base[RA_LOG * NRW],
+                     nhig = base[RA_NHIG * NRW];
+            unsigned vr = base[RA_VR * NRW], nvr = base[RA_NVR * NRW], lor = base[RA_LOR * NRW],
+                     nhir = base[RA_NHIR * NRW];
+            // c0 = max(0, u - hi2, lo2 - u); c1 = max(0, v - hi1, lo1 - v); cost = min(c0, c1)
+            unsigned c0 = __viaddmax_s16x2_relu(nhig, l0.x, __vadd2(log2_, l0.y));
+            unsigned c1 = __viaddmax_s16x2_relu(vg, l0.w, __vadd2(nvg, l0.z));
+            unsigned cg = __vmins2(c0, c1);
+            c0 = __viaddmax_s16x2_relu(nhir, l1.x, __vadd2(lor, l1.y));
+            c1 = __viaddmax_s16x2_relu(vr, l1.w, __vadd2(nvr, l1.z));
+            unsigned cr = (__vmins2(c0, c1) >> 2) & 0x3fff3fffu;
+            unsigned pix = cg + cr;
+            hs = hs + pix - pr[i % BS];
+            pr[i % BS] = pix;
+            if (i >= BS - 1) {
+                const int xo = i - (BS - 1);
+                unsigned* rp = ring + (slot * XT + xo) * NT + dp;
+                unsigned old = *rp;
+                *rp = hs;
+                V[xo] = V[xo] + hs - old;
+            }
+        }
+        // -- emit the output row whose window just completed
+        if (s - s_begin >= BS - 1) {
+            const int y = s - a.SH2;
+            const bool flat = (a.mode == B200S_MODE_HH4) && (y > 0) && (y + a.SH2 >= a.H);
+            unsigned* orow = (unsigned*)(out + ((size_t)y * a.W1 + xa) * a.Dp) + dp;
+#pragma unroll
+            for (int xo = 0; xo < XT; xo++)
+                if (xa + xo < a.W1) orow[(size_t)xo * (a.Dp / 2)] = flat ? 0u : V[xo];
+        }
+    }
+}
+
+template <int BS, int XT>
+static int launch_cost_t(const CostArgs& a, int B, int nseg, cudaStream_t st) {
+    const int NT = a.Dp / 2;
+    const int NXI = XT + BS - 1;
+    const int NRmax = NXI + 2 * NT + 2;
+    const int NRW = (NRmax + 1) / 2 + 1;
+    size_t smem = (size_t)BS * XT * NT * 4 + (size_t)NXI * 8 * 4 + (size_t)2 * RA_COUNT * NRW * 4 +
+                  (size_t)RA_COUNT * (NRmax + 2) * 2 + 64;
+    if (smem > 220 * 1024) return -1;
+    cudaFuncSetAttribute(k_cost<BS, XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    dim3 grid((a.W1 + XT - 1) / XT, nseg, B);
+    k_cost<BS, XT><<<grid, NT, smem, st>>>(a);
+    return 0;
+}
+
+template <int BS>
+static int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
+    // wide strips amortise the horizontal halo; fall back to narrow strips when the hsum ring
+    // would not fit in shared memory (large D x large block size)
+    size_t ring32 = (size_t)BS * 32 * (a.Dp / 2) * 4;
+    if (ring32 <= 96 * 1024) return launch_cost_t<BS, 32>(a, B, nseg, st);
+    return launch_cost_t<BS, 8>(a, B, nseg, st);
+}
+
+int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uint2* recR, int B, uint16_t* C,
+                uint16_t* Calt, cudaStream_t st) {
+    CostArgs a;
+    a.recL = recL; a.recR = recR; a.C = C; a.Calt = Calt;
+    a.H = e.H; a.W = e.W; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.minD = e.minD; a.minX1 = e.minX1;
+    a.SH2 = e.SH2; a.mode = e.mode;
+    a.RS = 32;
+    a.nreg = (e.H + a.RS - 1) / a.RS;
+    a.sp = sp;
+    int nseg = a.nreg + ((sp.alt_rows > 0 && sp.n > 1) ? sp.n - 1 : 0);
+    if (e.Dp / 2 > 128) return -2;  // D > 256 not supported by this kernel
+    switch (e.bs) {
+        case 1: return launch_cost_bs<1>(a, B, nseg, st);
+        case 3: return launch_cost_bs<3>(a, B, nseg, st);
+        case 5: return launch_cost_bs<5>(a, B, nseg, st);
+        case 7: return launch_cost_bs<7>(a, B, nseg, st);
+        case 9: return launch_cost_bs<9>(a, B, nseg, st);
+        case 11: return launch_cost_bs<11>(a, B, nseg, st);
+        default: return -3;
+    }
+}

@@ -1,0 +1,260 @@
+// imgops.cu — the O(N) image ops on depthlib's stereo path:
+//   remap         cv2.remap(gray, map1, map2, INTER_LINEAR)          depthlib/rectify.py:185-186
+//   bgr2gray      cv2.cvtColor(img, COLOR_BGR2GRAY)                  depthlib/rectify.py:116, stereo_core.py:157-159
+//   median3 s16   the medianBlur(3) inside StereoSGBM.compute (A.8)  depthlib/stereo_core.py:231
+//   speckle       cv2.filterSpeckles (A.8 and postprocess.py:30)     depthlib/postprocess.py:6-35
+//   outliers      detect_outliers + masking                          depthlib/postprocess.py:37-70,151-158
+//   median3 f32   cv2.medianBlur(float32, 3)                         depthlib/postprocess.py:169, stereo_core.py:173
+//   depth         StereoCore.disparity_to_depth                      depthlib/stereo_core.py:234-272
+// The float chain uses explicit round-to-nearest intrinsics (no FMA contraction, no fast math).
+#include "common.cuh"
+
+// ---- B.1 remap: fixed-point bilinear, 5 fractional bits, constant-0 border ---------------------
+__global__ void __launch_bounds__(256) k_remap(const uint8_t* __restrict__ src, int sH, int sW,
+                                               const float* __restrict__ m1, const float* __restrict__ m2, int H, int W,
+                                               uint8_t* __restrict__ dst) {
+    const size_t n = (size_t)H * W;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t* s = src + (size_t)blockIdx.y * sH * sW;
+    int sx = __float2int_rn(__fmul_rn(m1[i], 32.0f));
+    int sy = __float2int_rn(__fmul_rn(m2[i], 32.0f));
+    int ix = sx >> 5, iy = sy >> 5, fx = sx & 31, fy = sy & 31;
+    int p00 = 0, p01 = 0, p10 = 0, p11 = 0;
+    const bool x0 = (ix >= 0 && ix < sW), x1 = (ix + 1 >= 0 && ix + 1 < sW);
+    if (iy >= 0 && iy < sH) {
+        const uint8_t* r = s + (size_t)iy * sW;
+        if (x0) p00 = r[ix];
+        if (x1) p01 = r[ix + 1];
+    }
+    if (iy + 1 >= 0 && iy + 1 < sH) {
+        const uint8_t* r = s + (size_t)(iy + 1) * sW;
+        if (x0) p10 = r[ix];
+        if (x1) p11 = r[ix + 1];
+    }
+    int acc = (32 - fy) * ((32 - fx) * p00 + fx * p01) + fy * ((32 - fx) * p10 + fx * p11);
+    dst[(size_t)blockIdx.y * n + i] = (uint8_t)((acc * 32 + 16384) >> 15);
+}
+
+void launch_remap(const uint8_t* src, int B, int sH, int sW, const float* m1, const float* m2, int H, int W,
+                  uint8_t* dst, cudaStream_t st) {
+    dim3 grid((unsigned)(((size_t)H * W + 255) / 256), B);
+    k_remap<<<grid, 256, 0, st>>>(src, sH, sW, m1, m2, H, W, dst);
+}
+
+// ---- B.2 gray ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bgr2gray(const uint8_t* __restrict__ img, size_t npix, uint8_t* __restrict__ dst) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    int c0 = img[3 * i], c1 = img[3 * i + 1], c2 = img[3 * i + 2];
+    dst[i] = (uint8_t)((3735 * c0 + 19235 * c1 + 9798 * c2 + 16384) >> 15);
+}
+void launch_bgr2gray(const uint8_t* img, size_t npix, uint8_t* dst, cudaStream_t st) {
+    k_bgr2gray<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(img, npix, dst);
+}
+
+// ---- 3x3 median, replicate border ------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void cswap(T& a, T& b) {
+    T lo = a < b ? a : b, hi = a < b ? b : a;
+    a = lo; b = hi;
+}
+template <typename T>
+__device__ __forceinline__ T median9(T v0, T v1, T v2, T v3, T v4, T v5, T v6, T v7, T v8) {
+    cswap(v1, v2); cswap(v4, v5); cswap(v7, v8);
+    cswap(v0, v1); cswap(v3, v4); cswap(v6, v7);
+    cswap(v1, v2); cswap(v4, v5); cswap(v7, v8);
+    cswap(v0, v3); cswap(v5, v8); cswap(v4, v7);
+    cswap(v3, v6); cswap(v1, v4); cswap(v2, v5);
+    cswap(v4, v7); cswap(v4, v2); cswap(v6, v4);
+    cswap(v4, v2);
+    return v4;
+}
+template <typename T>
+__global__ void __launch_bounds__(256) k_median3(const T* __restrict__ src, T* __restrict__ dst, int H, int W) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    if (x >= W) return;
+    const T* s = src + (size_t)blockIdx.z * H * W;
+    int xm = max(x - 1, 0), xp = min(x + 1, W - 1);
+    const T* r0 = s + (size_t)max(y - 1, 0) * W;
+    const T* r1 = s + (size_t)y * W;
+    const T* r2 = s + (size_t)min(y + 1, H - 1) * W;
+    dst[(size_t)blockIdx.z * H * W + (size_t)y * W + x] =
+        median9<T>(r0[xm], r0[x], r0[xp], r1[xm], r1[x], r1[xp], r2[xm], r2[x], r2[xp]);
+}
+void launch_median3_s16(const int16_t* src, int16_t* dst, int B, int H, int W, cudaStream_t st) {
+    dim3 grid((W + 255) / 256, H, B);
+    k_median3<int16_t><<<grid, 256, 0, st>>>(src, dst, H, W);
+}
+void launch_median3_f32(const float* src, float* dst, int B, int H, int W, cudaStream_t st) {
+    dim3 grid((W + 255) / 256, H, B);
+    k_median3<float><<<grid, 256, 0, st>>>(src, dst, H, W);
+}
+
+// ---- B.3 speckle filter: union-find connected components with a neighbour-difference predicate ------
+__device__ __forceinline__ int uf_find(const int* lab, int i) {
+    int p = ((volatile const int*)lab)[i];
+    while (p != i) { i = p; p = ((volatile const int*)lab)[i]; }
+    return i;
+}
+__device__ __forceinline__ void uf_union(int* lab, int a, int b) {
+    while (true) {
+        a = uf_find(lab, a);
+        b = uf_find(lab, b);
+        if (a == b) return;
+        if (a < b) { int t = a; a = b; b = t; }   // hook the larger root under the smaller
+        int old = atomicMin(&lab[a], b);
+        if (old == a) return;
+        a = old;
+    }
+}
+__global__ void __launch_bounds__(256) k_ccl_init(const int16_t* __restrict__ img, size_t n, int newVal, int* lab, int* sizes) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    lab[i] = (img[i] != newVal) ? (int)i : -1;
+    sizes[i] = 0;
+}
+__global__ void __launch_bounds__(256) k_ccl_merge(const int16_t* __restrict__ img, int B, int H, int W, int newVal,
+                                                   int maxDiff, int* lab) {
+    size_t n = (size_t)B * H * W;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int v = img[i];
+    if (v == newVal) return;
+    int x = (int)(i % W), y = (int)((i / W) % H);
+    if (x + 1 < W) {
+        int q = img[i + 1];
+        if (q != newVal && abs(q - v) <= maxDiff) uf_union(lab, (int)i, (int)i + 1);
+    }
+    if (y + 1 < H) {
+        int q = img[i + W];
+        if (q != newVal && abs(q - v) <= maxDiff) uf_union(lab, (int)i, (int)i + W);
+    }
+}
+__global__ void __launch_bounds__(256) k_ccl_count(size_t n, int* lab, int* sizes) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int root = -1;
+    if (i < n && lab[i] >= 0) {
+        root = uf_find(lab, (int)i);
+        lab[i] = root;  // roots never change in this kernel, so compressing is race-free
+    }
+    // warp-aggregated count: one atomic per distinct root per warp
+    unsigned peers = __match_any_sync(0xffffffffu, root);
+    if (root >= 0 && (threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&sizes[root], __popc(peers));
+}
+__global__ void __launch_bounds__(256) k_ccl_apply(int16_t* img, size_t n, int newVal, int maxSize, const int* __restrict__ lab,
+                                                   const int* __restrict__ sizes) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int r = lab[i];
+    if (r >= 0 && sizes[r] <= maxSize) img[i] = (int16_t)newVal;
+}
+void launch_speckle(int16_t* img, int B, int H, int W, int newVal, int maxSize, int maxDiff, int* labels, int* sizes,
+                    cudaStream_t st, long long* launches) {
+    size_t n = (size_t)B * H * W;
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    k_ccl_init<<<blocks, 256, 0, st>>>(img, n, newVal, labels, sizes);
+    k_ccl_merge<<<blocks, 256, 0, st>>>(img, B, H, W, newVal, maxDiff, labels);
+    k_ccl_count<<<blocks, 256, 0, st>>>(n, labels, sizes);
+    k_ccl_apply<<<blocks, 256, 0, st>>>(img, n, newVal, maxSize, labels, sizes);
+    if (launches) *launches += 4;
+}
+
+// ---- conversions ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_d16_to_f32_crop(const int16_t* __restrict__ d16, int H, int W, int x0, float* __restrict__ out) {
+    int Wc = W - x0;
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= Wc) return;
+    size_t row = (size_t)blockIdx.z * H + blockIdx.y;
+    out[row * Wc + x] = __fdiv_rn((float)d16[row * W + x0 + x], 16.0f);
+}
+void launch_disp16_to_f32_crop(const int16_t* d16, int B, int H, int W, int x0, float* out, cudaStream_t st) {
+    dim3 grid((W - x0 + 255) / 256, H, B);
+    k_d16_to_f32_crop<<<grid, 256, 0, st>>>(d16, H, W, x0, out);
+}
+// (d * 16).astype(int16): C truncation toward zero, then wrap to 16 bits (numpy behaviour for in-range values)
+__global__ void __launch_bounds__(256) k_f32_to_s16x16(const float* __restrict__ d, size_t n, int16_t* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = (int16_t)__float2int_rz(__fmul_rn(d[i], 16.0f));
+}
+void launch_f32_to_s16x16(const float* d, size_t n, int16_t* out, cudaStream_t st) {
+    k_f32_to_s16x16<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d, n, out);
+}
+__global__ void __launch_bounds__(256) k_s16_to_f32_div16(const int16_t* __restrict__ d, size_t n, float* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = __fdiv_rn((float)d[i], 16.0f);
+}
+void launch_s16_to_f32_div16(const int16_t* d, size_t n, float* out, cudaStream_t st) {
+    k_s16_to_f32_div16<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d, n, out);
+}
+
+// ---- B.3' outlier mask: 5x5 box mean of d and d^2 (REFLECT_101, double accumulation) --------------------
+__device__ __forceinline__ int reflect101(int p, int n) {
+    if (n == 1) return 0;
+    while (p < 0 || p >= n) p = (p < 0) ? -p : 2 * (n - 1) - p;
+    return p;
+}
+__global__ void __launch_bounds__(256) k_outliers(const float* __restrict__ d, float* __restrict__ out, int H, int W, float thr) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    if (x >= W) return;
+    const float* s = d + (size_t)blockIdx.z * H * W;
+    double sum = 0.0, sumsq = 0.0;
+#pragma unroll
+    for (int dy = -2; dy <= 2; dy++) {
+        const float* r = s + (size_t)reflect101(y + dy, H) * W;
+        double rs = 0.0, rq = 0.0;
+#pragma unroll
+        for (int dx = -2; dx <= 2; dx++) {
+            float v = r[reflect101(x + dx, W)];
+            rs = __dadd_rn(rs, (double)v);
+            rq = __dadd_rn(rq, (double)__fmul_rn(v, v));
+        }
+        sum = __dadd_rn(sum, rs);
+        sumsq = __dadd_rn(sumsq, rq);
+    }
+    const float mean = (float)__dmul_rn(sum, 1.0 / 25.0);
+    const float msq = (float)__dmul_rn(sumsq, 1.0 / 25.0);
+    const float var = __fsub_rn(msq, __fmul_rn(mean, mean));
+    const float sd = __fsqrt_rn(fmaxf(var, 0.0f));
+    const float v = s[(size_t)y * W + x];
+    const float diff = fabsf(__fsub_rn(v, mean));
+    const bool outl = (diff > __fmul_rn(thr, sd)) && (v > 0.0f);
+    out[(size_t)blockIdx.z * H * W + (size_t)y * W + x] = outl ? 0.0f : v;
+}
+void launch_outliers(const float* d, float* out, int B, int H, int W, float thr, cudaStream_t st) {
+    dim3 grid((W + 255) / 256, H, B);
+    k_outliers<<<grid, 256, 0, st>>>(d, out, H, W, thr);
+}
+
+// ---- B.4 depth ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_depth(const float* __restrict__ disp, size_t n, float fB, float doffs, float eps,
+                                               float maxDepth, int hasMax, float* __restrict__ Z) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float adj = __fadd_rn(disp[i], doffs);
+    float z = __int_as_float(0x7f800000);
+    if (adj > eps) z = __fdiv_rn(fB, adj);
+    if (hasMax && z > maxDepth) z = maxDepth;
+    Z[i] = z;
+}
+void launch_depth(const float* disp, size_t n, const B200sDepthParams& dp, float* Z, cudaStream_t st) {
+    k_depth<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(disp, n, dp.fB, dp.doffs, dp.eps, dp.maxDepth, dp.hasMaxDepth, Z);
+}
+
+// ---- debug tap: strip the Dp padding (and add P2 back for C) ------------------------------------------------------
+__global__ void __launch_bounds__(256) k_debug_volume(const uint16_t* __restrict__ V, size_t npx, int Dp, int D, int add,
+                                                      int16_t* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npx * D) return;
+    size_t p = i / D;
+    int d = (int)(i % D);
+    out[i] = (int16_t)((int)V[p * Dp + d] + add);
+}
+void launch_debug_volume(const uint16_t* V, int H, int W1, int Dp, int D, int add, int16_t* out, cudaStream_t st) {
+    size_t npx = (size_t)H * W1;
+    k_debug_volume<<<(unsigned)((npx * D + 255) / 256), 256, 0, st>>>(V, npx, Dp, D, add, out);
+}

@@ -1,0 +1,153 @@
+/*
+ * b200stereo.h — C ABI of the B200-native stereo engine (libb200stereo.so).
+ *
+ * The reference (mspaintenjoyer/DepthEstimation, `depthlib`) has no FFI layer of its own: its
+ * boundary is the Python class StereoCore and the cv2.* calls it makes. Each entry point below
+ * replaces one of those calls on the per-frame path; the reference interface it stands in for is
+ * cited as depthlib/<file>:<line>. All signatures are plain C (pointers + sizes, no torch types).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative B200S_E_* code otherwise;
+ *     b200s_last_error(h) returns a human-readable message for the last failure on that handle
+ *   - "host" entry points take caller-owned host buffers (row stride given in BYTES for u8
+ *     images; other buffers are dense) and are synchronous: H2D copy -> kernels -> D2H copy
+ *   - "_dev" entry points take DEVICE pointers to dense batches and only enqueue work on the
+ *     handle's stream (call b200s_sync or synchronise the stream yourself)
+ *   - a handle owns one CUDA stream + all scratch (cost volume C, aggregate S, labels ...);
+ *     use one handle per host thread / per GPU, like one cv2.StereoSGBM object per thread
+ *   - there is NO CPU fallback: without a CUDA device every call fails with B200S_E_CUDA
+ */
+#ifndef B200STEREO_H
+#define B200STEREO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200S_ABI_VERSION 1
+
+enum {
+    B200S_OK = 0,
+    B200S_E_INVALID = -1,   /* bad argument / unsupported parameter combination */
+    B200S_E_CUDA = -2,      /* CUDA runtime error (no device, OOM, launch failure) */
+    B200S_E_STATE = -3      /* call order problem, e.g. remap before set_maps */
+};
+
+/* cv2.STEREO_SGBM_MODE_* values, as mapped at depthlib/stereo_core.py:55-61 */
+enum { B200S_MODE_SGBM = 0, B200S_MODE_HH = 1, B200S_MODE_SGBM_3WAY = 2, B200S_MODE_HH4 = 3 };
+
+/* Arguments of cv2.StereoSGBM_create as issued at depthlib/stereo_core.py:63-75. */
+typedef struct B200sParams {
+    int32_t minDisparity;       /* sgbm_params['min_disp'] */
+    int32_t numDisparities;     /* sgbm_params['num_disp'] (any value >= 1, need not be %16) */
+    int32_t blockSize;          /* sgbm_params['block_size'], odd, 1..11 */
+    int32_t P1;                 /* 8 * block_size^2  (stereo_core.py:51) */
+    int32_t P2;                 /* 32 * block_size^2 (stereo_core.py:52) */
+    int32_t disp12MaxDiff;
+    int32_t preFilterCap;
+    int32_t uniquenessRatio;
+    int32_t speckleWindowSize;
+    int32_t speckleRange;
+    int32_t mode;               /* B200S_MODE_* */
+} B200sParams;
+
+/* Keyword arguments of postprocess_disparity as passed at depthlib/stereo_core.py:175-184
+ * (hole filling is not on the GPU path). */
+typedef struct B200sPostParams {
+    int32_t fastMode;             /* 1: only medianBlur(3) (stereo_core.py:171-173) */
+    int32_t maxSpeckleSize;       /* int(100 * downscale_factor) */
+    int32_t maxDiff16;            /* int(max_diff * 16) (postprocess.py:30) */
+    float   outlierThreshold;     /* 2.5 */
+    int32_t applyOutlierRemoval;  /* 1 */
+} B200sPostParams;
+
+/* Arguments of StereoCore.disparity_to_depth (depthlib/stereo_core.py:234-272). */
+typedef struct B200sDepthParams {
+    int32_t enabled;      /* 0: focal_length/baseline unset -> no depth (stereo_core.py:191) */
+    float   fB;           /* float32(f_pixels * baseline_m), product taken in double */
+    float   doffs;
+    float   eps;          /* StereoCore passes min_disp here (stereo_core.py:189,195) */
+    float   maxDepth;
+    int32_t hasMaxDepth;
+} B200sDepthParams;
+
+typedef struct B200sHandle B200sHandle;
+
+int b200s_abi_version(void);
+
+/* Lifetime. b200s_create replaces StereoCore._build_sgbm (depthlib/stereo_core.py:44-75): it
+ * validates the matcher parameters and binds the handle to `device`. */
+int b200s_create(int device, const B200sParams* p, B200sHandle** out);
+int b200s_configure(B200sHandle* h, const B200sParams* p);
+int b200s_destroy(B200sHandle* h);
+const char* b200s_last_error(const B200sHandle* h);
+/* Use an existing cudaStream_t (e.g. torch's current stream) instead of the handle's own. */
+int b200s_set_stream(B200sHandle* h, void* cuda_stream);
+int b200s_sync(B200sHandle* h);
+
+/* Rectification maps: the four CV_32FC1 maps RectificationCache.get_maps returns
+ * (depthlib/rectify.py:68-80). Uploaded once per calibration; host pointers, dense HxW. */
+int b200s_set_maps(B200sHandle* h, const float* map1_L, const float* map2_L,
+                   const float* map1_R, const float* map2_R, int H, int W);
+
+/* ---- host-buffer entry points (one pair) ------------------------------------------------ */
+
+/* cv2.cvtColor(img, COLOR_BGR2GRAY) at depthlib/rectify.py:116, stereo_core.py:157-159. */
+int b200s_bgr2gray(B200sHandle* h, const uint8_t* img, int H, int W, size_t stride, uint8_t* gray);
+
+/* 2x cv2.remap(gray, map1, map2, INTER_LINEAR) at depthlib/rectify.py:185-186. Source images
+ * are srcH x srcW; outputs have the size of the maps (dense). */
+int b200s_remap_u8(B200sHandle* h, const uint8_t* L, const uint8_t* R, int srcH, int srcW,
+                   size_t stride, uint8_t* outL, uint8_t* outR);
+
+/* self.sgbm.compute(L, R) at depthlib/stereo_core.py:231: int16 HxW, 16x fixed point. */
+int b200s_sgbm_compute(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H, int W,
+                       size_t stride, int16_t* disp16);
+
+/* postprocess_disparity(...) (depthlib/postprocess.py:120-171, hole filling off) or, with
+ * fastMode, cv2.medianBlur(d, 3) (stereo_core.py:173). In place on a dense float32 H x W. */
+int b200s_postprocess(B200sHandle* h, float* disp, int H, int W, const B200sPostParams* pp);
+
+/* StereoCore.disparity_to_depth (depthlib/stereo_core.py:234-272) on n dense float32 values. */
+int b200s_disp_to_depth(B200sHandle* h, const float* disp, size_t n, const B200sDepthParams* dp,
+                        float* depth);
+
+/* StereoCore.estimate_depth for an already-gray pair (depthlib/stereo_core.py:274-293):
+ * [remap if maps are set and use_maps] -> sgbm -> crop [:, numDisparities:] -> post -> depth.
+ * disp/depth are dense H x (W - numDisparities) float32; depth may be NULL when !dp->enabled.
+ * rectL/rectR (dense HxW u8) may be NULL. */
+int b200s_pipeline(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H, int W, size_t stride,
+                   int use_maps, const B200sPostParams* pp, const B200sDepthParams* dp,
+                   float* disp, float* depth, uint8_t* rectL, uint8_t* rectR);
+
+/* ---- device-resident batch entry points (frames dense, B x H x W) ------------------------- */
+
+int b200s_sgbm_compute_batch_dev(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
+                                 int H, int W, int16_t* dDisp16);
+int b200s_pipeline_batch_dev(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int H,
+                             int W, int use_maps, const B200sPostParams* pp,
+                             const B200sDepthParams* dp, float* dDisp, float* dDepth);
+
+/* ---- introspection used by tests / bench -------------------------------------------------- */
+
+/* Cost-domain geometry for width W: W1 = columns with a full disparity range, minX1 = first of
+ * them, Dp = padded disparity pitch of the internal volumes, INV = invalid marker. */
+int b200s_geometry(const B200sHandle* h, int W, int* W1, int* minX1, int* Dp, int* INV);
+/* Copy an internal stage of the LAST b200s_sgbm_compute* call (frame `b`) to the host:
+ * which = 0: block cost C (int16 [H][W1][D], includes +P2 like the reference's C),
+ *         1: aggregate S (int16 [H][W1][D]), 2: raw disparity before median/speckle (int16 HxW). */
+int b200s_debug_stage(B200sHandle* h, int which, int b, int16_t* out);
+/* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
+long long b200s_launch_count(const B200sHandle* h);
+/* Device time in ms of the last *_dev / host call, measured with CUDA events on the handle's
+ * stream (0 if timing is disabled). */
+int b200s_enable_timing(B200sHandle* h, int on);
+float b200s_last_ms(const B200sHandle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200STEREO_H */
