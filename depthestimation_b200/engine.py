@@ -1,0 +1,224 @@
+"""Python face of the C ABI: one ``StereoEngine`` = one ``B200sHandle`` (GPU + stream + scratch).
+
+Plays the role ``cv2.StereoSGBM`` / ``cv2.remap`` / ``cv2.filterSpeckles`` ... play for the
+reference's ``StereoCore`` (depthlib/stereo_core.py:44-75, 212-293): numpy in, numpy out, all
+arithmetic on the GPU. Device-resident batch calls take integer device pointers (e.g.
+``torch.Tensor.data_ptr()``) so that torch is only ever used for memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import B200sDepthParams, B200sParams, B200sPostParams, MODES
+
+__all__ = ["StereoEngine", "EngineError", "make_params", "make_post_params", "make_depth_params"]
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+def make_params(min_disp=0, num_disp=128, block_size=5, P1=None, P2=None, disp12_max_diff=1, prefilter_cap=31,
+                uniqueness_ratio=10, speckle_window_size=50, speckle_range=2, sgbm_mode="sgbm_3way") -> B200sParams:
+    """Same derivation as StereoCore._build_sgbm (depthlib/stereo_core.py:44-75): P1 = 8 bs^2,
+    P2 = 32 bs^2, unknown mode strings fall back to sgbm_3way."""
+    if P1 is None:
+        P1 = 8 * block_size ** 2
+    if P2 is None:
+        P2 = 32 * block_size ** 2
+    mode = MODES.get(sgbm_mode, 2) if isinstance(sgbm_mode, str) else int(sgbm_mode)
+    return B200sParams(int(min_disp), int(num_disp), int(block_size), int(P1), int(P2), int(disp12_max_diff),
+                       int(prefilter_cap), int(uniqueness_ratio), int(speckle_window_size), int(speckle_range), mode)
+
+
+def make_post_params(fast_mode=False, max_speckle_size=50, max_diff=1.0, outlier_threshold=3.0,
+                     apply_outlier_removal=True) -> B200sPostParams:
+    return B200sPostParams(int(bool(fast_mode)), int(max_speckle_size), int(max_diff * 16),
+                           float(outlier_threshold), int(bool(apply_outlier_removal)))
+
+
+def make_depth_params(f_pixels=None, baseline_m=None, doffs=0.0, eps=1e-6, max_depth=None) -> B200sDepthParams:
+    if f_pixels is None or baseline_m is None:
+        return B200sDepthParams(0, 0.0, 0.0, 0.0, 0.0, 0)
+    fB = np.float32(float(f_pixels) * float(baseline_m))
+    return B200sDepthParams(1, float(fB), float(np.float32(doffs)), float(np.float32(eps)),
+                            float(np.float32(max_depth if max_depth is not None else 0.0)), int(max_depth is not None))
+
+
+def _u8(a):
+    a = np.asarray(a)
+    if a.dtype != np.uint8:
+        raise TypeError(f"expected uint8 image, got {a.dtype}")
+    if a.ndim != 2:
+        raise ValueError(f"expected a single-channel HxW image, got shape {a.shape}")
+    if a.strides[1] != 1 or a.strides[0] < a.shape[1]:
+        a = np.ascontiguousarray(a)
+    return a
+
+
+def _pair(left, right):
+    left, right = _u8(left), _u8(right)
+    if left.shape != right.shape:
+        raise ValueError("left and right images must have the same size")
+    if left.strides != right.strides:
+        left, right = np.ascontiguousarray(left), np.ascontiguousarray(right)
+    return left, right
+
+
+class StereoEngine:
+    """Owns one B200sHandle on ``device``."""
+
+    def __init__(self, device: int = 0, **sgbm_kw):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        self.params = make_params(**sgbm_kw)
+        rc = self._lib.b200s_create(int(device), C.byref(self.params), C.byref(self._h))
+        if rc == _lib.E_INVALID:
+            raise ValueError("b200s_create: invalid matcher parameters "
+                             "(num_disp in [1,256], odd block_size <= 11, mode in sgbm/hh/sgbm_3way/hh4)")
+        if rc != 0:
+            raise EngineError("b200s_create failed: no usable CUDA device (the engine has no CPU fallback)")
+        self.device = int(device)
+        self.maps_shape = None
+
+    # -- lifetime ---------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.b200s_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc == 0:
+            return
+        msg = self._lib.b200s_last_error(self._h).decode("utf-8", "replace")
+        if rc == _lib.E_INVALID:
+            raise ValueError(f"{what}: {msg}")
+        raise EngineError(f"{what}: {msg} (code {rc})")
+
+    def configure(self, **sgbm_kw):
+        p = make_params(**sgbm_kw)
+        self._check(self._lib.b200s_configure(self._h, C.byref(p)), "b200s_configure")
+        self.params = p
+
+    def set_stream(self, cuda_stream):
+        self._check(self._lib.b200s_set_stream(self._h, C.c_void_p(cuda_stream or 0)), "b200s_set_stream")
+
+    def sync(self):
+        self._check(self._lib.b200s_sync(self._h), "b200s_sync")
+
+    def enable_timing(self, on=True):
+        self._lib.b200s_enable_timing(self._h, int(on))
+
+    @property
+    def last_ms(self) -> float:
+        return float(self._lib.b200s_last_ms(self._h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.b200s_launch_count(self._h))
+
+    def geometry(self, W: int):
+        w1, mx, dp, inv = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        self._lib.b200s_geometry(self._h, int(W), C.byref(w1), C.byref(mx), C.byref(dp), C.byref(inv))
+        return dict(W1=w1.value, minX1=mx.value, Dp=dp.value, INV=inv.value)
+
+    # -- host-buffer ops ----------------------------------------------------------------------
+    def set_maps(self, map1_L, map2_L, map1_R, map2_R):
+        ms = [np.ascontiguousarray(m, dtype=np.float32) for m in (map1_L, map2_L, map1_R, map2_R)]
+        H, W = ms[0].shape
+        if any(m.shape != (H, W) for m in ms):
+            raise ValueError("rectification maps must share one HxW shape")
+        self._check(self._lib.b200s_set_maps(self._h, *[m.ctypes.data for m in ms], H, W), "b200s_set_maps")
+        self.maps_shape = (H, W)
+
+    def bgr2gray(self, img):
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        if img.ndim != 3 or img.shape[2] != 3:
+            raise ValueError("bgr2gray expects HxWx3 uint8")
+        H, W, _ = img.shape
+        out = np.empty((H, W), np.uint8)
+        self._check(self._lib.b200s_bgr2gray(self._h, img.ctypes.data, H, W, img.strides[0], out.ctypes.data),
+                    "b200s_bgr2gray")
+        return out
+
+    def remap(self, left, right):
+        if self.maps_shape is None:
+            raise EngineError("remap: rectification maps not set")
+        left, right = _pair(left, right)
+        H, W = self.maps_shape
+        oL, oR = np.empty((H, W), np.uint8), np.empty((H, W), np.uint8)
+        self._check(self._lib.b200s_remap_u8(self._h, left.ctypes.data, right.ctypes.data, left.shape[0],
+                                             left.shape[1], left.strides[0], oL.ctypes.data, oR.ctypes.data),
+                    "b200s_remap_u8")
+        return oL, oR
+
+    def compute(self, left, right) -> np.ndarray:
+        """== cv2.StereoSGBM.compute(left, right): int16 HxW, 16x fixed point."""
+        left, right = _pair(left, right)
+        H, W = left.shape
+        out = np.empty((H, W), np.int16)
+        self._check(self._lib.b200s_sgbm_compute(self._h, left.ctypes.data, right.ctypes.data, H, W,
+                                                 left.strides[0], out.ctypes.data), "b200s_sgbm_compute")
+        return out
+
+    def postprocess(self, disp, pp: B200sPostParams) -> np.ndarray:
+        out = np.array(disp, dtype=np.float32, order="C", copy=True)
+        if out.ndim != 2:
+            raise ValueError("postprocess expects a 2-D disparity map")
+        if out.size:
+            self._check(self._lib.b200s_postprocess(self._h, out.ctypes.data, out.shape[0], out.shape[1],
+                                                    C.byref(pp)), "b200s_postprocess")
+        return out
+
+    def disp_to_depth(self, disp, dp: B200sDepthParams) -> np.ndarray:
+        a = np.ascontiguousarray(disp, dtype=np.float32)
+        out = np.empty_like(a)
+        if a.size:
+            self._check(self._lib.b200s_disp_to_depth(self._h, a.ctypes.data, a.size, C.byref(dp), out.ctypes.data),
+                        "b200s_disp_to_depth")
+        return out
+
+    def pipeline(self, left, right, pp: B200sPostParams, dp: B200sDepthParams, use_maps=False, want_rect=False):
+        """rectify(optional) -> match -> crop -> post -> depth for one gray pair, one C-ABI call."""
+        left, right = _pair(left, right)
+        H, W = left.shape
+        Wc = W - self.params.numDisparities
+        if Wc <= 0:
+            raise ValueError("num_disp must be smaller than the image width")
+        disp = np.empty((H, Wc), np.float32)
+        depth = np.empty((H, Wc), np.float32) if dp.enabled else None
+        rl = np.empty((H, W), np.uint8) if want_rect else None
+        rr = np.empty((H, W), np.uint8) if want_rect else None
+        self._check(self._lib.b200s_pipeline(
+            self._h, left.ctypes.data, right.ctypes.data, H, W, left.strides[0], int(bool(use_maps)), C.byref(pp),
+            C.byref(dp), disp.ctypes.data, depth.ctypes.data if depth is not None else None,
+            rl.ctypes.data if rl is not None else None, rr.ctypes.data if rr is not None else None), "b200s_pipeline")
+        return disp, depth, rl, rr
+
+    # -- device-resident batch ops (pointers are ints, e.g. torch.Tensor.data_ptr()) ---------------
+    def compute_batch_dev(self, dL: int, dR: int, B: int, H: int, W: int, dDisp16: int):
+        self._check(self._lib.b200s_sgbm_compute_batch_dev(self._h, dL, dR, B, H, W, dDisp16),
+                    "b200s_sgbm_compute_batch_dev")
+
+    def pipeline_batch_dev(self, dL: int, dR: int, B: int, H: int, W: int, pp, dp, dDisp: int, dDepth,
+                           use_maps=False):
+        self._check(self._lib.b200s_pipeline_batch_dev(self._h, dL, dR, B, H, W, int(bool(use_maps)), C.byref(pp),
+                                                       C.byref(dp), dDisp, dDepth), "b200s_pipeline_batch_dev")
+
+    # -- stage taps (tests) ----------------------------------------------------------------------------
+    def debug_stage(self, which: str, H: int, W: int, b: int = 0) -> np.ndarray:
+        g = self.geometry(W)
+        D = self.params.numDisparities
+        idx = {"C": 0, "S": 1, "raw": 2}[which]
+        out = np.empty((H, W), np.int16) if idx == 2 else np.empty((H, g["W1"], D), np.int16)
+        self._check(self._lib.b200s_debug_stage(self._h, idx, b, out.ctypes.data), "b200s_debug_stage")
+        return out

@@ -1,0 +1,115 @@
+"""GPU parity: the CUDA matcher (through the C ABI) against the C oracle and the golden vectors.
+Bit-exact is the bar for int16 disparity (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+import oracle
+from conftest import golden_cases
+from helpers import golden_sgbm_kwargs
+from depthestimation_b200.synth import make_pair, make_adversarial
+
+pytestmark = pytest.mark.gpu
+
+MODES = ["sgbm", "hh", "sgbm_3way", "hh4"]
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from depthestimation_b200.engine import StereoEngine
+    e = StereoEngine(0)
+    yield e
+    e.close()
+
+
+def _check(engine, L, R, stages=True, **kw):
+    engine.configure(**kw)
+    got = engine.compute(L, R)
+    ref = oracle.sgbm_compute(L, R, oracle.make_params(**kw), stages=stages)
+    H, W = L.shape
+    if stages and ref["C"] is not None:
+        C = engine.debug_stage("C", H, W)
+        assert np.array_equal(C, ref["C"]), f"C: {(C != ref['C']).sum()} cells differ {kw}"
+        S = engine.debug_stage("S", H, W)
+        assert np.array_equal(S, ref["S"]), f"S: {(S != ref['S']).sum()} cells differ {kw}"
+        raw = engine.debug_stage("raw", H, W)
+        assert np.array_equal(raw, ref["raw"]), f"raw: {(raw != ref['raw']).sum()} px differ {kw}"
+    d = ref["disp"] if stages else ref
+    assert np.array_equal(got, d), f"disp: {(got != d).sum()} px differ {kw}"
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_golden_disp16(engine, name, golden):
+    g = golden(name)
+    kw = golden_sgbm_kwargs(g)
+    engine.configure(**kw)
+    got = engine.compute(g["left_rect"], g["right_rect"])
+    assert np.array_equal(got, g["disp16"]), f"{(got != g['disp16']).sum()} px differ"
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("D,bs", [(64, 5), (48, 3), (32, 9), (16, 1), (40, 11), (44, 5), (62, 7), (128, 5), (140, 5)])
+def test_modes_blocks(engine, mode, D, bs):
+    L, R, _ = make_pair(64, D + 120, D, seed=1000 + D + bs)
+    _check(engine, L, R, min_disp=0, num_disp=D, block_size=bs, sgbm_mode=mode)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("mind", [-24, -8, 3, 8])
+def test_min_disp(engine, mode, mind):
+    L, R, _ = make_pair(56, 170, 32, seed=77)
+    _check(engine, L, R, min_disp=mind, num_disp=32, block_size=5, sgbm_mode=mode)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("uniq,d12,cap,sws", [(0, 1, 31, 0), (30, -1, 5, 50), (75, 3, 63, 20), (10, 0, 20, 100)])
+def test_filters(engine, mode, uniq, d12, cap, sws):
+    L, R, _ = make_pair(60, 160, 40, seed=5)
+    _check(engine, L, R, min_disp=0, num_disp=40, block_size=5, sgbm_mode=mode, uniqueness_ratio=uniq,
+           disp12_max_diff=d12, prefilter_cap=cap, speckle_window_size=sws, speckle_range=1)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("kind", ["noise", "zeros", "quantized", "periodic"])
+def test_adversarial_inputs(engine, mode, kind):
+    L, R = make_adversarial(kind, 48, 150)
+    _check(engine, L, R, min_disp=0, num_disp=32, block_size=5, sgbm_mode=mode)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_kitti_shape(engine, mode):
+    L, R, _ = make_pair(375, 1242, 128, seed=1000)
+    _check(engine, L, R, stages=False, min_disp=0, num_disp=128, block_size=5, sgbm_mode=mode)
+
+
+def test_ragged_and_tiny(engine):
+    # widths/heights that are not multiples of any tile size, image barely wider than D, 1-row image
+    for (H, W, D) in [(37, 131, 24), (5, 70, 64), (1, 90, 16), (9, 41, 40), (33, 300, 8)]:
+        L, R, _ = make_pair(H, W, D, seed=H * W)
+        for mode in MODES:
+            _check(engine, L, R, min_disp=0, num_disp=D, block_size=3, sgbm_mode=mode)
+
+
+def test_no_full_range_column(engine):
+    L, R, _ = make_pair(20, 50, 16, seed=3)
+    engine.configure(num_disp=64, sgbm_mode="sgbm")
+    got = engine.compute(L, R)
+    assert np.all(got == -16)
+
+
+def test_strided_input(engine):
+    L, R, _ = make_pair(40, 200, 32, seed=11)
+    big = np.zeros((40, 512), np.uint8)
+    big2 = np.zeros((40, 512), np.uint8)
+    big[:, 7:207] = L
+    big2[:, 7:207] = R
+    engine.configure(num_disp=32, sgbm_mode="sgbm")
+    assert np.array_equal(engine.compute(big[:, 7:207], big2[:, 7:207]), engine.compute(L, R))
+
+
+def test_invalid_params(engine):
+    with pytest.raises(ValueError):
+        engine.configure(num_disp=0)
+    with pytest.raises(ValueError):
+        engine.configure(block_size=4)
+    with pytest.raises(ValueError):
+        engine.configure(block_size=13)
