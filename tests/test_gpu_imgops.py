@@ -1,0 +1,156 @@
+"""GPU parity for the O(N) ops and the fused per-frame pipeline, against the C oracle and the golden
+vectors recorded from the reference's StereoCore. Bit-exact everywhere except depth, where the
+north_star tolerance is 1e-4 relative (and we in fact expect exact float32 equality)."""
+import numpy as np
+import pytest
+
+import oracle
+from conftest import golden_cases
+from helpers import golden_sgbm_kwargs, golden_max_depth
+from depthestimation_b200.synth import make_pair
+
+pytestmark = pytest.mark.gpu
+
+DEPTH_RTOL = 1e-4  # BASELINE.json north_star: float depth within 1e-4 relative
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from depthestimation_b200.engine import StereoEngine
+    e = StereoEngine(0)
+    yield e
+    e.close()
+
+
+def _depth_close(a, b):
+    assert np.array_equal(np.isinf(a), np.isinf(b))
+    fin = np.isfinite(b)
+    assert np.allclose(a[fin], b[fin], rtol=DEPTH_RTOL, atol=0)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_cases() if n.startswith("calib")])
+def test_remap_golden(engine, name, golden):
+    g = golden(name)
+    engine.set_maps(g["map1_L"], g["map2_L"], g["map1_R"], g["map2_R"])
+    l, r = engine.remap(g["left"], g["right"])
+    assert np.array_equal(l, g["left_rect"]) and np.array_equal(r, g["right_rect"])
+
+
+def test_remap_out_of_range_maps(engine):
+    rng = np.random.default_rng(1)
+    H, W = 50, 77
+    src = rng.integers(0, 256, (H, W), dtype=np.uint8)
+    m1 = rng.uniform(-5, W + 5, (H, W)).astype(np.float32)
+    m2 = rng.uniform(-5, H + 5, (H, W)).astype(np.float32)
+    m1[0, :10] = np.arange(10) + 0.5          # exact .5 fractions (round-half-even of x*32 is exact here)
+    m2[0, :10] = 0.015625
+    engine.set_maps(m1, m2, m1, m2)
+    l, r = engine.remap(src, src)
+    ref = oracle.remap_u8(src, m1, m2)
+    assert np.array_equal(l, ref) and np.array_equal(r, ref)
+
+
+def test_bgr2gray(engine):
+    rng = np.random.default_rng(2)
+    img = rng.integers(0, 256, (33, 71, 3), dtype=np.uint8)
+    assert np.array_equal(engine.bgr2gray(img), oracle.bgr2gray(img))
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_post_and_depth_golden(engine, name, golden):
+    from depthestimation_b200.engine import make_post_params, make_depth_params
+    g = golden(name)
+    kw = golden_sgbm_kwargs(g)
+    d = (g["disp16"].astype(np.float32) / 16.0)[:, kw["num_disp"]:]
+    pp = make_post_params(fast_mode=bool(int(g["fast"])), max_speckle_size=int(100 * float(g["downscale"])),
+                          max_diff=1.0, outlier_threshold=2.5)
+    post = engine.postprocess(d, pp)
+    assert np.array_equal(post, g["disp"]), f"{(post != g['disp']).sum()} px differ"
+    dp = make_depth_params(float(g["focal_length"]), float(g["baseline"]), float(g["doffs"]), eps=kw["min_disp"],
+                           max_depth=golden_max_depth(g))
+    _depth_close(engine.disp_to_depth(post, dp), g["depth"])
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_pipeline_golden(engine, name, golden):
+    """One C-ABI call == StereoCore.estimate_depth (rectify -> match -> crop -> post -> depth)."""
+    from depthestimation_b200.engine import make_post_params, make_depth_params
+    g = golden(name)
+    kw = golden_sgbm_kwargs(g)
+    engine.configure(**kw)
+    calibrated = "map1_L" in g
+    if calibrated:
+        engine.set_maps(g["map1_L"], g["map2_L"], g["map1_R"], g["map2_R"])
+    pp = make_post_params(fast_mode=bool(int(g["fast"])), max_speckle_size=int(100 * float(g["downscale"])),
+                          max_diff=1.0, outlier_threshold=2.5)
+    dp = make_depth_params(float(g["focal_length"]), float(g["baseline"]), float(g["doffs"]), eps=kw["min_disp"],
+                           max_depth=golden_max_depth(g))
+    disp, depth, rl, rr = engine.pipeline(g["left"], g["right"], pp, dp, use_maps=calibrated, want_rect=True)
+    assert np.array_equal(rl, g["left_rect"]) and np.array_equal(rr, g["right_rect"])
+    assert np.array_equal(disp, g["disp"]), f"{(disp != g['disp']).sum()} px differ"
+    _depth_close(depth, g["depth"])
+
+
+def test_post_random_floats_vs_oracle(engine):
+    """postprocess on arbitrary floats (what tests/test_postproc_logic.py of the reference feeds)."""
+    from depthestimation_b200.engine import make_post_params
+    rng = np.random.default_rng(5)
+    d = (rng.random((64, 90)) * 60).astype(np.float32)
+    d[rng.random(d.shape) < 0.1] = -1.0
+    for outl in (True, False):
+        pp = make_post_params(False, 40, 1.0, 2.5, outl)
+        got = engine.postprocess(d, pp)
+        ref = oracle.postprocess(d, 40, 1.0, 2.5, outl)
+        assert np.array_equal(got, ref)
+    assert np.array_equal(engine.postprocess(d, make_post_params(True)), oracle.median3_f32(d))
+
+
+def test_speckle_large_components(engine):
+    """Speckle CCL on a realistic disparity (big connected regions + small islands)."""
+    L, R, _ = make_pair(200, 400, 64, seed=21)
+    for sws, sr in [(200, 1), (50, 2), (1000, 4)]:
+        kw = dict(num_disp=64, sgbm_mode="sgbm", speckle_window_size=sws, speckle_range=sr)
+        engine.configure(**kw)
+        assert np.array_equal(engine.compute(L, R), oracle.sgbm_compute(L, R, oracle.make_params(**kw)))
+
+
+def test_depth_edge_cases(engine):
+    from depthestimation_b200.engine import make_depth_params
+    d = np.array([[100.0, 0.0, -1.0, 1e-7, 5.0, 0.03125]], np.float32)
+    for kw in (dict(doffs=0.0, eps=1e-6, max_depth=None), dict(doffs=2.5, eps=0, max_depth=80.0),
+               dict(doffs=-1.0, eps=3.0, max_depth=10.0)):
+        got = engine.disp_to_depth(d, make_depth_params(1000.0, 0.5, **kw))
+        ref = oracle.disp_to_depth(d, 1000.0, 0.5, **kw)
+        assert np.array_equal(got, ref)
+    # the reference's own unit test value (tests/test_math_core.py:5-27 of the reference)
+    z = engine.disp_to_depth(np.array([[100.0]], np.float32), make_depth_params(1000.0, 0.5))
+    assert z.shape == (1, 1) and abs(float(z[0, 0]) - 5.0) < 1e-6
+
+
+def test_batch_dev_matches_single(engine):
+    """Device-resident batch entry point: every frame equals the single-pair host call."""
+    import torch
+    from depthestimation_b200.engine import make_post_params, make_depth_params
+    B, H, W, D = 3, 60, 200, 32
+    pairs = [make_pair(H, W, D, seed=1000 + k)[:2] for k in range(B)]
+    kw = dict(num_disp=D, sgbm_mode="sgbm")
+    engine.configure(**kw)
+    dL = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    dR = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    out = torch.empty((B, H, W), dtype=torch.int16, device="cuda")
+    torch.cuda.synchronize()
+    engine.compute_batch_dev(dL.data_ptr(), dR.data_ptr(), B, H, W, out.data_ptr())
+    engine.sync()
+    got = out.cpu().numpy()
+    for k in range(B):
+        assert np.array_equal(got[k], oracle.sgbm_compute(pairs[k][0], pairs[k][1], oracle.make_params(**kw)))
+    pp = make_post_params(False, 100, 1.0, 2.5)
+    dp = make_depth_params(0.8 * W, 0.54, 0.0, eps=0, max_depth=None)
+    disp = torch.empty((B, H, W - D), dtype=torch.float32, device="cuda")
+    depth = torch.empty_like(disp)
+    engine.pipeline_batch_dev(dL.data_ptr(), dR.data_ptr(), B, H, W, pp, dp, disp.data_ptr(), depth.data_ptr())
+    engine.sync()
+    for k in range(B):
+        d1, z1, _, _ = engine.pipeline(pairs[k][0], pairs[k][1], pp, dp)
+        assert np.array_equal(disp[k].cpu().numpy(), d1)
+        assert np.array_equal(depth[k].cpu().numpy(), z1)
