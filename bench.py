@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""bench.py — throughput of depthlib's stereo hot path on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl b200|reference]
+
+Workload (BASELINE.json configs[1]): KITTI-shape synthetic stereo pairs 1242x375, 128 disparities,
+5-path `sgbm`, and per pair the whole StereoCore.estimate_depth path (depthlib/stereo_core.py:274-293):
+rectify (remap through cached maps) -> match -> crop -> postprocess -> depth.
+A "step" = one batch of B pairs through that path. `value` = pairs/s with inputs resident in HBM;
+`e2e` = the same through the host-buffer C-ABI call (pinned host in, pinned host out, copies timed).
+One process per GPU under torchrun; pairs shard frame-per-GPU, no collective on the data path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+H, W, D = 375, 1242, 128
+MODE = "sgbm"
+SGBM_KW = dict(min_disp=0, num_disp=D, block_size=5, disp12_max_diff=1, prefilter_cap=31, uniqueness_ratio=10,
+               speckle_window_size=50, speckle_range=2, sgbm_mode=MODE)
+WORKLOAD = f"kitti_{W}x{H}_D{D}_{MODE}_5path_rectify+match+post+depth"
+METRIC = "stereo_pairs_per_second"
+UNIT = "frames/s"
+N_DISTINCT = 4  # distinct synthetic pairs, tiled to the batch
+
+
+def mde(fps: float) -> float:
+    return fps * H * W * D / 1e6
+
+
+def make_inputs(batch: int):
+    from depthestimation_b200.synth import make_pair
+    pairs = [make_pair(H, W, D, seed=1000 + k)[:2] for k in range(min(N_DISTINCT, batch))]
+    L = np.stack([pairs[i % len(pairs)][0] for i in range(batch)])
+    R = np.stack([pairs[i % len(pairs)][1] for i in range(batch)])
+    return L, R
+
+
+def make_maps():
+    """Rectification maps for the synthetic calibration: cv2 (as rectify.py:63-73) when importable,
+    else a numpy radial-distortion model of the same magnitude (map generation is host-side, once)."""
+    from depthestimation_b200.synth import make_calibration
+    cal = make_calibration(H, W)
+    try:
+        from oracle import cv2_reference as cr
+        if cr.HAVE_CV2:
+            return cr.build_maps(cal, alpha=1.0), cal
+    except Exception:
+        pass
+    ys, xs = np.mgrid[0:H, 0:W].astype(np.float32)
+    f, cx, cy = 0.8 * W, W / 2, H / 2
+    xn, yn = (xs - cx) / f, (ys - cy) / f
+    r2 = xn * xn + yn * yn
+    out = {}
+    for side, k1 in (("L", -0.05), ("R", -0.04)):
+        s = 1 + k1 * r2 + 0.01 * r2 * r2
+        out[f"map1_{side}"] = (xn * s * f + cx).astype(np.float32)
+        out[f"map2_{side}"] = (yn * s * f + cy).astype(np.float32)
+    return out, cal
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (profiling guide recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            p = [x.strip() for x in r.split(",")]
+            if len(p) < 8:
+                continue
+            try:
+                sm.append(float(p[1])); mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the reference's own per-frame path (cv2 driven exactly as depthlib does), frame-parallel
+# over all host cores; falls back to the C oracle port only when cv2 is not importable.
+# ---------------------------------------------------------------------------------------------
+class CpuReference:
+    def __init__(self, maps, cal):
+        from oracle import cv2_reference as cr
+        self.cores = os.cpu_count() or 1
+        self.have_cv2 = cr.HAVE_CV2
+        self.maps, self.cal = maps, cal
+        if self.have_cv2:
+            import cv2
+            cv2.setNumThreads(1)  # sgbm is single-threaded inside OpenCV; parallelism is across frames
+            self.kind = "reference"
+            self.desc = f"cv2 {cr.CV2_VERSION} driven as depthlib/stereo_core.py:125-293 does"
+            self.pipes = []
+            for _ in range(self.cores):
+                p = cr.Cv2StereoPipeline(SGBM_KW, calib=None, downscale=1.0, fast_mode=False,
+                                         focal_length=cal["focal_length"], baseline=cal["baseline"])
+                p.maps = maps
+                self.pipes.append(p)
+        else:
+            import oracle
+            self.kind = "port"
+            self.desc = "C oracle port (cv2 not importable)"
+            self.oracle = oracle
+            self.params = oracle.make_params(**SGBM_KW)
+
+    def _one(self, wid, L, R):
+        if self.have_cv2:
+            return self.pipes[wid](L, R)
+        o = self.oracle
+        l = o.remap_u8(L, self.maps["map1_L"], self.maps["map2_L"])
+        r = o.remap_u8(R, self.maps["map1_R"], self.maps["map2_R"])
+        d = (o.sgbm_compute(l, r, self.params).astype(np.float32) / 16.0)[:, D:]
+        d = o.postprocess(d, 100, 1.0, 2.5)
+        return d, o.disp_to_depth(d, self.cal["focal_length"], self.cal["baseline"], 0.0, eps=0)
+
+    def run_frames(self, L, R, nframes: int) -> float:
+        """Process nframes (cycled from the batch) on all cores; returns seconds."""
+        from concurrent.futures import ThreadPoolExecutor
+        idx = list(range(nframes))
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(self.cores) as ex:
+            def work(w):
+                for i in idx[w::self.cores]:
+                    self._one(w, L[i % len(L)], R[i % len(R)])
+            list(ex.map(work, range(self.cores)))
+        return time.perf_counter() - t0
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    L, R = make_inputs(N_DISTINCT)
+    maps, cal = make_maps()
+    ref = CpuReference(maps, cal)
+    per_step = ref.cores  # one frame per host thread and step: a bounded sample of the workload
+    for _ in range(min(args.warmup, 1)):
+        ref.run_frames(L, R, per_step)
+    t = 0.0
+    for _ in range(args.steps):
+        t += ref.run_frames(L, R, per_step)
+    fps = args.steps * per_step / t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int16/u8 (+f32 post)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_step": per_step, "distinct_pairs": N_DISTINCT},
+        "mde_per_s": mde(fps),
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
+                         "sample": f"{args.steps} steps x {per_step} frames, frame-parallel, {ref.desc}"},
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def algorithmic_bytes(eng, batch):
+    """int16 C and S volumes, V = H*W1*D cells per frame.
+    paths kernel (one direction per launch, generic line-scan): read C 2V + S read-modify-write 4V
+    (the first direction only writes S: 4V) -> (4V + 4*6V)/5 per launch on the 5-path sgbm.
+    whole matcher, canonical dataflow: 10 B/cell."""
+    g = eng.geometry(W)
+    V = H * g["W1"] * D
+    per_launch = (4 * V + 4 * 6 * V) / 5.0 * batch
+    matcher = 10.0 * V * batch
+    return V, per_launch, matcher
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from depthestimation_b200.engine import StereoEngine, make_post_params, make_depth_params
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    B = args.batch
+    L, R = make_inputs(B)
+    maps, cal = make_maps()
+    eng = StereoEngine(local, **SGBM_KW)
+    eng.set_maps(maps["map1_L"], maps["map2_L"], maps["map1_R"], maps["map2_R"])
+    pp = make_post_params(False, 100, 1.0, 2.5, True)            # stereo_core.py:175-184 at downscale 1.0
+    dp = make_depth_params(cal["focal_length"], cal["baseline"], 0.0, eps=0, max_depth=None)
+    stream = torch.cuda.current_stream()
+    eng.set_stream(stream.cuda_stream)
+
+    Wc = W - D
+    dL, dR = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+    disp = torch.empty((B, H, Wc), dtype=torch.float32, device="cuda")
+    depth = torch.empty_like(disp)
+
+    def step_dev():
+        eng.pipeline_batch_dev(dL.data_ptr(), dR.data_ptr(), B, H, W, pp, dp, disp.data_ptr(), depth.data_ptr(),
+                               use_maps=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_dev()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = eng.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_dev()
+    e1.record(stream)
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    launches = eng.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    fps = world * B * args.steps / (total_ms / 1e3)
+
+    # ---- per-stage device times (CUDA events on the launching stream), same workload ----------
+    eng.enable_timing(True)
+    eng.stage_times(reset=True)
+    nst = max(1, min(args.steps, 5))
+    for _ in range(nst):
+        step_dev()
+    stages = eng.stage_times(reset=True)
+    eng.enable_timing(False)
+    V, bytes_per_launch, matcher_bytes = algorithmic_bytes(eng, B)
+    peaks = {}
+    try:
+        peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    p_ms, p_n = stages["paths"]
+    path_launch_ms = p_ms / max(p_n, 1)
+    achieved = bytes_per_launch / (path_launch_ms * 1e-3) / 1e9 if path_launch_ms > 0 else 0.0
+    matcher_ms = sum(stages[k][0] for k in ("prefilter", "cost", "paths", "wta", "median", "speckle")) / nst
+    step_ms_sum = sum(v[0] for v in stages.values()) / nst
+
+    # ---- end to end through the host-buffer C-ABI call (pinned host in / out) --------------------
+    hL, hR = torch.from_numpy(L).pin_memory(), torch.from_numpy(R).pin_memory()
+    hDisp = torch.empty((B, H, Wc), dtype=torch.float32).pin_memory()
+    hDepth = torch.empty((B, H, Wc), dtype=torch.float32).pin_memory()
+    nL, nR, nDisp, nDepth = hL.numpy(), hR.numpy(), hDisp.numpy(), hDepth.numpy()
+
+    def step_e2e():
+        eng.pipeline_batch(nL, nR, pp, dp, use_maps=True, out_disp=nDisp, out_depth=nDepth)
+
+    for _ in range(min(args.warmup, 3)):
+        step_e2e()
+    barrier()
+    ke = max(1, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(ke):
+        step_e2e()
+        _ = float(nDepth[0, 0, 0])  # device->host result is consumed
+    torch.cuda.synchronize()
+    te = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_fps = world * B * ke / float(te.item())
+    same = bool(np.array_equal(nDisp, disp.cpu().numpy()))
+
+    # ---- CPU baseline beside it (rank 0, N=1 only): bounded sample of the same workload ----------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        try:
+            ref = CpuReference(maps, cal)
+            ref.run_frames(L, R, ref.cores)               # warm-up
+            n = 2 * ref.cores
+            t = ref.run_frames(L, R, n)
+            while t < 8.0 and n < 64 * ref.cores:          # grow the sample to roughly 10-20 s of work
+                n *= 2
+                t = ref.run_frames(L, R, n)
+            cpu = {"value": n / t, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
+                   "sample": f"{n} frames of the same workload, frame-parallel on {ref.cores} threads, {ref.desc}"}
+        except Exception as exc:  # the baseline is a report, not a dependency of the GPU number
+            cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u16x2 packed int (matcher), f32 (post/depth)",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "pairs_per_step_per_gpu": B, "distinct_pairs": min(N_DISTINCT, B),
+                       "cells_per_frame": V, "parallelism": f"frame-sharded x{world}, no collective",
+                       "l2": "inputs larger than L2: C+S volumes are %.1f GB per step (L2 = 126 MB)" %
+                             (2 * 2 * V * B / 1e9)},
+            "mde_per_s": mde(fps),
+            "e2e": {"value": e2e_fps, "unit": UNIT, "h2d_bytes_per_step": int(2 * B * H * W),
+                    "d2h_bytes_per_step": int(2 * B * H * Wc * 4), "mde_per_s": mde(e2e_fps),
+                    "api": "b200s_pipeline_batch (pinned host buffers)", "matches_device_path": same},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "k_path<16> (one direction per launch)", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": None,
+                         "peak_source": peak_src, "launch_ms": path_launch_ms,
+                         "algorithmic_bytes_per_launch": bytes_per_launch},
+            "roofline_matcher": {"bytes_per_cell": 10, "achieved": matcher_bytes / (matcher_ms * 1e-3) / 1e9,
+                                 "frac": matcher_bytes / (matcher_ms * 1e-3) / 1e9 / peak, "ms_per_step": matcher_ms,
+                                 "nominal_8TBs_frac": matcher_bytes / (matcher_ms * 1e-3) / 1e9 / 8000.0},
+            "stage_ms_per_step": {k: v[0] / nst for k, v in stages.items()},
+            "stage_ms_sum": step_ms_sum,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    eng.close()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=32, help="stereo pairs per step and GPU")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

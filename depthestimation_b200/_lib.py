@@ -13,6 +13,7 @@ CSRC = _PKG / "csrc"
 MODES = {"sgbm": 0, "hh": 1, "sgbm_3way": 2, "hh4": 3}
 
 OK, E_INVALID, E_CUDA, E_STATE = 0, -1, -2, -3
+STAGES = ("remap", "prefilter", "cost", "paths", "wta", "median", "speckle", "post", "depth")
 
 
 class B200sParams(C.Structure):
@@ -54,6 +55,9 @@ SYMBOLS = {
                                  _VP, _VP, _VP, _VP]),
     "b200s_sgbm_compute_batch_dev": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int, _VP]),
     "b200s_pipeline_batch_dev": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _PP, _DP, _VP, _VP]),
+    "b200s_pipeline_batch": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _PP, _DP, _VP, _VP]),
+    "b200s_stage_times": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.c_int]),
+    "b200s_reset_stage_times": (C.c_int, [_H]),
     "b200s_geometry": (C.c_int, [_H, C.c_int, _IP, _IP, _IP, _IP]),
     "b200s_debug_stage": (C.c_int, [_H, C.c_int, C.c_int, _VP]),
     "b200s_launch_count": (C.c_longlong, [_H]),

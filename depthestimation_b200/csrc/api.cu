@@ -34,6 +34,15 @@ struct B200sHandle {
     bool timing = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
+    // per-stage device timing (only when timing is on): marks are events recorded at stage ends
+    enum { NSTAGE = B200S_NUM_STAGES, MAXMARK = 32 };
+    cudaEvent_t mark_ev[MAXMARK] = {};
+    int mark_stage[MAXMARK] = {};
+    int mark_launches[MAXMARK] = {};
+    int nmark = 0;
+    long long mark_launch_base = 0;
+    double stage_ms[NSTAGE] = {};
+    long long stage_launches[NSTAGE] = {};
     // maps
     int mapH = 0, mapW = 0;
     DevBuf maps;  // 4 x H x W float
@@ -190,6 +199,17 @@ int b200s_set_maps(B200sHandle* h, const float* m1L, const float* m2L, const flo
 
 // ---- internal stage graph (device pointers) -----------------------------------------------------------
 
+// end-of-stage mark: device time since the previous mark is attributed to `stage`
+static void mark(B200sHandle* h, int stage) {
+    if (!h->timing || h->nmark >= B200sHandle::MAXMARK) return;
+    int i = h->nmark++;
+    if (!h->mark_ev[i]) cudaEventCreate(&h->mark_ev[i]);
+    cudaEventRecord(h->mark_ev[i], h->stream);
+    h->mark_stage[i] = stage;
+    h->mark_launches[i] = (int)(h->launches - h->mark_launch_base);
+    h->mark_launch_base = h->launches;
+}
+
 static int check_launch(B200sHandle* h, const char* what) {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { h->set_error(B200S_E_CUDA, "%s: %s", what, cudaGetErrorString(e)); return B200S_E_CUDA; }
@@ -203,6 +223,7 @@ static int dev_remap(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B
     launch_remap(dL, B, sH, sW, m, m + n, h->mapH, h->mapW, oL, h->stream);
     launch_remap(dR, B, sH, sW, m + 2 * n, m + 3 * n, h->mapH, h->mapW, oR, h->stream);
     h->launches += 2;
+    mark(h, B200S_STAGE_REMAP);
     return check_launch(h, "remap");
 }
 
@@ -236,20 +257,26 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
     CUDA_TRY(h, h->raw.ensure(npx * 2));
     launch_prefilter(e, dL, dR, B, h->recL.as<uint2>(), h->recR.as<uint2>(), h->stream);
     h->launches++;
+    mark(h, B200S_STAGE_PREFILTER);
     int rc = launch_cost(e, sp, h->recL.as<uint2>(), h->recR.as<uint2>(), B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->stream);
     if (rc) { h->set_error(B200S_E_INVALID, "cost kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
     h->launches++;
+    mark(h, B200S_STAGE_COST);
     rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches);
     if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
+    mark(h, B200S_STAGE_PATHS);
     launch_wta(e, B, h->S.as<uint16_t>(), h->raw.as<int16_t>(), h->stream);
     h->launches++;
+    mark(h, B200S_STAGE_WTA);
     launch_median3_s16(h->raw.as<int16_t>(), dDisp, B, H, W, h->stream);
     h->launches++;
+    mark(h, B200S_STAGE_MEDIAN);
     if (e.speckleWindowSize > 0) {
         CUDA_TRY(h, h->labels.ensure(npx * sizeof(int)));
         CUDA_TRY(h, h->sizes.ensure(npx * sizeof(int)));
         launch_speckle(dDisp, B, H, W, e.INV, e.speckleWindowSize, 16 * e.speckleRange, h->labels.as<int>(), h->sizes.as<int>(),
                        h->stream, &h->launches);
+        mark(h, B200S_STAGE_SPECKLE);
     }
     return check_launch(h, "sgbm");
 }
@@ -316,21 +343,37 @@ static int dev_pipeline(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, in
     h->launches++;
     rc = dev_post(h, h->f0.as<float>(), B, H, Wc, pp, dDisp);
     if (rc) return rc;
+    mark(h, B200S_STAGE_POST);
     if (dp.enabled && dDepth) {
         launch_depth(dDisp, nc, dp, dDepth, h->stream);
         h->launches++;
+        mark(h, B200S_STAGE_DEPTH);
     }
     return check_launch(h, "pipeline");
 }
 
 struct Timed {
     B200sHandle* h;
-    explicit Timed(B200sHandle* h_) : h(h_) { if (h->timing) cudaEventRecord(h->ev0, h->stream); }
+    explicit Timed(B200sHandle* h_) : h(h_) {
+        if (h->timing) {
+            h->nmark = 0;
+            h->mark_launch_base = h->launches;
+            cudaEventRecord(h->ev0, h->stream);
+        }
+    }
     void stop() {
         if (h->timing) {
             cudaEventRecord(h->ev1, h->stream);
             cudaEventSynchronize(h->ev1);
             cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+            cudaEvent_t prev = h->ev0;
+            for (int i = 0; i < h->nmark; i++) {
+                float ms = 0.f;
+                cudaEventElapsedTime(&ms, prev, h->mark_ev[i]);
+                h->stage_ms[h->mark_stage[i]] += ms;
+                h->stage_launches[h->mark_stage[i]] += h->mark_launches[i];
+                prev = h->mark_ev[i];
+            }
         }
     }
 };
@@ -491,6 +534,46 @@ int b200s_debug_stage(B200sHandle* h, int which, int b, int16_t* out) {
     CUDA_TRY(h, cudaMemcpyAsync(out, h->hostio.p, cells * 2, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     return check_launch(h, "debug_stage");
+}
+
+int b200s_stage_times(const B200sHandle* h, double* ms, long long* launches, int n) {
+    if (!h) return B200S_E_INVALID;
+    for (int i = 0; i < n && i < B200S_NUM_STAGES; i++) {
+        if (ms) ms[i] = h->stage_ms[i];
+        if (launches) launches[i] = h->stage_launches[i];
+    }
+    return B200S_NUM_STAGES;
+}
+
+int b200s_reset_stage_times(B200sHandle* h) {
+    if (!h) return B200S_E_INVALID;
+    for (int i = 0; i < B200S_NUM_STAGES; i++) { h->stage_ms[i] = 0.0; h->stage_launches[i] = 0; }
+    return B200S_OK;
+}
+
+int b200s_pipeline_batch(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W, int use_maps,
+                         const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth) {
+    if (!h) return B200S_E_INVALID;
+    if (!L || !R || !pp || !dp || !disp || B <= 0 || H <= 0 || W <= 0) { h->set_error(B200S_E_INVALID, "pipeline_batch: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const int Wc = W - h->params.numDisparities;
+    if (Wc <= 0) { h->set_error(B200S_E_INVALID, "pipeline_batch: numDisparities >= image width"); return B200S_E_INVALID; }
+    const size_t npx = (size_t)B * H * W, nc = (size_t)B * H * Wc;
+    CUDA_TRY(h, h->imgL.ensure(npx));
+    CUDA_TRY(h, h->imgR.ensure(npx));
+    CUDA_TRY(h, h->hostio.ensure(2 * nc * sizeof(float)));
+    CUDA_TRY(h, cudaMemcpyAsync(h->imgL.p, L, npx, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(h->imgR.p, R, npx, cudaMemcpyHostToDevice, h->stream));
+    float* dDisp = h->hostio.as<float>();
+    float* dDepth = dDisp + nc;
+    Timed t(h);
+    int rc = dev_pipeline(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), B, H, W, use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
+    if (rc) return rc;
+    t.stop();
+    CUDA_TRY(h, cudaMemcpyAsync(disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (dp->enabled && depth) CUDA_TRY(h, cudaMemcpyAsync(depth, dDepth, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "pipeline_batch");
 }
 
 }  // extern "C"

@@ -214,6 +214,33 @@ class StereoEngine:
         self._check(self._lib.b200s_pipeline_batch_dev(self._h, dL, dR, B, H, W, int(bool(use_maps)), C.byref(pp),
                                                        C.byref(dp), dDisp, dDepth), "b200s_pipeline_batch_dev")
 
+    def pipeline_batch(self, lefts, rights, pp, dp, use_maps=False, out_disp=None, out_depth=None):
+        """Host batch: lefts/rights uint8 [B,H,W] C-contiguous (pinned for best speed) -> float32 [B,H,W-D]."""
+        lefts, rights = np.asarray(lefts), np.asarray(rights)
+        if lefts.dtype != np.uint8 or rights.dtype != np.uint8 or lefts.ndim != 3 or lefts.shape != rights.shape:
+            raise ValueError("pipeline_batch expects two uint8 [B,H,W] arrays of equal shape")
+        lefts, rights = np.ascontiguousarray(lefts), np.ascontiguousarray(rights)
+        B, H, W = lefts.shape
+        Wc = W - self.params.numDisparities
+        if Wc <= 0:
+            raise ValueError("num_disp must be smaller than the image width")
+        disp = out_disp if out_disp is not None else np.empty((B, H, Wc), np.float32)
+        depth = (out_depth if out_depth is not None else np.empty((B, H, Wc), np.float32)) if dp.enabled else None
+        self._check(self._lib.b200s_pipeline_batch(
+            self._h, lefts.ctypes.data, rights.ctypes.data, B, H, W, int(bool(use_maps)), C.byref(pp), C.byref(dp),
+            disp.ctypes.data, depth.ctypes.data if depth is not None else None), "b200s_pipeline_batch")
+        return disp, depth
+
+    def stage_times(self, reset=False):
+        """{stage: (device ms, kernel launches)} accumulated while timing is enabled."""
+        n = len(_lib.STAGES)
+        ms = (C.c_double * n)()
+        ln = (C.c_longlong * n)()
+        self._lib.b200s_stage_times(self._h, ms, ln, n)
+        if reset:
+            self._lib.b200s_reset_stage_times(self._h)
+        return {name: (ms[i], int(ln[i])) for i, name in enumerate(_lib.STAGES)}
+
     # -- stage taps (tests) ----------------------------------------------------------------------------
     def debug_stage(self, which: str, H: int, W: int, b: int = 0) -> np.ndarray:
         g = self.geometry(W)

@@ -36,6 +36,11 @@ enum {
     B200S_E_STATE = -3      /* call order problem, e.g. remap before set_maps */
 };
 
+enum {
+    B200S_STAGE_REMAP = 0, B200S_STAGE_PREFILTER, B200S_STAGE_COST, B200S_STAGE_PATHS, B200S_STAGE_WTA,
+    B200S_STAGE_MEDIAN, B200S_STAGE_SPECKLE, B200S_STAGE_POST, B200S_STAGE_DEPTH, B200S_NUM_STAGES
+};
+
 /* cv2.STEREO_SGBM_MODE_* values, as mapped at depthlib/stereo_core.py:55-61 */
 enum { B200S_MODE_SGBM = 0, B200S_MODE_HH = 1, B200S_MODE_SGBM_3WAY = 2, B200S_MODE_HH4 = 3 };
 
@@ -131,6 +136,12 @@ int b200s_pipeline_batch_dev(B200sHandle* h, const uint8_t* dL, const uint8_t* d
                              int W, int use_maps, const B200sPostParams* pp,
                              const B200sDepthParams* dp, float* dDisp, float* dDepth);
 
+/* Host-buffer batch: B dense frames in, B dense results out, one H2D + one D2H per buffer.
+ * What a video/batch driver (depthlib/StereoDepthEstimatorVideo.py:84-148) calls per chunk. */
+int b200s_pipeline_batch(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W,
+                         int use_maps, const B200sPostParams* pp, const B200sDepthParams* dp,
+                         float* disp, float* depth);
+
 /* ---- introspection used by tests / bench -------------------------------------------------- */
 
 /* Cost-domain geometry for width W: W1 = columns with a full disparity range, minX1 = first of
@@ -146,6 +157,10 @@ long long b200s_launch_count(const B200sHandle* h);
  * stream (0 if timing is disabled). */
 int b200s_enable_timing(B200sHandle* h, int on);
 float b200s_last_ms(const B200sHandle* h);
+/* Accumulated device ms and kernel launches per stage (B200S_STAGE_* order) while timing is on.
+ * Returns B200S_NUM_STAGES. */
+int b200s_stage_times(const B200sHandle* h, double* ms, long long* launches, int n);
+int b200s_reset_stage_times(B200sHandle* h);
 
 #ifdef __cplusplus
 }
