@@ -231,7 +231,10 @@ def run_b200(args):
     eng.set_maps(maps["map1_L"], maps["map2_L"], maps["map1_R"], maps["map2_R"])
     pp = make_post_params(False, 100, 1.0, 2.5, True)            # stereo_core.py:175-184 at downscale 1.0
     dp = make_depth_params(cal["focal_length"], cal["baseline"], 0.0, eps=0, max_depth=None)
-    stream = torch.cuda.current_stream()
+    # the engine launches on a dedicated torch stream, so torch.cuda.Event on it times our kernels
+    # (NULL / the legacy default stream would make the handle fall back to its own private stream)
+    stream = torch.cuda.Stream()
+    assert stream.cuda_stream != 0
     eng.set_stream(stream.cuda_stream)
 
     Wc = W - D
@@ -261,6 +264,7 @@ def run_b200(args):
         step_dev()
     e1.record(stream)
     barrier()
+    stream.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
     launches = eng.launch_count - l0
     clocks = sampler.stop() if rank == 0 else None

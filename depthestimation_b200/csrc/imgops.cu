@@ -92,75 +92,6 @@ void launch_median3_f32(const float* src, float* dst, int B, int H, int W, cudaS
     k_median3<float><<<grid, 256, 0, st>>>(src, dst, H, W);
 }
 
-// ---- B.3 speckle filter: union-find connected components with a neighbour-difference predicate ------
-__device__ __forceinline__ int uf_find(const int* lab, int i) {
-    int p = ((volatile const int*)lab)[i];
-    while (p != i) { i = p; p = ((volatile const int*)lab)[i]; }
-    return i;
-}
-__device__ __forceinline__ void uf_union(int* lab, int a, int b) {
-    while (true) {
-        a = uf_find(lab, a);
-        b = uf_find(lab, b);
-        if (a == b) return;
-        if (a < b) { int t = a; a = b; b = t; }   // hook the larger root under the smaller
-        int old = atomicMin(&lab[a], b);
-        if (old == a) return;
-        a = old;
-    }
-}
-__global__ void __launch_bounds__(256) k_ccl_init(const int16_t* __restrict__ img, size_t n, int newVal, int* lab, int* sizes) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    lab[i] = (img[i] != newVal) ? (int)i : -1;
-    sizes[i] = 0;
-}
-__global__ void __launch_bounds__(256) k_ccl_merge(const int16_t* __restrict__ img, int B, int H, int W, int newVal,
-                                                   int maxDiff, int* lab) {
-    size_t n = (size_t)B * H * W;
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int v = img[i];
-    if (v == newVal) return;
-    int x = (int)(i % W), y = (int)((i / W) % H);
-    if (x + 1 < W) {
-        int q = img[i + 1];
-        if (q != newVal && abs(q - v) <= maxDiff) uf_union(lab, (int)i, (int)i + 1);
-    }
-    if (y + 1 < H) {
-        int q = img[i + W];
-        if (q != newVal && abs(q - v) <= maxDiff) uf_union(lab, (int)i, (int)i + W);
-    }
-}
-__global__ void __launch_bounds__(256) k_ccl_count(size_t n, int* lab, int* sizes) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int root = -1;
-    if (i < n && lab[i] >= 0) {
-        root = uf_find(lab, (int)i);
-        lab[i] = root;  // roots never change in this kernel, so compressing is race-free
-    }
-    // warp-aggregated count: one atomic per distinct root per warp
-    unsigned peers = __match_any_sync(0xffffffffu, root);
-    if (root >= 0 && (threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&sizes[root], __popc(peers));
-}
-__global__ void __launch_bounds__(256) k_ccl_apply(int16_t* img, size_t n, int newVal, int maxSize, const int* __restrict__ lab,
-                                                   const int* __restrict__ sizes) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int r = lab[i];
-    if (r >= 0 && sizes[r] <= maxSize) img[i] = (int16_t)newVal;
-}
-void launch_speckle(int16_t* img, int B, int H, int W, int newVal, int maxSize, int maxDiff, int* labels, int* sizes,
-                    cudaStream_t st, long long* launches) {
-    size_t n = (size_t)B * H * W;
-    unsigned blocks = (unsigned)((n + 255) / 256);
-    k_ccl_init<<<blocks, 256, 0, st>>>(img, n, newVal, labels, sizes);
-    k_ccl_merge<<<blocks, 256, 0, st>>>(img, B, H, W, newVal, maxDiff, labels);
-    k_ccl_count<<<blocks, 256, 0, st>>>(n, labels, sizes);
-    k_ccl_apply<<<blocks, 256, 0, st>>>(img, n, newVal, maxSize, labels, sizes);
-    if (launches) *launches += 4;
-}
-
 // ---- conversions ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_d16_to_f32_crop(const int16_t* __restrict__ d16, int H, int W, int x0, float* __restrict__ out) {
     int Wc = W - x0;

@@ -1,0 +1,177 @@
+// speckle.cu — cv2.filterSpeckles: 4-connected components over pixels != newVal,
+// neighbours joined iff |p - q| <= maxDiff; components with size <= maxSize are set to newVal.
+// Used twice per frame: inside StereoSGBM.compute (A.8, depthlib/stereo_core.py:231) and in
+// postprocess.filter_speckles (depthlib/postprocess.py:6-35).
+//
+// Tiled union-find: (A) each CTA labels a 64x16 tile entirely in shared memory (horizontal runs by
+// pointer jumping, vertical links by shared-memory atomicMin, redundant links skipped), and writes
+// per pixel the global index of its tile-local root plus, at roots, the local component size;
+// (B) only tile-border pixels link across tiles in global memory; (C) tile-local roots add their
+// size to the global root; (D) every pixel looks its root's size up. The result does not depend on
+// traversal order, so it is bit-identical to the sequential flood fill.
+#include "common.cuh"
+
+#define TW 64
+#define TH 16
+
+__device__ __forceinline__ int uf_find(const int* lab, int i) {
+    int p = ((volatile const int*)lab)[i];
+    while (p != i) { i = p; p = ((volatile const int*)lab)[i]; }
+    return i;
+}
+__device__ __forceinline__ void uf_union(int* lab, int a, int b) {
+    while (true) {
+        a = uf_find(lab, a);
+        b = uf_find(lab, b);
+        if (a == b) return;
+        if (a < b) { int t = a; a = b; b = t; }   // hook the larger root under the smaller
+        int old = atomicMin(&lab[a], b);
+        if (old == a) return;
+        a = old;
+    }
+}
+__device__ __forceinline__ bool joined(int p, int q, int newVal, int maxDiff) {
+    return p != newVal && q != newVal && abs(p - q) <= maxDiff;
+}
+
+__global__ void __launch_bounds__(256) k_ccl_tile(const int16_t* __restrict__ img, int H, int W, int newVal, int maxDiff,
+                                                  int* __restrict__ lab, int* __restrict__ sizes) {
+    __shared__ short val[TH][TW + 1];
+    __shared__ int par[TH * TW];
+    __shared__ int cnt[TH * TW];
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+    const size_t frame = (size_t)blockIdx.z * H * W;
+    const int16_t* src = img + frame;
+    for (int p = threadIdx.x; p < TH * TW; p += 256) {
+        int lx = p % TW, ly = p / TW, x = x0 + lx, y = y0 + ly;
+        val[ly][lx] = (x < W && y < H) ? src[(size_t)y * W + x] : (short)newVal;
+        cnt[p] = 0;
+    }
+    __syncthreads();
+    // horizontal runs: parent = left neighbour if joined
+    for (int p = threadIdx.x; p < TH * TW; p += 256) {
+        int lx = p % TW, ly = p / TW;
+        par[p] = (lx > 0 && joined(val[ly][lx], val[ly][lx - 1], newVal, maxDiff)) ? p - 1 : p;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < 6; it++) {  // pointer jumping: 2^6 = TW
+        int np[TH * TW / 256];
+#pragma unroll
+        for (int k = 0; k < TH * TW / 256; k++) { int p = threadIdx.x + 256 * k; np[k] = par[par[p]]; }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < TH * TW / 256; k++) par[threadIdx.x + 256 * k] = np[k];
+        __syncthreads();
+    }
+    // vertical links; skipped when the left neighbour pair already carries the same link
+    for (int p = threadIdx.x; p < TH * TW; p += 256) {
+        int lx = p % TW, ly = p / TW;
+        if (ly == 0) continue;
+        int v = val[ly][lx], u = val[ly - 1][lx];
+        if (!joined(v, u, newVal, maxDiff)) continue;
+        if (lx > 0) {
+            int vl = val[ly][lx - 1], ul = val[ly - 1][lx - 1];
+            if (joined(v, vl, newVal, maxDiff) && joined(u, ul, newVal, maxDiff) && joined(vl, ul, newVal, maxDiff)) continue;
+        }
+        uf_union(par, p, p - TW);
+    }
+    __syncthreads();
+    int root[TH * TW / 256];
+#pragma unroll
+    for (int k = 0; k < TH * TW / 256; k++) {
+        int p = threadIdx.x + 256 * k;
+        int lx = p % TW, ly = p / TW;
+        root[k] = (val[ly][lx] != newVal) ? uf_find(par, p) : -1;
+    }
+    // local component sizes, warp-aggregated
+#pragma unroll
+    for (int k = 0; k < TH * TW / 256; k++) {
+        unsigned peers = __match_any_sync(0xffffffffu, root[k]);
+        if (root[k] >= 0 && (threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&cnt[root[k]], __popc(peers));
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < TH * TW / 256; k++) {
+        int p = threadIdx.x + 256 * k;
+        int lx = p % TW, ly = p / TW, x = x0 + lx, y = y0 + ly;
+        if (x < W && y < H) {
+            size_t gi = frame + (size_t)y * W + x;
+            int r = root[k];
+            lab[gi] = (r >= 0) ? (int)(frame + (size_t)(y0 + r / TW) * W + (x0 + r % TW)) : -1;
+            sizes[gi] = (r == p) ? cnt[p] : 0;
+        }
+    }
+}
+
+// links across tile borders: item < nh: horizontal border rows (y = TH*k), else vertical border columns (x = TW*k)
+__global__ void __launch_bounds__(256) k_ccl_border(const int16_t* __restrict__ img, int H, int W, int newVal, int maxDiff,
+                                                    int* lab) {
+    const int nby = (H - 1) / TH, nbx = (W - 1) / TW;  // number of interior borders
+    const int nh = nby * W, nv = nbx * H;
+    int item = blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= nh + nv) return;
+    const size_t frame = (size_t)blockIdx.z * H * W;
+    const int16_t* s = img + frame;
+    if (item < nh) {
+        int y = (item / W + 1) * TH, x = item % W;
+        int v = s[(size_t)y * W + x], u = s[(size_t)(y - 1) * W + x];
+        if (!joined(v, u, newVal, maxDiff)) return;
+        if (x % TW != 0) {
+            int vl = s[(size_t)y * W + x - 1], ul = s[(size_t)(y - 1) * W + x - 1];
+            if (joined(v, vl, newVal, maxDiff) && joined(u, ul, newVal, maxDiff) && joined(vl, ul, newVal, maxDiff)) return;
+        }
+        uf_union(lab, (int)(frame + (size_t)y * W + x), (int)(frame + (size_t)(y - 1) * W + x));
+    } else {
+        item -= nh;
+        int x = (item / H + 1) * TW, y = item % H;
+        int v = s[(size_t)y * W + x], l = s[(size_t)y * W + x - 1];
+        if (!joined(v, l, newVal, maxDiff)) return;
+        if (y % TH != 0) {
+            int vu = s[(size_t)(y - 1) * W + x], lu = s[(size_t)(y - 1) * W + x - 1];
+            if (joined(v, vu, newVal, maxDiff) && joined(l, lu, newVal, maxDiff) && joined(vu, lu, newVal, maxDiff)) return;
+        }
+        uf_union(lab, (int)(frame + (size_t)y * W + x), (int)(frame + (size_t)y * W + x - 1));
+    }
+}
+
+// tile-local roots hand their size to the global root
+__global__ void __launch_bounds__(256) k_ccl_count(size_t n, int* lab, int* sizes) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int c = sizes[i];
+    if (c == 0) return;               // not a tile-local root
+    int r = uf_find(lab, (int)i);
+    if (r != (int)i) {
+        atomicAdd(&sizes[r], c);
+        lab[i] = r;                   // roots do not change in this kernel
+    }
+}
+
+__global__ void __launch_bounds__(256) k_ccl_apply(int16_t* img, size_t n, int newVal, int maxSize, const int* lab,
+                                                   const int* __restrict__ sizes) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int l = lab[i];
+    if (l < 0) return;
+    int r = uf_find(lab, l);
+    if (sizes[r] <= maxSize) img[i] = (int16_t)newVal;
+}
+
+void launch_speckle(int16_t* img, int B, int H, int W, int newVal, int maxSize, int maxDiff, int* labels, int* sizes,
+                    cudaStream_t st, long long* launches) {
+    size_t n = (size_t)B * H * W;
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    dim3 tg((W + TW - 1) / TW, (H + TH - 1) / TH, B);
+    k_ccl_tile<<<tg, 256, 0, st>>>(img, H, W, newVal, maxDiff, labels, sizes);
+    int items = ((H - 1) / TH) * W + ((W - 1) / TW) * H;
+    int nl = 3;
+    if (items > 0) {
+        dim3 bg((items + 255) / 256, 1, B);
+        k_ccl_border<<<bg, 256, 0, st>>>(img, H, W, newVal, maxDiff, labels);
+        nl++;
+    }
+    k_ccl_count<<<blocks, 256, 0, st>>>(n, labels, sizes);
+    k_ccl_apply<<<blocks, 256, 0, st>>>(img, n, newVal, maxSize, labels, sizes);
+    if (launches) *launches += nl;
+}
