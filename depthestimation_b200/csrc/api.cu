@@ -47,7 +47,8 @@ struct B200sHandle {
     int mapH = 0, mapW = 0;
     DevBuf maps;  // 4 x H x W float
     // scratch
-    DevBuf imgL, imgR, rectL, rectR, recL, recR, C, S, Calt, raw, med, labels, sizes, f0, f1, s16c, hostio;
+    DevBuf imgL, imgR, rectL, rectR, recL, recR, C, S, Calt, raw, med, labels, sizes, f0, f1, s16c, hostio, ck, keys;
+    bool debug_flow = false;  // materialise the full S volume with the generic per-direction kernels (stage taps)
     // geometry of the last sgbm call (for debug taps)
     Eff last_eff;
     int last_B = 0;
@@ -62,7 +63,7 @@ struct B200sHandle {
     }
     void release_all() {
         DevBuf* all[] = {&maps, &imgL, &imgR, &rectL, &rectR, &recL, &recR, &C, &S, &Calt, &raw, &med,
-                         &labels, &sizes, &f0, &f1, &s16c, &hostio};
+                         &labels, &sizes, &f0, &f1, &s16c, &hostio, &ck, &keys};
         for (DevBuf* b : all) b->release();
     }
 };
@@ -167,6 +168,7 @@ int b200s_sync(B200sHandle* h) {
     return B200S_OK;
 }
 
+int b200s_set_debug_flow(B200sHandle* h, int on) { if (!h) return B200S_E_INVALID; h->debug_flow = on != 0; return B200S_OK; }
 int b200s_enable_timing(B200sHandle* h, int on) { if (!h) return B200S_E_INVALID; h->timing = on != 0; return B200S_OK; }
 float b200s_last_ms(const B200sHandle* h) { return h ? h->last_ms : 0.f; }
 long long b200s_launch_count(const B200sHandle* h) { return h ? h->launches : 0; }
@@ -262,11 +264,23 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
     if (rc) { h->set_error(B200S_E_INVALID, "cost kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
     h->launches++;
     mark(h, B200S_STAGE_COST);
-    rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches);
-    if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
-    mark(h, B200S_STAGE_PATHS);
-    launch_wta(e, B, h->S.as<uint16_t>(), h->raw.as<int16_t>(), h->stream);
-    h->launches++;
+    if (h->debug_flow) {
+        rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches, 0);
+        if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
+        mark(h, B200S_STAGE_PATHS);
+        launch_wta(e, B, h->S.as<uint16_t>(), h->raw.as<int16_t>(), h->stream);
+        h->launches++;
+    } else {
+        rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches, 1);
+        if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
+        mark(h, B200S_STAGE_PATHS);
+        CUDA_TRY(h, h->ck.ensure(rows_ck_bytes(e, B)));
+        CUDA_TRY(h, h->keys.ensure(npx * sizeof(unsigned)));
+        rc = launch_rows(e, B, h->C.as<uint16_t>(), h->S.as<uint16_t>(), h->ck.as<uint16_t>(), h->keys.as<unsigned>(),
+                         h->raw.as<int16_t>(), h->stream);
+        if (rc) { h->set_error(B200S_E_INVALID, "row kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
+        h->launches++;
+    }
     mark(h, B200S_STAGE_WTA);
     launch_median3_s16(h->raw.as<int16_t>(), dDisp, B, H, W, h->stream);
     h->launches++;

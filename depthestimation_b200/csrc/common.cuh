@@ -91,7 +91,11 @@ int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uin
                 uint16_t* Calt, cudaStream_t st);
 // all path directions of the mode, accumulated into S
 int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, const uint16_t* Calt, uint16_t* S,
-                 cudaStream_t st, long long* launches);
+                 cudaStream_t st, long long* launches, int vertical_only);
+// fused horizontal paths + winner selection (rows.cu): C', Sv -> raw disparity
+size_t rows_ck_bytes(const Eff& e, int B);
+int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,
+                cudaStream_t st);
 void launch_wta(const Eff& e, int B, const uint16_t* S, int16_t* raw, cudaStream_t st);
 void launch_median3_s16(const int16_t* src, int16_t* dst, int B, int H, int W, cudaStream_t st);
 // speckle filter (B.3) in place; labels/sizes are int32 scratch of B*H*W each

@@ -164,7 +164,7 @@ static void launch_one(const PathArgs& a, int B, cudaStream_t st) {
 }
 
 int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, const uint16_t* Calt, uint16_t* S,
-                 cudaStream_t st, long long* launches) {
+                 cudaStream_t st, long long* launches, int vertical_only) {
     if (e.Dp > 256) return -2;
     PathArgs a;
     a.C = C; a.Calt = nullptr; a.S = S;
@@ -185,9 +185,12 @@ int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, c
         case B200S_MODE_HH4: add(-1, 0); add(1, 0); add(0, -1); add(0, 1); break;
         default: add(-1, 0); add(1, 0); add(0, -1); break;  // sgbm_3way
     }
+    bool first = true;
     for (int k = 0; k < nd; k++) {
         a.px = dirs[k][0]; a.py = dirs[k][1];
-        a.first = (k == 0);
+        if (vertical_only && a.py == 0) continue;  // the two horizontal paths live in rows.cu
+        a.first = first;
+        first = false;
         a.quirk = 0;
         a.sp = whole;
         a.Calt = nullptr;

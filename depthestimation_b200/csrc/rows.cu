@@ -1,0 +1,339 @@
+// rows.cu — fused horizontal aggregation + winner selection, one scan line (image row) per lane group.
+//
+// Replaces, for every mode, the two horizontal paths (x-1,y) / (x+1,y) of A.5 and the per-row
+// selection of A.6 inside cv2.StereoSGBM.compute (depthlib/stereo_core.py:231). Inputs: block cost
+// C' and the vertical-family aggregate Sv; output: the raw int16 disparity row (before the 3x3
+// median). The final S = Sv + L(->) + L(<-) never goes to HBM.
+//
+// A row's two scans run in opposite directions, so L(<-) of a column is needed long after it was
+// produced. Instead of spilling a 2V scratch volume the kernel checkpoints:
+//   pass 1: scan <- over the whole row, keep only L(<-) at every K-th column (checkpoint, 2*Dp bytes);
+//   pass 2: for each K-column chunk, left to right: re-run <- inside the chunk from its checkpoint
+//           into shared memory, then scan -> over the chunk, add Sv + L(->) + L(<-) and select.
+// HBM traffic: C twice (the third read of a chunk hits L1/L2) + Sv once = 6 B/cell instead of the
+// 14 B/cell of two read-modify-write passes plus a selection pass.
+#include "sgm_step.cuh"
+
+#define ROW_K 8  // columns per chunk
+
+struct RowArgs {
+    const uint16_t* C;
+    const uint16_t* Sv;
+    uint16_t* ck;      // checkpoints [B*H][nck][Dp]
+    unsigned* keys;    // right-view candidates [B*H][W]
+    int16_t* raw;      // [B*H][W]
+    int H, W, W1, D, Dp, P1, P2, minD, minX1, maxX1, INV, ue, d12e, mode, nck, nlines;
+};
+
+template <int NR>
+__device__ __forceinline__ void load_regs(const uint16_t* p, unsigned (&r)[NR]) {
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++) {
+        uint4 t = *(const uint4*)(p + 8 * q);
+        r[4 * q] = t.x; r[4 * q + 1] = t.y; r[4 * q + 2] = t.z; r[4 * q + 3] = t.w;
+    }
+}
+template <int NR>
+__device__ __forceinline__ void load_regs_nc(const uint16_t* p, unsigned (&r)[NR]) {
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++) {
+        uint4 t = __ldg((const uint4*)(p + 8 * q));
+        r[4 * q] = t.x; r[4 * q + 1] = t.y; r[4 * q + 2] = t.z; r[4 * q + 3] = t.w;
+    }
+}
+template <int NR>
+__device__ __forceinline__ void store_regs(uint16_t* p, const unsigned (&r)[NR]) {
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++) *(uint4*)(p + 8 * q) = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+}
+
+// ---- A.6 steps 1-4 for one pixel whose S(., d) sits in v[] across the lane group ------------------
+template <int LW, int NR>
+__device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigned (&pm)[NR], const RowArgs& a,
+                                          const unsigned gmask, const int gl, const int gbase, const int xc,
+                                          unsigned* keys, int16_t* out) {
+    constexpr int DPL = 2 * NR;
+    unsigned w[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) w[j] = umax2(v[j], pm[j]);
+    const int d0 = 8 * (a.D / 8);
+    const bool simd3 = (a.mode == B200S_MODE_SGBM_3WAY) && d0 > 0;
+    const unsigned gbits = (LW == 32) ? 0xffffffffu : ((1u << LW) - 1u);
+    int minS, best;
+    if (!simd3) {
+        const unsigned ml = local_min2<NR>(w);
+        const int lm = (int)min(ml & 0xffffu, ml >> 16);
+        const unsigned mg = group_min2<LW>(ml, gmask);
+        minS = (int)min(mg & 0xffffu, mg >> 16);
+        int cand = 0;
+        if (lm == minS) {
+#pragma unroll
+            for (int j = NR - 1; j >= 0; j--) {
+                if ((int)(w[j] >> 16) == minS) cand = 2 * j + 1;
+                if ((int)(w[j] & 0xffffu) == minS) cand = 2 * j;
+            }
+        }
+        const unsigned bits = (__ballot_sync(gmask, lm == minS) >> gbase) & gbits;
+        const int fl = __ffs(bits) - 1;                       // lowest lane reaching the minimum
+        best = fl * DPL + __shfl_sync(gmask, cand, fl, LW);   // lowest d reaching the minimum
+    } else {
+        // sgbm_3way: minimum over d < d0 taken 8 SIMD lanes wide (lane = d % 8); inside a SIMD lane the
+        // LAST d reaching the lane minimum is kept, across SIMD lanes the lowest such d; the scalar
+        // tail d >= d0 only wins when strictly smaller.
+        unsigned lm4[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            unsigned t = 0x7fff7fffu;
+#pragma unroll
+            for (int h = 0; h < NR / 4; h++) {
+                const int dreg = gl * DPL + 8 * h;            // first d of this 8-block
+                t = umin2(t, (dreg + 8 <= d0) ? v[4 * h + j] : 0x7fff7fffu);
+            }
+            lm4[j] = group_min2<LW>(t, gmask);
+        }
+        minS = 32767;
+#pragma unroll
+        for (int j = 0; j < 4; j++) minS = min(minS, (int)min(lm4[j] & 0xffffu, lm4[j] >> 16));
+        best = 0x7fffffff;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int lmin = (k & 1) ? (int)(lm4[k >> 1] >> 16) : (int)(lm4[k >> 1] & 0xffffu);
+            int dk = -1;
+#pragma unroll
+            for (int h = NR / 4 - 1; h >= 0; h--) {           // upper 8-block first: larger d
+                const int dreg = gl * DPL + 8 * h;
+                const unsigned r = v[4 * h + (k >> 1)];
+                const int val = (k & 1) ? (int)(r >> 16) : (int)(r & 0xffffu);
+                const unsigned bits = (__ballot_sync(gmask, (dreg + 8 <= d0) && val == lmin) >> gbase) & gbits;
+                if (bits) dk = max(dk, (31 - __clz(bits)) * DPL + 8 * h + k);
+            }
+            if (lmin == minS && dk >= 0) best = min(best, dk);
+        }
+        if (a.D > d0) {  // scalar tail, evaluated by the lane that holds it, then broadcast
+            const int ql = d0 / DPL, e0 = d0 % DPL;
+            int ms = minS, bs_ = best;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (e0 + k < DPL && d0 + k < a.D) {
+                    const int val = elem_of<NR>(v, e0 + k);
+                    if (val < ms) { ms = val; bs_ = d0 + k; }
+                }
+            }
+            minS = __shfl_sync(gmask, ms, ql, LW);
+            best = __shfl_sync(gmask, bs_, ql, LW);
+        }
+    }
+
+    // ---- uniqueness: smallest S outside [best-1, best+1] ------------------------------------------
+    unsigned e[NR];
+    const int rel = best - gl * DPL;  // position of the winner relative to this lane's first d
+#pragma unroll
+    for (int j = 0; j < NR; j++) {
+        unsigned x = w[j];
+        if (rel >= 2 * j - 1 && rel <= 2 * j + 1) x |= 0x0000ffffu;       // d = 2j     excluded
+        if (rel >= 2 * j && rel <= 2 * j + 2) x |= 0xffff0000u;           // d = 2j + 1 excluded
+        e[j] = x;
+    }
+    bool reject;
+    const int nexcl = 1 + (best > 0) + (best < a.D - 1);
+    if (a.mode != B200S_MODE_SGBM_3WAY) {
+        const unsigned mg = group_min2<LW>(local_min2<NR>(e), gmask);
+        const int min2 = (int)min(mg & 0xffffu, mg >> 16);
+        reject = (a.D > nexcl) && (min2 * (100 - a.ue) < minS * 100);
+    } else {
+        reject = false;
+        if (a.ue > 0) {
+            // SIMD part d < d0: S[d] < (int16)(thr + 1); scalar tail d >= d0: S[d]*(100-ue) < minS*100
+            unsigned la = 0xffffffffu, lb = 0xffffffffu;
+#pragma unroll
+            for (int j = 0; j < NR; j++) {
+                const int d = gl * DPL + 2 * j;  // d0 is even, so a register is entirely on one side
+                if (d < d0) la = umin2(la, e[j]); else lb = umin2(lb, e[j]);
+            }
+            unsigned key = min(la & 0xffffu, la >> 16) | (min(lb & 0xffffu, lb >> 16) << 16);
+            key = group_min2<LW>(key, gmask);
+            const int m2a = (int)(key & 0xffffu), m2b = (int)(key >> 16);
+            const int thr = (100 * minS) / (100 - a.ue);
+            const int t16 = (int)(short)(thr + 1);
+            if (m2a != 0xffff && m2a < t16) reject = true;
+            if (m2b != 0xffff && m2b < 0x7fff + 1 && (m2b * (100 - a.ue) < minS * 100)) {
+                // padded disparities (forced to 0x7fff) are not candidates: make sure a real tail element exists
+                const int lo = max(d0, 0), hi = a.D - 1;
+                int ntail = hi - lo + 1;
+                for (int d = best - 1; d <= best + 1; d++) ntail -= (d >= lo && d <= hi);
+                if (ntail > 0) reject = true;
+            }
+        }
+    }
+    // ---- neighbours of the winner for the parabola fit -------------------------------------------
+    const int dm = max(best - 1, 0), dq = min(best + 1, a.Dp - 1);
+    const int Sm = __shfl_sync(gmask, elem_of<NR>(v, dm % DPL), dm / DPL, LW);
+    const int Sq = __shfl_sync(gmask, elem_of<NR>(v, dq % DPL), dq / DPL, LW);
+    if (reject || gl != 0) return;
+    const int x2 = xc + a.minX1 - best - a.minD;
+    if (minS < 32767) {
+        const unsigned nk = ((unsigned)minS << 16) | (0xffffu - (unsigned)best);
+        if (nk < keys[x2]) keys[x2] = nk;   // this row's keys are private to this lane: plain update
+    }
+    int d16 = best * 16;
+    if (best > 0 && best < a.D - 1) {
+        const int den2 = max(Sm + Sq - 2 * minS, 1);
+        d16 += ((Sm - Sq) * 16 + den2) / (2 * den2);  // C truncating division
+    }
+    out[xc + a.minX1] = (int16_t)(d16 + a.minD * 16);
+}
+
+template <int LW, int NR>
+__global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
+    constexpr int DPL = 2 * NR;
+    constexpr int LINES = 128 / LW;                 // lines per CTA
+    extern __shared__ __align__(16) uint4 rsm[];    // [LINES][ROW_K][NR/4][LW] uint4: L(<-) of the current chunk
+    const int gl = threadIdx.x % LW;
+    const int lic = threadIdx.x / LW;               // line in CTA
+    const int line = blockIdx.x * LINES + lic;
+    if (line >= a.nlines) return;
+    const unsigned gmask = group_mask<LW>();
+    const int gbase = (threadIdx.x & 31) / LW * LW;
+    const bool active = gl * DPL < a.Dp;
+    uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;
+
+    unsigned pm[NR];
+    make_padmask<NR>(pm, gl, a.D);
+    const unsigned P1P1 = pk2((unsigned)a.P1), P2mP1 = (unsigned)(a.P2 - a.P1);
+    const int d0 = 8 * (a.D / 8);
+    const bool tail3 = (a.mode == B200S_MODE_SGBM_3WAY) && (a.D % 8 != 0) && d0 > 0;
+    const int quirkL = tail3 ? 2 : 0;               // the (x+1, y) path ignores the d-1 neighbour at d0 (A.7)
+
+    const uint16_t* Crow = a.C + (size_t)line * a.W1 * a.Dp + gl * DPL;
+    const uint16_t* Srow = a.Sv + (size_t)line * a.W1 * a.Dp + gl * DPL;
+    uint16_t* ck = a.ck + (size_t)line * a.nck * a.Dp + gl * DPL;
+    unsigned* keys = a.keys + (size_t)line * a.W;
+    int16_t* out = a.raw + (size_t)line * a.W;
+
+    for (int x = gl; x < a.W; x += LW) { keys[x] = 0xffffffffu; out[x] = (int16_t)a.INV; }
+    __syncwarp(gmask);
+
+    unsigned L[NR], Cq[NR];
+    unsigned m;
+    // ---- pass 1: <- over the row, checkpoint L at every K-th column ------------------------------
+    const int nchunks = (a.W1 + ROW_K - 1) / ROW_K;
+    sgm_reset<NR>(L, m);
+    for (int x = a.W1 - 1; x >= ROW_K; x--) {
+#pragma unroll
+        for (int j = 0; j < NR; j++) Cq[j] = 0u;
+        if (active) load_regs_nc<NR>(Crow + (size_t)x * a.Dp, Cq);
+        sgm_step<LW, NR>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
+        if ((x % ROW_K) == 0 && active) store_regs<NR>(ck + (size_t)(x / ROW_K) * a.Dp, L);
+    }
+    __syncwarp(gmask);
+    // ---- pass 2: chunk by chunk, left to right ------------------------------------------------------
+    unsigned Lr[NR];   // L(->)
+    unsigned mr;
+    sgm_reset<NR>(Lr, mr);
+    for (int c = 0; c < nchunks; c++) {
+        const int xs = c * ROW_K, xe = min(xs + ROW_K, a.W1);
+        // re-run <- inside the chunk from the checkpoint at xe (or from the border)
+        if (xe < a.W1) {
+#pragma unroll
+            for (int j = 0; j < NR; j++) L[j] = 0x7fff7fffu;
+            if (active) load_regs<NR>(ck + (size_t)(c + 1) * a.Dp, L);
+            const unsigned mn = group_min2<LW>(local_min2<NR>(L), gmask);
+            m = min(mn & 0xffffu, mn >> 16);
+        } else {
+            sgm_reset<NR>(L, m);
+        }
+        for (int x = xe - 1; x >= xs; x--) {
+#pragma unroll
+            for (int j = 0; j < NR; j++) Cq[j] = 0u;
+            if (active) load_regs_nc<NR>(Crow + (size_t)x * a.Dp, Cq);
+            sgm_step<LW, NR>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
+#pragma unroll
+            for (int q = 0; q < NR / 4; q++)
+                Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+        }
+        __syncwarp(gmask);
+        // -> over the chunk, S = Sv + L(->) + L(<-), winner selection
+        for (int x = xs; x < xe; x++) {
+            unsigned Sq[NR];
+#pragma unroll
+            for (int j = 0; j < NR; j++) { Cq[j] = 0u; Sq[j] = 0u; }
+            if (active) {
+                load_regs_nc<NR>(Crow + (size_t)x * a.Dp, Cq);
+                load_regs_nc<NR>(Srow + (size_t)x * a.Dp, Sq);
+            }
+            sgm_step<LW, NR>(Lr, mr, Cq, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+#pragma unroll
+            for (int q = 0; q < NR / 4; q++) {
+                const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
+                Sq[4 * q] = uaddmin2(uaddmin2(Sq[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
+                Sq[4 * q + 1] = uaddmin2(uaddmin2(Sq[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);
+                Sq[4 * q + 2] = uaddmin2(uaddmin2(Sq[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
+                Sq[4 * q + 3] = uaddmin2(uaddmin2(Sq[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
+            }
+            wta_pixel<LW, NR>(Sq, pm, a, gmask, gl, gbase, x, keys, out);
+        }
+        __syncwarp(gmask);
+    }
+    // ---- A.6 step 5: left-right check on the finished row ---------------------------------------------
+    __syncwarp(gmask);
+    for (int x = a.minX1 + gl; x < a.maxX1; x += LW) {
+        int d1 = out[x];
+        if (d1 == a.INV) continue;
+        const int _d = d1 >> 4, d_ = (d1 + 15) >> 4;
+        const int _x = x - _d, x_ = x - d_;
+        bool c1 = false, c2 = false;
+        if (_x >= 0 && _x < a.W) {
+            unsigned k = keys[_x];
+            int v2 = (k == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (k & 0xffffu)) + a.minD);
+            c1 = v2 >= a.minD && abs(v2 - _d) > a.d12e;
+        }
+        if (x_ >= 0 && x_ < a.W) {
+            unsigned k = keys[x_];
+            int v2 = (k == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (k & 0xffffu)) + a.minD);
+            c2 = v2 >= a.minD && abs(v2 - d_) > a.d12e;
+        }
+        if (c1 && c2) out[x] = (int16_t)a.INV;
+    }
+}
+
+template <int LW, int NR>
+static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
+    constexpr int LINES = 128 / LW;
+    size_t smem = (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4);
+    cudaFuncSetAttribute(k_rows<LW, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_rows<LW, NR><<<(a.nlines + LINES - 1) / LINES, 128, smem, st>>>(a);
+}
+
+size_t rows_ck_bytes(const Eff& e, int B) {
+    int nck = (e.W1 + ROW_K - 1) / ROW_K + 1;
+    return (size_t)B * e.H * nck * e.Dp * sizeof(uint16_t);
+}
+
+int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,
+                cudaStream_t st) {
+    RowArgs a;
+    a.C = C; a.Sv = Sv; a.ck = ck; a.keys = keys; a.raw = raw;
+    a.H = e.H; a.W = e.W; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e; a.minD = e.minD;
+    a.minX1 = e.minX1; a.maxX1 = e.maxX1; a.INV = e.INV; a.ue = e.ue; a.d12e = e.d12e; a.mode = e.mode;
+    a.nck = (e.W1 + ROW_K - 1) / ROW_K + 1;
+    a.nlines = B * e.H;
+    if (e.Dp > 512) return -2;
+    if (e.Dp > 64) {             // 16 disparities per lane
+        int LW = 2;
+        while (LW * 16 < e.Dp) LW *= 2;
+        switch (LW) {
+            case 2: case 4: case 8: launch_rows_t<8, 8>(a, st); break;
+            case 16: launch_rows_t<16, 8>(a, st); break;
+            default: launch_rows_t<32, 8>(a, st); break;
+        }
+    } else {                     // 8 disparities per lane
+        int LW = 2;
+        while (LW * 8 < e.Dp) LW *= 2;
+        switch (LW) {
+            case 2: launch_rows_t<2, 4>(a, st); break;
+            case 4: launch_rows_t<4, 4>(a, st); break;
+            default: launch_rows_t<8, 4>(a, st); break;
+        }
+    }
+    return 0;
+}

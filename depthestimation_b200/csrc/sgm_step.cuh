@@ -1,0 +1,104 @@
+// sgm_step.cuh — one step of the SGM path recursion (A.4) for a group of LW lanes holding
+// 2*NR disparities per lane (NR packed u16x2 registers, d contiguous within the lane).
+//
+//   L(p,d) = C'(p,d) + min(L(q,d), L(q,d-1)+P1, L(q,d+1)+P1, m+P2) - m,   m = min_d L(q,d)
+//
+// with C' the block cost without the reference's +P2 (same L values as A.4). Per register:
+//   2 PRMT (d-1 / d+1 neighbours) + VIMNMX3.U16x2 + VIADDMNMX.U16x2 + 2 integer add/sub + VIMNMX.U16x2
+// Values stay in [0, 32767] (pads are forced to 0x7fff), so no u16 half ever carries or borrows.
+#pragma once
+#include "common.cuh"
+
+template <int LW>
+__device__ __forceinline__ unsigned group_mask() {
+    if (LW == 32) return 0xffffffffu;
+    return ((1u << LW) - 1u) << ((threadIdx.x & 31) / LW * LW);
+}
+
+template <int LW>
+__device__ __forceinline__ unsigned group_min2(unsigned v, unsigned gmask) {
+#pragma unroll
+    for (int o = LW / 2; o > 0; o >>= 1) v = umin2(v, __shfl_xor_sync(gmask, v, o, LW));
+    return v;
+}
+
+template <int NR>
+__device__ __forceinline__ unsigned local_min2(const unsigned (&v)[NR]) {
+    unsigned m = v[0];
+#pragma unroll
+    for (int j = 1; j + 1 < NR; j += 2) m = umin3_2(m, v[j], v[j + 1]);
+    if ((NR & 1) == 0) m = umin2(m, v[NR - 1]);
+    return m;
+}
+
+// pad mask: 0x7fff in every half whose disparity index is >= D
+template <int NR>
+__device__ __forceinline__ void make_padmask(unsigned (&pm)[NR], int gl, int D) {
+#pragma unroll
+    for (int j = 0; j < NR; j++) {
+        int d = gl * 2 * NR + 2 * j;
+        pm[j] = (d >= D ? 0x7fffu : 0u) | (d + 1 >= D ? 0x7fff0000u : 0u);
+    }
+}
+
+// quirk: sgbm_3way D%8 tail artefact (A.7): 0 none, 1 "d-1 neighbour of d0 comes from the
+// already-updated current column", 2 "d-1 neighbour of d0 is ignored". d0 = 8*floor(D/8).
+template <int LW, int NR>
+__device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const unsigned (&Cq)[NR],
+                                         const unsigned (&pm)[NR], const unsigned gmask, const int gl,
+                                         const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
+    unsigned up = __shfl_up_sync(gmask, L[NR - 1], 1, LW);
+    unsigned dn = __shfl_down_sync(gmask, L[0], 1, LW);
+    if (gl == 0) up = 0x7fff7fffu;
+    if (gl == LW - 1) dn = 0x7fff7fffu;
+    const unsigned mm = pk2(m);
+    const unsigned dmp = pk2(m + P2mP1);
+    unsigned Ln[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) {
+        unsigned bq = shift_pair(j == 0 ? up : L[j - 1], L[j]);            // (L[d-1], L[d])
+        unsigned cn = shift_pair(L[j], j == NR - 1 ? dn : L[j + 1]);       // (L[d+1], L[d+2])
+        unsigned tt = umin3_2(bq, cn, dmp);
+        tt = uaddmin2(tt, P1P1, L[j]);
+        Ln[j] = umax2(Cq[j] + tt - mm, pm[j]);
+    }
+    if (quirk) {
+        // d0 is a multiple of 8, so it sits in register 0 or (NR == 8) register 4 of lane d0 / (2 NR)
+        const unsigned upn = __shfl_up_sync(gmask, Ln[NR - 1], 1, LW);
+        const int ql = d0 / (2 * NR), jq = (d0 % (2 * NR)) / 2;
+        if (gl == ql) {
+            if (jq == 0) {
+                unsigned bq = shift_pair(quirk == 1 ? upn : 0x7fff7fffu, L[0]);
+                unsigned cn = shift_pair(L[0], NR == 1 ? dn : L[NR > 1 ? 1 : 0]);
+                unsigned tt = uaddmin2(umin3_2(bq, cn, dmp), P1P1, L[0]);
+                Ln[0] = umax2(Cq[0] + tt - mm, pm[0]);
+            } else if (NR >= 8) {
+                constexpr int J = NR / 2;
+                unsigned bq = shift_pair(quirk == 1 ? Ln[J - 1] : 0x7fff7fffu, L[J]);
+                unsigned cn = shift_pair(L[J], L[J + 1 < NR ? J + 1 : J]);
+                unsigned tt = uaddmin2(umin3_2(bq, cn, dmp), P1P1, L[J]);
+                Ln[J] = umax2(Cq[J] + tt - mm, pm[J]);
+            }
+        }
+    }
+    unsigned mn = group_min2<LW>(local_min2<NR>(Ln), gmask);
+    m = min(mn & 0xffffu, mn >> 16);
+#pragma unroll
+    for (int j = 0; j < NR; j++) L[j] = Ln[j];
+}
+
+template <int NR>
+__device__ __forceinline__ void sgm_reset(unsigned (&L)[NR], unsigned& m) {
+#pragma unroll
+    for (int j = 0; j < NR; j++) L[j] = 0u;
+    m = 0u;
+}
+
+// dynamic element fetch from a register array (k in [0, 2*NR))
+template <int NR>
+__device__ __forceinline__ int elem_of(const unsigned (&v)[NR], int k) {
+    unsigned r = v[0];
+#pragma unroll
+    for (int j = 1; j < NR; j++) r = ((k >> 1) == j) ? v[j] : r;
+    return (k & 1) ? (int)(r >> 16) : (int)(r & 0xffffu);
+}

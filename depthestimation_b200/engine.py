@@ -115,6 +115,10 @@ class StereoEngine:
     def sync(self):
         self._check(self._lib.b200s_sync(self._h), "b200s_sync")
 
+    def set_debug_flow(self, on=True):
+        """Generic per-direction kernels that materialise the full S volume (for the S stage tap)."""
+        self._lib.b200s_set_debug_flow(self._h, int(on))
+
     def enable_timing(self, on=True):
         self._lib.b200s_enable_timing(self._h, int(on))
 

@@ -151,6 +151,10 @@ int b200s_geometry(const B200sHandle* h, int W, int* W1, int* minX1, int* Dp, in
  * which = 0: block cost C (int16 [H][W1][D], includes +P2 like the reference's C),
  *         1: aggregate S (int16 [H][W1][D]), 2: raw disparity before median/speckle (int16 HxW). */
 int b200s_debug_stage(B200sHandle* h, int which, int b, int16_t* out);
+/* on != 0: run the matcher with the generic one-direction-per-launch kernels that materialise the
+ * full aggregate S (needed for the S tap above; slower, same results). Default off: horizontal
+ * paths + winner selection are fused (rows.cu) and S holds only the vertical-family aggregate. */
+int b200s_set_debug_flow(B200sHandle* h, int on);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 long long b200s_launch_count(const B200sHandle* h);
 /* Device time in ms of the last *_dev / host call, measured with CUDA events on the handle's

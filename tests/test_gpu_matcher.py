@@ -22,10 +22,21 @@ def engine():
 
 
 def _check(engine, L, R, stages=True, **kw):
+    """Product flow (fused row kernel) against the oracle's disparity; then the debug flow (generic
+    kernels, full S materialised) against the oracle's C / S / raw stages."""
     engine.configure(**kw)
+    engine.set_debug_flow(False)
     got = engine.compute(L, R)
     ref = oracle.sgbm_compute(L, R, oracle.make_params(**kw), stages=stages)
     H, W = L.shape
+    d = ref["disp"] if stages else ref
+    assert np.array_equal(got, d), f"disp: {(got != d).sum()} px differ {kw}"
+    if stages and ref["raw"] is not None:
+        raw = engine.debug_stage("raw", H, W)
+        assert np.array_equal(raw, ref["raw"]), f"raw(fused): {(raw != ref['raw']).sum()} px differ {kw}"
+    engine.set_debug_flow(True)
+    got = engine.compute(L, R)
+    engine.set_debug_flow(False)
     if stages and ref["C"] is not None:
         C = engine.debug_stage("C", H, W)
         assert np.array_equal(C, ref["C"]), f"C: {(C != ref['C']).sum()} cells differ {kw}"
