@@ -47,11 +47,14 @@ __device__ __forceinline__ void store_regs(uint16_t* p, const unsigned (&r)[NR])
     for (int q = 0; q < NR / 4; q++) *(uint4*)(p + 8 * q) = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#define ROW_PD 6  // L2 prefetch distance in columns
+
 // ---- A.6 steps 1-4 for one pixel whose S(., d) sits in v[] across the lane group ------------------
 template <int LW, int NR>
 __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigned (&pm)[NR], const RowArgs& a,
                                           const unsigned gmask, const int gl, const int gbase, const int xc,
-                                          unsigned* keys, int16_t* out) {
+                                          unsigned* keys, int16_t* out, const bool valid) {
     constexpr int DPL = 2 * NR;
     unsigned w[NR];
 #pragma unroll
@@ -169,7 +172,7 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
     const int dm = max(best - 1, 0), dq = min(best + 1, a.Dp - 1);
     const int Sm = __shfl_sync(gmask, elem_of<NR>(v, dm % DPL), dm / DPL, LW);
     const int Sq = __shfl_sync(gmask, elem_of<NR>(v, dq % DPL), dq / DPL, LW);
-    if (reject || gl != 0) return;
+    if (reject || gl != 0 || !valid) return;
     const int x2 = xc + a.minX1 - best - a.minD;
     if (minS < 32767) {
         const unsigned nk = ((unsigned)minS << 16) | (0xffffu - (unsigned)best);
@@ -190,9 +193,12 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
     extern __shared__ __align__(16) uint4 rsm[];    // [LINES][ROW_K][NR/4][LW] uint4: L(<-) of the current chunk
     const int gl = threadIdx.x % LW;
     const int lic = threadIdx.x / LW;               // line in CTA
-    const int line = blockIdx.x * LINES + lic;
-    if (line >= a.nlines) return;
-    const unsigned gmask = group_mask<LW>();
+    const int line_raw = blockIdx.x * LINES + lic;
+    const bool valid = line_raw < a.nlines;
+    const int line = valid ? line_raw : a.nlines - 1;   // keep the warp converged: surplus groups shadow the last line
+    // every lane of the warp runs the same loops, so shuffles use the full mask with width LW (no
+    // divergence check per shuffle); ballots are shifted by gbase
+    const unsigned gmask = 0xffffffffu;
     const int gbase = (threadIdx.x & 31) / LW * LW;
     const bool active = gl * DPL < a.Dp;
     uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;
@@ -210,22 +216,30 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
     unsigned* keys = a.keys + (size_t)line * a.W;
     int16_t* out = a.raw + (size_t)line * a.W;
 
-    for (int x = gl; x < a.W; x += LW) { keys[x] = 0xffffffffu; out[x] = (int16_t)a.INV; }
-    __syncwarp(gmask);
+    if (valid)
+        for (int x = gl; x < a.W; x += LW) { keys[x] = 0xffffffffu; out[x] = (int16_t)a.INV; }
+    __syncwarp();
 
     unsigned L[NR], Cq[NR];
     unsigned m;
     // ---- pass 1: <- over the row, checkpoint L at every K-th column ------------------------------
     const int nchunks = (a.W1 + ROW_K - 1) / ROW_K;
     sgm_reset<NR>(L, m);
+    unsigned Cn[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) Cn[j] = 0u;
+    if (active && a.W1 - 1 >= ROW_K) load_regs_nc<NR>(Crow + (size_t)(a.W1 - 1) * a.Dp, Cn);
     for (int x = a.W1 - 1; x >= ROW_K; x--) {
 #pragma unroll
-        for (int j = 0; j < NR; j++) Cq[j] = 0u;
-        if (active) load_regs_nc<NR>(Crow + (size_t)x * a.Dp, Cq);
+        for (int j = 0; j < NR; j++) Cq[j] = Cn[j];
+        if (active) {
+            if (x - 1 >= ROW_K) load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, Cn);
+            if (x - ROW_PD >= ROW_K) prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
+        }
         sgm_step<LW, NR>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
-        if ((x % ROW_K) == 0 && active) store_regs<NR>(ck + (size_t)(x / ROW_K) * a.Dp, L);
+        if ((x % ROW_K) == 0 && active && valid) store_regs<NR>(ck + (size_t)(x / ROW_K) * a.Dp, L);
     }
-    __syncwarp(gmask);
+    __syncwarp();
     // ---- pass 2: chunk by chunk, left to right ------------------------------------------------------
     unsigned Lr[NR];   // L(->)
     unsigned mr;
@@ -242,24 +256,43 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
         } else {
             sgm_reset<NR>(L, m);
         }
+        if (active) {
+            load_regs_nc<NR>(Crow + (size_t)(xe - 1) * a.Dp, Cn);
+            // next chunk: bring C and Sv towards L2 while this chunk is processed
+            if (xe + gl < a.W1 && gl < ROW_K) {
+                prefetch_l2(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL);
+                prefetch_l2(Srow + (size_t)(xe + gl) * a.Dp - gl * DPL);
+                if (a.Dp > 64) {
+                    prefetch_l2(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL + 64);
+                    prefetch_l2(Srow + (size_t)(xe + gl) * a.Dp - gl * DPL + 64);
+                }
+            }
+        }
         for (int x = xe - 1; x >= xs; x--) {
 #pragma unroll
-            for (int j = 0; j < NR; j++) Cq[j] = 0u;
-            if (active) load_regs_nc<NR>(Crow + (size_t)x * a.Dp, Cq);
+            for (int j = 0; j < NR; j++) Cq[j] = Cn[j];
+            if (active && x - 1 >= xs) load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, Cn);
             sgm_step<LW, NR>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
 #pragma unroll
             for (int q = 0; q < NR / 4; q++)
                 Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
         }
-        __syncwarp(gmask);
+        __syncwarp();
         // -> over the chunk, S = Sv + L(->) + L(<-), winner selection
+        unsigned Sn[NR];
+#pragma unroll
+        for (int j = 0; j < NR; j++) { Cn[j] = 0u; Sn[j] = 0u; }
+        if (active) {
+            load_regs_nc<NR>(Crow + (size_t)xs * a.Dp, Cn);
+            load_regs_nc<NR>(Srow + (size_t)xs * a.Dp, Sn);
+        }
         for (int x = xs; x < xe; x++) {
             unsigned Sq[NR];
 #pragma unroll
-            for (int j = 0; j < NR; j++) { Cq[j] = 0u; Sq[j] = 0u; }
-            if (active) {
-                load_regs_nc<NR>(Crow + (size_t)x * a.Dp, Cq);
-                load_regs_nc<NR>(Srow + (size_t)x * a.Dp, Sq);
+            for (int j = 0; j < NR; j++) { Cq[j] = Cn[j]; Sq[j] = Sn[j]; }
+            if (active && x + 1 < xe) {
+                load_regs_nc<NR>(Crow + (size_t)(x + 1) * a.Dp, Cn);
+                load_regs_nc<NR>(Srow + (size_t)(x + 1) * a.Dp, Sn);
             }
             sgm_step<LW, NR>(Lr, mr, Cq, pm, gmask, gl, P1P1, P2mP1, 0, d0);
 #pragma unroll
@@ -270,13 +303,13 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
                 Sq[4 * q + 2] = uaddmin2(uaddmin2(Sq[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
                 Sq[4 * q + 3] = uaddmin2(uaddmin2(Sq[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
             }
-            wta_pixel<LW, NR>(Sq, pm, a, gmask, gl, gbase, x, keys, out);
+            wta_pixel<LW, NR>(Sq, pm, a, gmask, gl, gbase, x, keys, out, valid);
         }
-        __syncwarp(gmask);
+        __syncwarp();
     }
     // ---- A.6 step 5: left-right check on the finished row ---------------------------------------------
-    __syncwarp(gmask);
-    for (int x = a.minX1 + gl; x < a.maxX1; x += LW) {
+    __syncwarp();
+    for (int x = a.minX1 + gl; x < a.maxX1 && valid; x += LW) {
         int d1 = out[x];
         if (d1 == a.INV) continue;
         const int _d = d1 >> 4, d_ = (d1 + 15) >> 4;

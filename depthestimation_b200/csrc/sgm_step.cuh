@@ -94,11 +94,12 @@ __device__ __forceinline__ void sgm_reset(unsigned (&L)[NR], unsigned& m) {
     m = 0u;
 }
 
-// dynamic element fetch from a register array (k in [0, 2*NR))
+// dynamic element fetch from a register array (k in [0, 2*NR)), kept in registers (mask-and-or, no local memory)
 template <int NR>
 __device__ __forceinline__ int elem_of(const unsigned (&v)[NR], int k) {
-    unsigned r = v[0];
+    unsigned r = 0u;
+    const int kk = k >> 1;
 #pragma unroll
-    for (int j = 1; j < NR; j++) r = ((k >> 1) == j) ? v[j] : r;
+    for (int j = 0; j < NR; j++) r |= v[j] & (0u - (unsigned)(kk == j));
     return (k & 1) ? (int)(r >> 16) : (int)(r & 0xffffu);
 }
