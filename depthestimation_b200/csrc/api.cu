@@ -298,11 +298,18 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
 // postprocess_disparity (hole filling off) / fast-mode median on a dense device batch, result in `out`
 static int dev_post(B200sHandle* h, const float* dIn, int B, int H, int W, const B200sPostParams& pp, float* out) {
     const size_t n = (size_t)B * H * W;
-    if (pp.fastMode) {
+    const int mode = pp.fastMode;   // B200S_POST_*
+    if (mode == B200S_POST_MEDIAN_ONLY) {
         launch_median3_f32(dIn, out, B, H, W, h->stream);
         h->launches++;
         return check_launch(h, "post(fast)");
     }
+    if (mode == B200S_POST_OUTLIERS_ONLY) {
+        launch_outliers(dIn, out, B, H, W, pp.outlierThreshold, h->stream);
+        h->launches++;
+        return check_launch(h, "post(outliers)");
+    }
+    if (mode < 0 || mode > B200S_POST_NO_MEDIAN) { h->set_error(B200S_E_INVALID, "postprocess: bad fastMode/stage selector %d", mode); return B200S_E_INVALID; }
     CUDA_TRY(h, h->s16c.ensure(n * 2));
     CUDA_TRY(h, h->labels.ensure(n * sizeof(int)));
     CUDA_TRY(h, h->sizes.ensure(n * sizeof(int)));
@@ -312,15 +319,23 @@ static int dev_post(B200sHandle* h, const float* dIn, int B, int H, int W, const
     launch_f32_to_s16x16(dIn, n, s16, h->stream);
     launch_speckle(s16, B, H, W, 0, pp.maxSpeckleSize, pp.maxDiff16, h->labels.as<int>(), h->sizes.as<int>(), h->stream, &h->launches);
     h->launches += 2;
-    if (pp.applyOutlierRemoval) {
+    const bool outl = pp.applyOutlierRemoval && mode != B200S_POST_SPECKLE_ONLY;
+    const bool med = (mode == B200S_POST_FULL);
+    if (outl && med) {
         launch_s16_to_f32_div16(s16, n, out, h->stream);       // out used as temp
         launch_outliers(out, t, B, H, W, pp.outlierThreshold, h->stream);
         launch_median3_f32(t, out, B, H, W, h->stream);
         h->launches += 2;
-    } else {
+    } else if (outl) {
+        launch_s16_to_f32_div16(s16, n, t, h->stream);
+        launch_outliers(t, out, B, H, W, pp.outlierThreshold, h->stream);
+        h->launches += 1;
+    } else if (med) {
         launch_s16_to_f32_div16(s16, n, t, h->stream);
         launch_median3_f32(t, out, B, H, W, h->stream);
         h->launches += 1;
+    } else {
+        launch_s16_to_f32_div16(s16, n, out, h->stream);
     }
     return check_launch(h, "post");
 }

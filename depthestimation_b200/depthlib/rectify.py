@@ -1,0 +1,143 @@
+"""Stereo rectification — drop-in for depthlib/rectify.py of the reference.
+
+Per frame (hot path): gray conversion and the two bilinear remaps run on the GPU (C ABI
+``b200s_bgr2gray`` / ``b200s_remap_u8``; reference: rectify.py:108-119, 185-186).
+Once per calibration (cold): the maps themselves come from host ``cv2.stereoRectify`` +
+``cv2.initUndistortRectifyMap`` exactly as rectify.py:63-73 does (double-precision camera math,
+out of the hot path — SURVEY.md §2 row 2). Size fix-up (rectify.py:92-105) stays host ``cv2.resize``.
+"""
+from __future__ import annotations
+
+import warnings
+from typing import Any, Dict, Optional, Tuple
+
+import numpy as np
+
+__all__ = ["rectify_images", "RectificationCache"]
+
+_shared_engine = None
+
+
+def _engine(engine=None):
+    """The caller's engine, or a lazily created module-level one (device 0) for the free functions."""
+    global _shared_engine
+    if engine is not None:
+        return engine
+    if _shared_engine is None:
+        from ..engine import StereoEngine
+        _shared_engine = StereoEngine(0)
+    return _shared_engine
+
+
+def _cv2():
+    try:
+        import cv2
+        return cv2
+    except Exception as exc:  # pragma: no cover
+        raise RuntimeError("building rectification maps needs host cv2 (stereoRectify / initUndistortRectifyMap); "
+                           "pass precomputed maps to StereoEngine.set_maps instead") from exc
+
+
+def _key_part(arr):
+    return None if arr is None else tuple(np.asarray(arr).flatten())
+
+
+class RectificationCache:
+    """Keeps the four CV_32FC1 maps of the last calibration (reference: rectify.py:14-87): same key,
+    same dict object returned while the calibration is unchanged."""
+
+    def __init__(self):
+        self._cache_key: Optional[tuple] = None
+        self._maps: Optional[Dict[str, np.ndarray]] = None
+
+    def _make_key(self, cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
+                  dist_coeff_L, dist_coeff_R, rotation, translation, alpha) -> tuple:
+        return (_key_part(cam_matrix_L), _key_part(cam_matrix_R), baseline, image_width, image_height,
+                _key_part(dist_coeff_L), _key_part(dist_coeff_R), _key_part(rotation), _key_part(translation), alpha)
+
+    def get_maps(self, cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
+                 dist_coeff_L=None, dist_coeff_R=None, rotation=None, translation=None,
+                 alpha=0.0) -> Dict[str, np.ndarray]:
+        key = self._make_key(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
+                             dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
+        if self._cache_key == key and self._maps is not None:
+            return self._maps
+        self._maps = _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
+                                 dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
+        self._cache_key = key
+        return self._maps
+
+    def clear(self):
+        self._cache_key = None
+        self._maps = None
+
+
+_global_cache = RectificationCache()
+
+
+def _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height, dist_coeff_L, dist_coeff_R,
+                rotation, translation, alpha) -> Dict[str, np.ndarray]:
+    """cv2.stereoRectify(CALIB_ZERO_DISPARITY) + 2x initUndistortRectifyMap(CV_32FC1); defaults as the
+    reference: zero distortion, R = I, T = [-baseline, 0, 0] (rectify.py:52-73)."""
+    cv2 = _cv2()
+    K_L = np.asarray(cam_matrix_L, dtype=np.float64)
+    K_R = np.asarray(cam_matrix_R, dtype=np.float64)
+    zero = np.zeros(5, dtype=np.float64)
+    d_L = np.asarray(dist_coeff_L, dtype=np.float64) if dist_coeff_L is not None else zero
+    d_R = np.asarray(dist_coeff_R, dtype=np.float64) if dist_coeff_R is not None else zero
+    size = (image_width, image_height)
+    R = np.asarray(rotation, dtype=np.float64) if rotation is not None else np.eye(3, dtype=np.float64)
+    T = (np.asarray(translation, dtype=np.float64) if translation is not None
+         else np.array([-baseline, 0.0, 0.0], dtype=np.float64))
+    rect_L, rect_R, proj_L, proj_R, _Q, _roi_L, _roi_R = cv2.stereoRectify(
+        K_L, d_L, K_R, d_R, size, R, T, flags=cv2.CALIB_ZERO_DISPARITY, alpha=alpha)
+    map1_L, map2_L = cv2.initUndistortRectifyMap(K_L, d_L, rect_L, proj_L, size, cv2.CV_32FC1)
+    map1_R, map2_R = cv2.initUndistortRectifyMap(K_R, d_R, rect_R, proj_R, size, cv2.CV_32FC1)
+    return {'map1_L': map1_L, 'map2_L': map2_L, 'map1_R': map1_R, 'map2_R': map2_R}
+
+
+def _ensure_image_size(image: np.ndarray, size: Tuple[int, int]) -> np.ndarray:
+    """Warn and resize (INTER_LINEAR, host) when the image does not match the calibration size."""
+    height, width = image.shape[:2]
+    if (width, height) == tuple(size):
+        return image
+    warnings.warn("Input image size %sx%s does not match calibration %sx%s; resizing for rectification." %
+                  (width, height, size[0], size[1]), RuntimeWarning, stacklevel=2)
+    return _cv2().resize(image, tuple(size), interpolation=_cv2().INTER_LINEAR)
+
+
+def _to_grayscale(image: np.ndarray, engine=None) -> np.ndarray:
+    """Gray conversion with BGR weights on the channels as stored (GPU; reference: rectify.py:108-119)."""
+    if image.ndim == 2:
+        return image
+    if image.ndim == 3 and image.shape[2] == 1:
+        return image[:, :, 0]
+    if image.ndim == 3 and image.shape[2] == 3:
+        return _engine(engine).bgr2gray(image)
+    raise ValueError("Unsupported image format for grayscale conversion")
+
+
+def rectify_images(img_L: np.ndarray, img_R: np.ndarray, cam_matrix_L: np.ndarray, cam_matrix_R: np.ndarray,
+                   baseline: float, image_width: int, image_height: int,
+                   dist_coeff_L: Any = None, dist_coeff_R: Any = None, rotation: Any = None, translation: Any = None,
+                   alpha: float = 0.0, cache: Optional[RectificationCache] = None, engine=None
+                   ) -> Tuple[np.ndarray, np.ndarray]:
+    """Rectify a stereo pair; returns two uint8 gray images of the calibration size (rectify.py:122-237).
+    With ``cache`` the maps are reused across frames; without it they are rebuilt per call, as upstream."""
+    if cache is not None:
+        maps = cache.get_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
+                              dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
+    else:
+        maps = _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
+                           dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
+    size = (image_width, image_height)
+    img_L = _ensure_image_size(img_L, size)
+    img_R = _ensure_image_size(img_R, size)
+    eng = _engine(engine)
+    gray_L = np.ascontiguousarray(_to_grayscale(img_L, eng))
+    gray_R = np.ascontiguousarray(_to_grayscale(img_R, eng))
+    if getattr(eng, "_maps_id", None) != id(maps):
+        eng.set_maps(maps['map1_L'], maps['map2_L'], maps['map1_R'], maps['map2_R'])
+        eng._maps_id = id(maps)
+        eng._maps_ref = maps  # keep the dict alive so its id cannot be reused
+    return eng.remap(gray_L, gray_R)

@@ -1,0 +1,215 @@
+"""StereoCore — drop-in for depthlib/stereo_core.py of the reference, with every per-frame op on the GPU.
+
+Same constructor, attributes (``sgbm_params`` with the reference's 22 keys, ``sgbm``, ``_rect_cache``,
+``disparity_map``, ``depth_map``, ``left_rectified``, ``right_rectified``), methods and error texts as
+the reference (file:line cited per method). What changes is what sits behind them:
+
+* ``self.sgbm`` is a ``B200SGBM`` whose ``.compute(L, R)`` has the contract of ``cv2.StereoSGBM.compute``
+  (int16, 16x fixed point) but runs libb200stereo.so (C ABI ``b200s_sgbm_compute``)
+* rectification remap, post-filters and depth reprojection are C-ABI calls too
+* ``estimate_depth`` uses ONE fused C-ABI call (``b200s_pipeline``) when nothing was monkey-patched
+
+There is no CPU fallback: the first compute without a CUDA device raises ``EngineError``.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+
+from ..engine import StereoEngine, make_depth_params, make_post_params
+from .rectify import RectificationCache, _ensure_image_size, _to_grayscale, rectify_images
+from .postprocess import postprocess_disparity
+
+_SGBM_KEYS = ("min_disp", "num_disp", "block_size", "disp12_max_diff", "prefilter_cap", "uniqueness_ratio",
+              "speckle_window_size", "speckle_range", "sgbm_mode")
+
+
+class B200SGBM:
+    """Stands where ``cv2.StereoSGBM`` stands in the reference (stereo_core.py:63-75): ``compute`` returns
+    the int16 fixed-point disparity. The engine (GPU handle) is created on first use."""
+
+    def __init__(self, device: int = 0, **sgbm_kw):
+        self.device = device
+        self.kw = dict(sgbm_kw)
+        self._engine: Optional[StereoEngine] = None
+
+    @property
+    def engine(self) -> StereoEngine:
+        if self._engine is None:
+            self._engine = StereoEngine(self.device, **self.kw)
+        return self._engine
+
+    def reconfigure(self, **sgbm_kw):
+        self.kw = dict(sgbm_kw)
+        if self._engine is not None:
+            self._engine.configure(**self.kw)
+
+    def compute(self, left: np.ndarray, right: np.ndarray) -> np.ndarray:
+        return self.engine.compute(left, right)
+
+
+class StereoCore:
+    '''Handles common stereo operations (reference: depthlib/stereo_core.py:7-293).'''
+
+    def __init__(self, downscale_factor=1.0, fast_mode=False, device: int = 0) -> None:
+        self.downscale_factor = downscale_factor
+        self.fast_mode = fast_mode
+        self.device = device
+        self.sgbm = None
+        self._rect_cache = RectificationCache()
+        # same keys, order and defaults as stereo_core.py:16-39
+        self.sgbm_params = {
+            'min_disp': 0, 'num_disp': 128, 'block_size': 5, 'disp12_max_diff': 1, 'prefilter_cap': 31,
+            'uniqueness_ratio': 10, 'speckle_window_size': 50, 'speckle_range': 2, 'sgbm_mode': 'sgbm_3way',
+            'focal_length': None, 'baseline': None, 'doffs': 0.0, 'max_depth': None,
+            'cam_matrix_L': None, 'cam_matrix_R': None, 'image_width': None, 'image_height': None,
+            'dist_coeff_L': None, 'dist_coeff_R': None, 'rotation': None, 'translation': None,
+            'hole_filling': False,
+        }
+        self._build_sgbm()
+        self.disparity_map = None
+        self.depth_map = None
+        self.left_rectified = None
+        self.right_rectified = None
+
+    # -- matcher configuration (stereo_core.py:44-123) ------------------------------------------------
+    def _matcher_kwargs(self):
+        p = self.sgbm_params
+        kw = {k: p[k] for k in _SGBM_KEYS}
+        kw['sgbm_mode'] = p.get('sgbm_mode', 'sgbm_3way')
+        return kw  # P1 = 8 bs^2 and P2 = 32 bs^2 are derived in engine.make_params, as at :51-52
+
+    def _build_sgbm(self):
+        """(Re)configure the matcher from ``sgbm_params`` (reference: stereo_core.py:44-75)."""
+        kw = self._matcher_kwargs()
+        if isinstance(self.sgbm, B200SGBM):
+            self.sgbm.reconfigure(**kw)
+        else:
+            self.sgbm = B200SGBM(self.device, **kw)
+
+    def configure_sgbm(self, **kwargs):
+        """Update parameters and rebuild the matcher (reference: stereo_core.py:77-123). As in the
+        reference, num_disp / focal_length / doffs are scaled by downscale_factor on EVERY call."""
+        valid_params = self.sgbm_params.keys()
+        for key in kwargs:
+            if key not in valid_params:
+                raise ValueError(f"Invalid parameter '{key}'. Valid parameters: {list(valid_params)}")
+        if 'num_disp' in kwargs:
+            kwargs['num_disp'] = int(kwargs['num_disp'] * self.downscale_factor)
+        if 'focal_length' in kwargs:
+            kwargs['focal_length'] = kwargs['focal_length'] * self.downscale_factor
+        if 'doffs' in kwargs:
+            kwargs['doffs'] = kwargs['doffs'] * self.downscale_factor
+        self.sgbm_params.update(kwargs)
+        self._build_sgbm()
+
+    def get_sgbm_params(self) -> Dict[str, int]:
+        return self.sgbm_params.copy()
+
+    # -- rectification (stereo_core.py:125-160) ------------------------------------------------------------
+    def _calibration(self):
+        p = self.sgbm_params
+        need = [p.get('cam_matrix_L'), p.get('cam_matrix_R'), p.get('baseline'), p.get('image_width'),
+                p.get('image_height')]
+        return all(v is not None for v in need)
+
+    def _prepare_rectified(self, left_img: np.ndarray, right_img: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+        """Rectify if calibration exists, otherwise ensure grayscale."""
+        p = self.sgbm_params
+        if self._calibration():
+            return rectify_images(
+                left_img, right_img, p['cam_matrix_L'], p['cam_matrix_R'], p['baseline'], p['image_width'],
+                p['image_height'], dist_coeff_L=p.get('dist_coeff_L'), dist_coeff_R=p.get('dist_coeff_R'),
+                rotation=p.get('rotation'), translation=p.get('translation'), alpha=1.0, cache=self._rect_cache,
+                engine=self.sgbm.engine)
+        eng = self.sgbm.engine
+        if left_img.ndim == 3:
+            left_img = eng.bgr2gray(left_img)
+        if right_img.ndim == 3:
+            right_img = eng.bgr2gray(right_img)
+        return left_img, right_img
+
+    # -- per-pair pipeline (stereo_core.py:162-200) -----------------------------------------------------------
+    def _post_params(self):
+        return make_post_params(self.fast_mode, int(100 * self.downscale_factor), 1.0, 2.5, True)
+
+    def _depth_params(self):
+        p = self.sgbm_params
+        return make_depth_params(p.get('focal_length', None), p.get('baseline', None), p.get('doffs', 0.0),
+                                 eps=p.get('min_disp', 5.0), max_depth=p.get('max_depth'))
+
+    def _process_pair(self, left_img: np.ndarray, right_img: np.ndarray) -> Tuple[np.ndarray, Optional[np.ndarray]]:
+        """Full pipeline for a single rectified pair. ``compute_disparity`` is looked up on ``self`` so that
+        it can be replaced (the reference's tests/test_postproc_logic.py does)."""
+        disparity_px = self.compute_disparity(left_img, right_img)
+        disparity_px = disparity_px[:, self.sgbm_params['num_disp']:]   # crop the left band (:168)
+        eng = self.sgbm.engine
+        if self.fast_mode:
+            disparity_px = eng.postprocess(disparity_px, make_post_params(True))
+        else:
+            disparity_px = postprocess_disparity(
+                disparity_px, left_image=left_img, max_speckle_size=int(100 * self.downscale_factor), max_diff=1.0,
+                outlier_threshold=2.5, fill_method='inpaint', apply_outlier_removal=True,
+                apply_hole_filling=self.sgbm_params.get('hole_filling', False), engine=eng)
+        depth_m = None
+        f_pixels = self.sgbm_params.get('focal_length', None)
+        baseline_m = self.sgbm_params.get('baseline', None)
+        if f_pixels is not None and baseline_m is not None:
+            depth_m = self.disparity_to_depth(disparity_px, f_pixels, baseline_m, self.sgbm_params.get('doffs', 0.0),
+                                              eps=self.sgbm_params.get('min_disp', 5.0),
+                                              max_depth=self.sgbm_params.get('max_depth'))
+        self.disparity_map = disparity_px
+        self.depth_map = depth_m
+        return disparity_px, depth_m
+
+    def compute_disparity(self, rectified_L: np.ndarray, rectified_R: np.ndarray) -> np.ndarray:
+        """Disparity in pixels, float32 HxW (reference: stereo_core.py:212-232)."""
+        if self.sgbm is None:
+            self._build_sgbm()
+        disp_fixed = self.sgbm.compute(rectified_L, rectified_R)
+        return disp_fixed.astype(np.float32) / 16.0
+
+    def disparity_to_depth(self, disp: np.ndarray, f_pixels: float, baseline_m: float, doffs: float = 0.0,
+                           eps: float = 1e-6, max_depth: Optional[float] = None) -> np.ndarray:
+        """Z = f*B / (d + doffs), inf where d + doffs <= eps, clamped to max_depth (stereo_core.py:234-272)."""
+        disp = np.asarray(disp, dtype=np.float32)
+        dp = make_depth_params(f_pixels, baseline_m, doffs, eps, max_depth)
+        return self.sgbm.engine.disp_to_depth(disp, dp).reshape(disp.shape)
+
+    # -- public entry (stereo_core.py:274-293) ------------------------------------------------------------------
+    def _can_fuse(self, left, right) -> bool:
+        if 'compute_disparity' in self.__dict__ or type(self).compute_disparity is not StereoCore.compute_disparity:
+            return False   # somebody replaced the matcher call: honour it
+        if type(self)._process_pair is not StereoCore._process_pair or '_process_pair' in self.__dict__:
+            return False
+        if self.sgbm_params.get('hole_filling', False) and not self.fast_mode:
+            return False   # Telea inpainting stays on the host
+        return isinstance(self.sgbm, B200SGBM)
+
+    def estimate_depth(self, left_source, right_source) -> Tuple[np.ndarray, Optional[np.ndarray]]:
+        """Raw images -> rectification -> disparity -> depth. One fused C-ABI call when possible."""
+        if left_source is None or right_source is None:
+            raise ValueError("Left and right sources must be set before estimating depth.")
+        if not self._can_fuse(left_source, right_source):
+            self.left_rectified, self.right_rectified = self._prepare_rectified(left_source, right_source)
+            return self._process_pair(self.left_rectified, self.right_rectified)
+        eng = self.sgbm.engine
+        p = self.sgbm_params
+        use_maps = self._calibration()
+        left, right = left_source, right_source
+        if use_maps:
+            maps = self._rect_cache.get_maps(p['cam_matrix_L'], p['cam_matrix_R'], p['baseline'], p['image_width'],
+                                             p['image_height'], p.get('dist_coeff_L'), p.get('dist_coeff_R'),
+                                             p.get('rotation'), p.get('translation'), 1.0)
+            size = (p['image_width'], p['image_height'])
+            left, right = _ensure_image_size(left, size), _ensure_image_size(right, size)
+            if getattr(eng, "_maps_id", None) != id(maps):
+                eng.set_maps(maps['map1_L'], maps['map2_L'], maps['map1_R'], maps['map2_R'])
+                eng._maps_id, eng._maps_ref = id(maps), maps
+        left, right = _to_grayscale(left, eng), _to_grayscale(right, eng)
+        disp, depth, rl, rr = eng.pipeline(left, right, self._post_params(), self._depth_params(),
+                                           use_maps=use_maps, want_rect=use_maps)
+        self.left_rectified, self.right_rectified = (rl, rr) if use_maps else (left, right)
+        self.disparity_map, self.depth_map = disp, depth
+        return disp, depth

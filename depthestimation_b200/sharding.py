@@ -1,0 +1,131 @@
+"""Frame sharding across GPUs: frames are independent, so frame/chunk i goes to GPU
+i mod G; every GPU has its own engine handle + stream + host worker thread, results are gathered on
+the host in frame order. No collective on the data path.
+
+Two drivers:
+* ``ThreadedSharder``  — one process, G engines, G worker threads (what StereoDepthEstimatorVideo uses)
+* ``frames_for_rank`` / ``gather_in_order`` — one process per GPU under torchrun (what bench.py uses);
+  the gather is a host-side ``torch.distributed`` object gather (gloo is enough)
+"""
+from __future__ import annotations
+
+import queue
+import threading
+from typing import Callable, Dict, Iterable, Iterator, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+
+def frames_for_rank(n_frames: int, rank: int, world: int) -> List[int]:
+    """Indices of the frames rank ``rank`` of ``world`` processes owns: i = rank (mod world)."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("need 0 <= rank < world")
+    return list(range(rank, n_frames, world))
+
+
+def gather_in_order(local: Dict[int, object], n_frames: int, group=None, dst: int = 0) -> Optional[List[object]]:
+    """Host-side gather of per-frame results to ``dst`` in frame order. Every rank passes the results of
+    the frames it owns (index -> object). Returns the ordered list on ``dst``, None elsewhere.
+    Raises if a frame is missing or produced twice."""
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    bucket = [None] * world if rank == dst else None
+    dist.gather_object(local, bucket, dst=dst, group=group)
+    if rank != dst:
+        return None
+    out: List[object] = [None] * n_frames
+    seen = [False] * n_frames
+    for part in bucket:
+        for i, v in part.items():
+            if not (0 <= i < n_frames) or seen[i]:
+                raise RuntimeError(f"frame {i} gathered twice or out of range")
+            out[i], seen[i] = v, True
+    if not all(seen):
+        raise RuntimeError(f"frames missing after gather: {[i for i, s in enumerate(seen) if not s][:8]}")
+    return out
+
+
+class ThreadedSharder:
+    """Chunks of frames -> GPUs round-robin, ordered results back.
+
+    ``make_worker(device) -> callable(lefts[B,H,W], rights[B,H,W]) -> (disp[B,...], depth[B,...] | None)``
+    is called once per device inside that device's worker thread (so each thread owns its handle, like one
+    cv2.StereoSGBM per thread in the reference). A failing worker re-queues its chunk for the others; when
+    every worker has failed the error is raised to the caller.
+    """
+
+    def __init__(self, devices: Sequence[int], make_worker: Callable[[int], Callable], chunk: int = 8,
+                 max_inflight: int = 4):
+        if not devices:
+            raise ValueError("ThreadedSharder needs at least one device")
+        self.devices, self.make_worker, self.chunk = list(devices), make_worker, max(1, int(chunk))
+        self.max_inflight = max(1, int(max_inflight))
+
+    def run(self, pairs: Iterable[Tuple[np.ndarray, np.ndarray]]) -> Iterator[Tuple[np.ndarray, Optional[np.ndarray]]]:
+        G = len(self.devices)
+        work: "queue.Queue" = queue.Queue()
+        done: Dict[int, object] = {}
+        cv = threading.Condition()
+        alive = [G]
+        errors: List[BaseException] = []
+
+        def worker(dev):
+            try:
+                fn = self.make_worker(dev)
+            except BaseException as exc:  # noqa: BLE001
+                with cv:
+                    errors.append(exc); alive[0] -= 1; cv.notify_all()
+                return
+            while True:
+                item = work.get()
+                if item is None:
+                    break
+                cid, L, R = item
+                try:
+                    res = fn(L, R)
+                except BaseException as exc:  # noqa: BLE001
+                    with cv:
+                        errors.append(exc); alive[0] -= 1
+                        if alive[0] > 0:
+                            work.put(item)       # another GPU picks the chunk up
+                        cv.notify_all()
+                    return
+                with cv:
+                    done[cid] = res
+                    cv.notify_all()
+
+        threads = [threading.Thread(target=worker, args=(d,), daemon=True) for d in self.devices]
+        for t in threads:
+            t.start()
+        submitted = emitted = 0
+        it = iter(pairs)
+        exhausted = False
+        try:
+            while True:
+                while not exhausted and submitted - emitted < self.max_inflight * G:
+                    Ls, Rs = [], []
+                    for l, r in it:
+                        Ls.append(l); Rs.append(r)
+                        if len(Ls) == self.chunk:
+                            break
+                    if not Ls:
+                        exhausted = True
+                        break
+                    work.put((submitted, np.ascontiguousarray(np.stack(Ls)), np.ascontiguousarray(np.stack(Rs))))
+                    submitted += 1
+                    if len(Ls) < self.chunk:
+                        exhausted = True
+                if emitted == submitted and exhausted:
+                    break
+                with cv:
+                    while emitted not in done:
+                        if alive[0] <= 0:
+                            raise RuntimeError(f"all GPU workers failed: {errors[-1]!r}") from errors[-1]
+                        cv.wait(timeout=0.5)
+                    disp, depth = done.pop(emitted)
+                emitted += 1
+                for k in range(disp.shape[0]):
+                    yield disp[k], (depth[k] if depth is not None else None)
+        finally:
+            for _ in threads:
+                work.put(None)

@@ -59,10 +59,21 @@ typedef struct B200sParams {
     int32_t mode;               /* B200S_MODE_* */
 } B200sParams;
 
+/* Which stages of postprocess_disparity run (B200sPostParams.fastMode). 0 and 1 are the two paths
+ * StereoCore._process_pair takes; 2-4 back the stand-alone functions of depthlib/postprocess.py. */
+enum {
+    B200S_POST_FULL = 0,           /* speckles -> outlier mask -> median (postprocess.py:120-171) */
+    B200S_POST_MEDIAN_ONLY = 1,    /* fast_mode (stereo_core.py:171-173) */
+    B200S_POST_SPECKLE_ONLY = 2,   /* filter_speckles (postprocess.py:6-35) */
+    B200S_POST_OUTLIERS_ONLY = 3,  /* detect_outliers + masking (postprocess.py:37-70, 151-158) */
+    B200S_POST_NO_MEDIAN = 4       /* speckles -> outlier mask; the caller fills holes, then runs 1 */
+};
+
 /* Keyword arguments of postprocess_disparity as passed at depthlib/stereo_core.py:175-184
  * (hole filling is not on the GPU path). */
 typedef struct B200sPostParams {
-    int32_t fastMode;             /* 1: only medianBlur(3) (stereo_core.py:171-173) */
+    int32_t fastMode;             /* B200S_POST_* stage selector; 1 = StereoCore fast_mode: only
+                                     medianBlur(3) (stereo_core.py:171-173) */
     int32_t maxSpeckleSize;       /* int(100 * downscale_factor) */
     int32_t maxDiff16;            /* int(max_diff * 16) (postprocess.py:30) */
     float   outlierThreshold;     /* 2.5 */
