@@ -9,6 +9,8 @@
 // with a register ring of the last BS pixel costs (horizontal box sum), and keeps XT running
 // vertical sums in registers, fed by a shared-memory ring of the last BS horizontal-sum rows.
 // Everything is packed-16x2 integer SIMD (VIADD.16x2 / VIADDMNMX.S16x2.RELU / VIMNMX.S16x2).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -78,8 +80,11 @@ struct CostArgs {
 // right-image arrays in shared memory, stored reversed in x so that increasing d walks forward
 enum { RA_VG = 0, RA_NVG, RA_LOG, RA_NHIG, RA_VR, RA_NVR, RA_LOR, RA_NHIR, RA_COUNT };
 
+#ifndef COST_MINB
+#define COST_MINB 4
+#endif
 template <int BS, int XT>
-__global__ void __launch_bounds__(128) k_cost(const CostArgs a) {
+__global__ void __launch_bounds__(128, COST_MINB) k_cost(const CostArgs a) {
     constexpr int NXI = XT + BS - 1;  // pixel-cost columns evaluated per row (with halo)
     extern __shared__ __align__(16) unsigned smem[];
     const int NT = blockDim.x;        // Dp / 2 threads, one disparity pair each
@@ -234,7 +239,13 @@ static int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
     // wide strips amortise the horizontal halo; fall back to narrow strips when the hsum ring
     // would not fit in shared memory (large D x large block size)
     size_t ring32 = (size_t)BS * 32 * (a.Dp / 2) * 4;
-    if (ring32 <= 96 * 1024) return launch_cost_t<BS, 32>(a, B, nseg, st);
+    static int xt_env = -1;
+    if (xt_env < 0) { const char* v = getenv("B200S_COST_XT"); xt_env = v ? atoi(v) : 0; }
+    int xt = xt_env ? xt_env : 16;   // measured on B200: 16-column strips + 64-row segments are fastest (tools/exp_cost.sh)
+    if (xt == 32 && ring32 > 96 * 1024) xt = 16;
+    if (xt == 16 && ring32 / 2 > 96 * 1024) xt = 8;
+    if (xt == 32) return launch_cost_t<BS, 32>(a, B, nseg, st);
+    if (xt == 16) return launch_cost_t<BS, 16>(a, B, nseg, st);
     return launch_cost_t<BS, 8>(a, B, nseg, st);
 }
 
@@ -244,7 +255,9 @@ int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uin
     a.recL = recL; a.recR = recR; a.C = C; a.Calt = Calt;
     a.H = e.H; a.W = e.W; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.minD = e.minD; a.minX1 = e.minX1;
     a.SH2 = e.SH2; a.mode = e.mode;
-    a.RS = 32;
+    static int rs_env = -1;
+    if (rs_env < 0) { const char* v = getenv("B200S_COST_RS"); rs_env = v ? atoi(v) : 0; }
+    a.RS = rs_env > 0 ? rs_env : 64;
     a.nreg = (e.H + a.RS - 1) / a.RS;
     a.sp = sp;
     int nseg = a.nreg + ((sp.alt_rows > 0 && sp.n > 1) ? sp.n - 1 : 0);
