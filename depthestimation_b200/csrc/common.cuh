@@ -92,6 +92,9 @@ int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uin
 // all path directions of the mode, accumulated into S
 int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, const uint16_t* Calt, uint16_t* S,
                  cudaStream_t st, long long* launches, int vertical_only);
+// fused vertical family (vert.cu): 0 = launched, 1 = configuration does not fit (use launch_paths)
+int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, int accumulate, cudaStream_t st,
+                       int* clusters_out);
 // fused horizontal paths + winner selection (rows.cu): C', Sv -> raw disparity
 size_t rows_ck_bytes(const Eff& e, int B);
 int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,

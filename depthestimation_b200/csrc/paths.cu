@@ -186,9 +186,23 @@ int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, c
         default: add(-1, 0); add(1, 0); add(0, -1); break;  // sgbm_3way
     }
     bool first = true;
+    // sgbm / hh: each vertical family ((x-1|x|x+1, y-1) and, for hh, (.., y+1)) runs as ONE cluster kernel
+    // (vert.cu) when the strip state fits in shared memory; otherwise one generic launch per direction
+    bool fused_down = false, fused_up = false;
+    if (vertical_only && (e.mode == B200S_MODE_SGBM || e.mode == B200S_MODE_HH)) {
+        if (launch_vert_family(e, B, C, S, +1, 0, st, nullptr) == 0) {
+            fused_down = true; first = false;
+            if (launches) (*launches)++;
+            if (e.mode == B200S_MODE_HH && launch_vert_family(e, B, C, S, -1, 1, st, nullptr) == 0) {
+                fused_up = true;
+                if (launches) (*launches)++;
+            }
+        }
+    }
     for (int k = 0; k < nd; k++) {
         a.px = dirs[k][0]; a.py = dirs[k][1];
         if (vertical_only && a.py == 0) continue;  // the two horizontal paths live in rows.cu
+        if ((fused_down && a.py == -1) || (fused_up && a.py == 1)) continue;
         a.first = first;
         first = false;
         a.quirk = 0;

@@ -25,28 +25,6 @@ struct RowArgs {
     int H, W, W1, D, Dp, P1, P2, minD, minX1, maxX1, INV, ue, d12e, mode, nck, nlines;
 };
 
-template <int NR>
-__device__ __forceinline__ void load_regs(const uint16_t* p, unsigned (&r)[NR]) {
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++) {
-        uint4 t = *(const uint4*)(p + 8 * q);
-        r[4 * q] = t.x; r[4 * q + 1] = t.y; r[4 * q + 2] = t.z; r[4 * q + 3] = t.w;
-    }
-}
-template <int NR>
-__device__ __forceinline__ void load_regs_nc(const uint16_t* p, unsigned (&r)[NR]) {
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++) {
-        uint4 t = __ldg((const uint4*)(p + 8 * q));
-        r[4 * q] = t.x; r[4 * q + 1] = t.y; r[4 * q + 2] = t.z; r[4 * q + 3] = t.w;
-    }
-}
-template <int NR>
-__device__ __forceinline__ void store_regs(uint16_t* p, const unsigned (&r)[NR]) {
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++) *(uint4*)(p + 8 * q) = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
-}
-
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 #define ROW_PD 6  // L2 prefetch distance in columns
 

@@ -9,6 +9,29 @@
 #pragma once
 #include "common.cuh"
 
+// ---- 16-byte global loads / stores of a lane's NR packed registers --------------------------------
+template <int NR>
+__device__ __forceinline__ void load_regs(const uint16_t* p, unsigned (&r)[NR]) {
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++) {
+        uint4 t = *(const uint4*)(p + 8 * q);
+        r[4 * q] = t.x; r[4 * q + 1] = t.y; r[4 * q + 2] = t.z; r[4 * q + 3] = t.w;
+    }
+}
+template <int NR>
+__device__ __forceinline__ void load_regs_nc(const uint16_t* p, unsigned (&r)[NR]) {
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++) {
+        uint4 t = __ldg((const uint4*)(p + 8 * q));
+        r[4 * q] = t.x; r[4 * q + 1] = t.y; r[4 * q + 2] = t.z; r[4 * q + 3] = t.w;
+    }
+}
+template <int NR>
+__device__ __forceinline__ void store_regs(uint16_t* p, const unsigned (&r)[NR]) {
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++) *(uint4*)(p + 8 * q) = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+}
+
 template <int LW>
 __device__ __forceinline__ unsigned group_mask() {
     if (LW == 32) return 0xffffffffu;
