@@ -224,10 +224,10 @@ def run_b200(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    B = args.batch
+    eng = StereoEngine(local, **SGBM_KW)
+    B = args.batch if args.batch > 0 else eng.preferred_batch(H, W)
     L, R = make_inputs(B)
     maps, cal = make_maps()
-    eng = StereoEngine(local, **SGBM_KW)
     eng.set_maps(maps["map1_L"], maps["map2_L"], maps["map1_R"], maps["map2_R"])
     pp = make_post_params(False, 100, 1.0, 2.5, True)            # stereo_core.py:175-184 at downscale 1.0
     dp = make_depth_params(cal["focal_length"], cal["baseline"], 0.0, eps=0, max_depth=None)
@@ -374,7 +374,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=32, help="stereo pairs per step and GPU")
+    ap.add_argument("--batch", type=int, default=0,
+                    help="stereo pairs per step and GPU (0: the engine's preferred batch for this shape)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

@@ -60,6 +60,7 @@ SYMBOLS = {
     "b200s_reset_stage_times": (C.c_int, [_H]),
     "b200s_geometry": (C.c_int, [_H, C.c_int, _IP, _IP, _IP, _IP]),
     "b200s_debug_stage": (C.c_int, [_H, C.c_int, C.c_int, _VP]),
+    "b200s_preferred_batch": (C.c_int, [_H, C.c_int, C.c_int, _IP]),
     "b200s_set_debug_flow": (C.c_int, [_H, C.c_int]),
     "b200s_launch_count": (C.c_longlong, [_H]),
     "b200s_enable_timing": (C.c_int, [_H, C.c_int]),

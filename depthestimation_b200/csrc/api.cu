@@ -168,6 +168,22 @@ int b200s_sync(B200sHandle* h) {
     return B200S_OK;
 }
 
+int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch) {
+    if (!h || !batch || H <= 0 || W <= 0) return B200S_E_INVALID;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    Eff e = make_eff(h->params, H, W);
+    *batch = 16;
+    if (e.W1 <= 0) return B200S_OK;
+    int granule = 0;
+    if (e.mode == B200S_MODE_SGBM || e.mode == B200S_MODE_HH)
+        if (launch_vert_family(e, 0, nullptr, nullptr, +1, 0, h->stream, &granule) != 0) granule = 0;
+    int cap = rows_capacity_lines(e) / H;      // frames whose rows fit one wave of the row kernel
+    if (granule <= 0) { *batch = cap > 0 ? cap : 16; return B200S_OK; }
+    int b = granule;
+    while (b + granule <= cap) b += granule;   // largest multiple of the cluster granule within one row-kernel wave
+    *batch = b;
+    return B200S_OK;
+}
 int b200s_set_debug_flow(B200sHandle* h, int on) { if (!h) return B200S_E_INVALID; h->debug_flow = on != 0; return B200S_OK; }
 int b200s_enable_timing(B200sHandle* h, int on) { if (!h) return B200S_E_INVALID; h->timing = on != 0; return B200S_OK; }
 float b200s_last_ms(const B200sHandle* h) { return h ? h->last_ms : 0.f; }

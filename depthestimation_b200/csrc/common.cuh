@@ -97,6 +97,7 @@ int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int 
                        int* clusters_out);
 // fused horizontal paths + winner selection (rows.cu): C', Sv -> raw disparity
 size_t rows_ck_bytes(const Eff& e, int B);
+int rows_capacity_lines(const Eff& e);
 int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,
                 cudaStream_t st);
 void launch_wta(const Eff& e, int B, const uint16_t* S, int16_t* raw, cudaStream_t st);

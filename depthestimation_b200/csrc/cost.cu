@@ -118,7 +118,6 @@ __global__ void __launch_bounds__(128, COST_MINB) k_cost(const CostArgs a) {
     unsigned* ring = smem;                                             // [BS][XT][NT]
     unsigned* sL = ring + BS * XT * NT;                                // [NXI][8]
     unsigned* sR = sL + NXI * 8;                                       // [2][RA_COUNT][NRW]
-    unsigned short* sRh = (unsigned short*)(sR + 2 * RA_COUNT * NRW);  // staging: [RA_COUNT][NR + 2] halves
 
     for (int i = threadIdx.x; i < BS * XT * NT; i += NT) ring[i] = 0u;
 
@@ -146,30 +145,30 @@ __global__ void __launch_bounds__(128, COST_MINB) k_cost(const CostArgs a) {
             *(uint4*)(sL + i * 8) = w0;
             *(uint4*)(sL + i * 8 + 4) = w1;
         }
-        // -- right pixels, reversed: half index i <-> right x = xr_hi - i
-        for (int i = threadIdx.x; i < NR + 2; i += NT) {
-            int xr = xr_hi - i;
-            unsigned g = 0, glo = 0, ghi = 0, rr = 0, rlo = 0, rhi = 0;
-            if (xr >= 0 && xr < a.W) {
-                uint2 r = a.recR[frame + (size_t)yc * a.W + xr];
-                g = r.x & 255u; glo = (r.x >> 8) & 255u; ghi = (r.x >> 16) & 255u;
-                rr = r.x >> 24; rlo = r.y & 255u; rhi = (r.y >> 8) & 255u;
+        // -- right pixels, reversed: half index i <-> right x = xr_hi - i. Two alignment copies of packed
+        //    pairs are written directly: copy c, word k = (half[2k + c], half[2k + c + 1]), i.e. half i sits
+        //    at u16 position i of copy 0 and at u16 position i - 1 of copy 1
+        {
+            unsigned short* c0 = (unsigned short*)sR;
+            unsigned short* c1 = (unsigned short*)(sR + RA_COUNT * NRW);
+            const int P = 2 * NRW;   // u16 per array and copy
+            for (int i = threadIdx.x; i < NR + 2; i += NT) {
+                int xr = xr_hi - i;
+                unsigned g = 0, glo = 0, ghi = 0, rr = 0, rlo = 0, rhi = 0;
+                if (xr >= 0 && xr < a.W) {
+                    uint2 r = __ldg(a.recR + frame + (size_t)yc * a.W + xr);
+                    g = r.x & 255u; glo = (r.x >> 8) & 255u; ghi = (r.x >> 16) & 255u;
+                    rr = r.x >> 24; rlo = r.y & 255u; rhi = (r.y >> 8) & 255u;
+                }
+                const unsigned short v[RA_COUNT] = {(unsigned short)g, (unsigned short)(0u - g), (unsigned short)glo,
+                                                    (unsigned short)(0u - ghi), (unsigned short)rr, (unsigned short)(0u - rr),
+                                                    (unsigned short)rlo, (unsigned short)(0u - rhi)};
+#pragma unroll
+                for (int arr = 0; arr < RA_COUNT; arr++) {
+                    if (i < P) c0[arr * P + i] = v[arr];
+                    if (i >= 1 && i - 1 < P) c1[arr * P + i - 1] = v[arr];
+                }
             }
-            const int P = NR + 2;
-            sRh[RA_VG * P + i] = (unsigned short)g;    sRh[RA_NVG * P + i] = (unsigned short)(0u - g);
-            sRh[RA_LOG * P + i] = (unsigned short)glo; sRh[RA_NHIG * P + i] = (unsigned short)(0u - ghi);
-            sRh[RA_VR * P + i] = (unsigned short)rr;   sRh[RA_NVR * P + i] = (unsigned short)(0u - rr);
-            sRh[RA_LOR * P + i] = (unsigned short)rlo; sRh[RA_NHIR * P + i] = (unsigned short)(0u - rhi);
-        }
-        __syncthreads();
-        // -- two alignment copies of packed pairs: copy c word k = (half[2k + c], half[2k + c + 1])
-        for (int i = threadIdx.x; i < 2 * RA_COUNT * NRW; i += NT) {
-            int k = i % NRW, arr = (i / NRW) % RA_COUNT, c = i / (NRW * RA_COUNT);
-            int h0 = 2 * k + c;
-            const int P = NR + 2;
-            unsigned lo = (h0 < P) ? sRh[arr * P + h0] : 0u;
-            unsigned hi = (h0 + 1 < P) ? sRh[arr * P + h0 + 1] : 0u;
-            sR[i] = lo | (hi << 16);
         }
         __syncthreads();
 
@@ -225,8 +224,7 @@ static int launch_cost_t(const CostArgs& a, int B, int nseg, cudaStream_t st) {
     const int NXI = XT + BS - 1;
     const int NRmax = NXI + 2 * NT + 2;
     const int NRW = (NRmax + 1) / 2 + 1;
-    size_t smem = (size_t)BS * XT * NT * 4 + (size_t)NXI * 8 * 4 + (size_t)2 * RA_COUNT * NRW * 4 +
-                  (size_t)RA_COUNT * (NRmax + 2) * 2 + 64;
+    size_t smem = (size_t)BS * XT * NT * 4 + (size_t)NXI * 8 * 4 + (size_t)2 * RA_COUNT * NRW * 4 + 64;
     if (smem > 220 * 1024) return -1;
     cudaFuncSetAttribute(k_cost<BS, XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((a.W1 + XT - 1) / XT, nseg, B);

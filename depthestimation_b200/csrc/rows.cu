@@ -315,6 +315,30 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
     k_rows<LW, NR><<<(a.nlines + LINES - 1) / LINES, 128, smem, st>>>(a);
 }
 
+template <int LW, int NR>
+static int rows_capacity_t() {
+    constexpr int LINES = 128 / LW;
+    size_t smem = (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4);
+    cudaFuncSetAttribute(k_rows<LW, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int nb = 0, dev = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return nb * sms * LINES;
+}
+
+// image rows the row kernel keeps in flight at once (one wave); a batch of B frames is B*H rows
+int rows_capacity_lines(const Eff& e) {
+    if (e.Dp > 64) {
+        int LW = 8;
+        while (LW * 16 < e.Dp) LW *= 2;
+        return LW == 8 ? rows_capacity_t<8, 8>() : (LW == 16 ? rows_capacity_t<16, 8>() : rows_capacity_t<32, 8>());
+    }
+    int LW = 2;
+    while (LW * 8 < e.Dp) LW *= 2;
+    return LW == 2 ? rows_capacity_t<2, 4>() : (LW == 4 ? rows_capacity_t<4, 4>() : rows_capacity_t<8, 4>());
+}
+
 size_t rows_ck_bytes(const Eff& e, int B) {
     int nck = (e.W1 + ROW_K - 1) / ROW_K + 1;
     return (size_t)B * e.H * nck * e.Dp * sizeof(uint16_t);

@@ -115,6 +115,12 @@ class StereoEngine:
     def sync(self):
         self._check(self._lib.b200s_sync(self._h), "b200s_sync")
 
+    def preferred_batch(self, H: int, W: int) -> int:
+        """Frames per batch call that fill the GPU without a partial last wave (throughput hint)."""
+        b = C.c_int()
+        self._check(self._lib.b200s_preferred_batch(self._h, int(H), int(W), C.byref(b)), "b200s_preferred_batch")
+        return int(b.value)
+
     def set_debug_flow(self, on=True):
         """Generic per-direction kernels that materialise the full S volume (for the S stage tap)."""
         self._lib.b200s_set_debug_flow(self._h, int(on))

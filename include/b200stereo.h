@@ -162,6 +162,10 @@ int b200s_geometry(const B200sHandle* h, int W, int* W1, int* minX1, int* Dp, in
  * which = 0: block cost C (int16 [H][W1][D], includes +P2 like the reference's C),
  *         1: aggregate S (int16 [H][W1][D]), 2: raw disparity before median/speckle (int16 HxW). */
 int b200s_debug_stage(B200sHandle* h, int which, int b, int16_t* out);
+/* Batch size (frames per *_batch* call) that fills the GPU without a partial last wave for HxW images
+ * under the current parameters: a multiple of the number of frames the cluster kernel keeps
+ * co-resident, capped by one wave of the row kernel. A throughput hint, any B works. */
+int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch);
 /* on != 0: run the matcher with the generic one-direction-per-launch kernels that materialise the
  * full aggregate S (needed for the S tap above; slower, same results). Default off: horizontal
  * paths + winner selection are fused (rows.cu) and S holds only the vertical-family aggregate. */
