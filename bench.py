@@ -198,15 +198,26 @@ def run_reference(args):
 # GPU arm
 # ---------------------------------------------------------------------------------------------
 def algorithmic_bytes(eng, batch):
-    """int16 C and S volumes, V = H*W1*D cells per frame.
-    paths kernel (one direction per launch, generic line-scan): read C 2V + S read-modify-write 4V
-    (the first direction only writes S: 4V) -> (4V + 4*6V)/5 per launch on the 5-path sgbm.
-    whole matcher, canonical dataflow: 10 B/cell."""
+    """u16 C and S volumes, V = H*W1*D cells per frame; canonical dataflow 10 B/cell:
+    k_cost writes C (2V); k_vert (the three top-down directions fused in one launch) reads C and writes S (4V);
+    k_rows (both horizontal directions + winner selection + LR check in one launch) reads C and S (4V).
+    Each is ONE launch per step over the whole batch."""
     g = eng.geometry(W)
     V = H * g["W1"] * D
-    per_launch = (4 * V + 4 * 6 * V) / 5.0 * batch
-    matcher = 10.0 * V * batch
-    return V, per_launch, matcher
+    per_kernel = {"cost": ("k_cost<5,16> (prefiltered rows -> C)", 2.0 * V * batch),
+                  "paths": ("k_vert<16,8> (3 vertical-family directions, cluster per frame)", 4.0 * V * batch),
+                  "wta": ("k_rows<16,8> (2 horizontal directions + WTA + LR check)", 4.0 * V * batch)}
+    return V, per_kernel, 10.0 * V * batch
+
+
+def ncu_traffic(stage, batch):
+    """DRAM bytes per launch of the stage's kernel from the committed `ncu --set full` capture (profiles/), scaled
+    from the captured batch to this run's batch (traffic is proportional to the number of frames); None if absent."""
+    try:
+        t = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text())[stage]
+        return float(t["dram_bytes_per_launch"]) * batch / float(t["batch"])
+    except Exception:
+        return None
 
 
 def run_b200(args):
@@ -258,6 +269,10 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     l0 = eng.launch_count
+    # per-stage CUDA events (recorded by the library on the launching stream) run INSIDE the timed region: the
+    # roofline's launch durations are those of the timed steps themselves (cost: one host sync per step)
+    eng.enable_timing(True)
+    eng.stage_times(reset=True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(args.steps):
@@ -265,6 +280,9 @@ def run_b200(args):
     e1.record(stream)
     barrier()
     stream.synchronize()
+    stages = eng.stage_times(reset=True)
+    eng.enable_timing(False)
+    nst = args.steps
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
     launches = eng.launch_count - l0
     clocks = sampler.stop() if rank == 0 else None
@@ -273,15 +291,7 @@ def run_b200(args):
     total_ms = float(ms.item())
     fps = world * B * args.steps / (total_ms / 1e3)
 
-    # ---- per-stage device times (CUDA events on the launching stream), same workload ----------
-    eng.enable_timing(True)
-    eng.stage_times(reset=True)
-    nst = max(1, min(args.steps, 5))
-    for _ in range(nst):
-        step_dev()
-    stages = eng.stage_times(reset=True)
-    eng.enable_timing(False)
-    V, bytes_per_launch, matcher_bytes = algorithmic_bytes(eng, B)
+    V, per_kernel, matcher_bytes = algorithmic_bytes(eng, B)
     peaks = {}
     try:
         peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
@@ -289,9 +299,16 @@ def run_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    p_ms, p_n = stages["paths"]
-    path_launch_ms = p_ms / max(p_n, 1)
-    achieved = bytes_per_launch / (path_launch_ms * 1e-3) / 1e9 if path_launch_ms > 0 else 0.0
+    kern = {}
+    for st, (name, nbytes) in per_kernel.items():
+        k_ms, k_n = stages[st]
+        launch_ms = k_ms / max(k_n, 1)
+        ach = nbytes / (launch_ms * 1e-3) / 1e9 if launch_ms > 0 else 0.0
+        kern[st] = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s",
+                    "frac": ach / peak if peak else None, "traffic": ncu_traffic(st, B), "launch_ms": launch_ms,
+                    "launches_per_step": k_n / max(nst, 1), "algorithmic_bytes_per_launch": nbytes,
+                    "peak_source": peak_src}
+    dominant = max(kern, key=lambda k: stages[k][0])
     matcher_ms = sum(stages[k][0] for k in ("prefilter", "cost", "paths", "wta", "median", "speckle")) / nst
     step_ms_sum = sum(v[0] for v in stages.values()) / nst
 
@@ -351,10 +368,8 @@ def run_b200(args):
                     "api": "b200s_pipeline_batch (pinned host buffers)", "matches_device_path": same},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "k_path<16> (one direction per launch)", "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": None,
-                         "peak_source": peak_src, "launch_ms": path_launch_ms,
-                         "algorithmic_bytes_per_launch": bytes_per_launch},
+            "roofline": kern[dominant],
+            "roofline_other_kernels": {k: v for k, v in kern.items() if k != dominant},
             "roofline_matcher": {"bytes_per_cell": 10, "achieved": matcher_bytes / (matcher_ms * 1e-3) / 1e9,
                                  "frac": matcher_bytes / (matcher_ms * 1e-3) / 1e9 / peak, "ms_per_step": matcher_ms,
                                  "nominal_8TBs_frac": matcher_bytes / (matcher_ms * 1e-3) / 1e9 / 8000.0},

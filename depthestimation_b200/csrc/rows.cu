@@ -29,30 +29,42 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 #define ROW_PD 6  // L2 prefetch distance in columns
 
 // ---- A.6 steps 1-4 for one pixel whose S(., d) sits in v[] across the lane group ------------------
-template <int LW, int NR>
+template <int LW, int NR, bool PAD>
 __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigned (&pm)[NR], const RowArgs& a,
                                           const unsigned gmask, const int gl, const int gbase, const int xc,
-                                          unsigned* keys, int16_t* out, const bool valid) {
+                                          unsigned* keys, int16_t* out, const bool valid, unsigned short* stash) {
     constexpr int DPL = 2 * NR;
     unsigned w[NR];
 #pragma unroll
-    for (int j = 0; j < NR; j++) w[j] = umax2(v[j], pm[j]);
+    for (int j = 0; j < NR; j++) w[j] = PAD ? umax2(v[j], pm[j]) : v[j];
     const int d0 = 8 * (a.D / 8);
     const bool simd3 = (a.mode == B200S_MODE_SGBM_3WAY) && d0 > 0;
     const unsigned gbits = (LW == 32) ? 0xffffffffu : ((1u << LW) - 1u);
     int minS, best;
     if (!simd3) {
-        const unsigned ml = local_min2<NR>(w);
+        // binary min tree over the lane's registers; the winner's position is found by walking it down
+        unsigned t1[NR / 2 > 0 ? NR / 2 : 1], t2[NR / 4 > 0 ? NR / 4 : 1];
+#pragma unroll
+        for (int j = 0; j < NR / 2; j++) t1[j] = umin2(w[2 * j], w[2 * j + 1]);
+#pragma unroll
+        for (int j = 0; j < NR / 4; j++) t2[j] = umin2(t1[2 * j], t1[2 * j + 1]);
+        const unsigned ml = (NR == 8) ? umin2(t2[0], t2[1]) : t2[0];
         const int lm = (int)min(ml & 0xffffu, ml >> 16);
         const unsigned mg = group_min2<LW>(ml, gmask);
         minS = (int)min(mg & 0xffffu, mg >> 16);
+        auto has = [&](unsigned x) { return (int)min(x & 0xffffu, x >> 16) == minS; };
         int cand = 0;
-        if (lm == minS) {
+        {   // lowest index wins at every level
+            int j4 = 0;
+            if (NR == 8 && !has(t2[0])) j4 = 1;
+            const unsigned a0 = (NR == 8 && j4) ? t1[2] : t1[0];
+            const int j2 = 2 * j4 + (has(a0) ? 0 : 1);
+            unsigned b0 = w[0], b1 = w[1];
 #pragma unroll
-            for (int j = NR - 1; j >= 0; j--) {
-                if ((int)(w[j] >> 16) == minS) cand = 2 * j + 1;
-                if ((int)(w[j] & 0xffffu) == minS) cand = 2 * j;
-            }
+            for (int j = 1; j < NR / 2; j++) { b0 = (j2 == j) ? w[2 * j] : b0; b1 = (j2 == j) ? w[2 * j + 1] : b1; }
+            const int j1 = 2 * j2 + (has(b0) ? 0 : 1);
+            const unsigned c0 = has(b0) ? b0 : b1;
+            cand = 2 * j1 + (((int)(c0 & 0xffffu) == minS) ? 0 : 1);
         }
         const unsigned bits = (__ballot_sync(gmask, lm == minS) >> gbase) & gbits;
         const int fl = __ffs(bits) - 1;                       // lowest lane reaching the minimum
@@ -147,25 +159,36 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
         }
     }
     // ---- neighbours of the winner for the parabola fit -------------------------------------------
-    const int dm = max(best - 1, 0), dq = min(best + 1, a.Dp - 1);
-    const int Sm = __shfl_sync(gmask, elem_of<NR>(v, dm % DPL), dm / DPL, LW);
-    const int Sq = __shfl_sync(gmask, elem_of<NR>(v, dq % DPL), dq / DPL, LW);
+    // S(., d) of this pixel goes through a per-line shared-memory stash so that lane 0 can read the two
+    // neighbours of the winner by address (cheaper than a dynamic register select + shuffle)
+    __syncwarp();   // lane 0 is done with the previous pixel's stash
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++)
+        *(uint4*)(stash + (gl * DPL + 8 * q)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+    __syncwarp();
     if (reject || gl != 0 || !valid) return;
+    const int Sm = stash[max(best - 1, 0)], Sq = stash[min(best + 1, LW * DPL - 1)];
     const int x2 = xc + a.minX1 - best - a.minD;
     if (minS < 32767) {
         const unsigned nk = ((unsigned)minS << 16) | (0xffffu - (unsigned)best);
-        if (nk < keys[x2]) keys[x2] = nk;   // this row's keys are private to this lane: plain update
+        atomicMin(&keys[x2], nk);           // result unused -> RED.MIN: no round trip on the scan's critical path
     }
     int d16 = best * 16;
     if (best > 0 && best < a.D - 1) {
         const int den2 = max(Sm + Sq - 2 * minS, 1);
-        d16 += ((Sm - Sq) * 16 + den2) / (2 * den2);  // C truncating division
+        // C truncating division. |Sm - Sq| <= den2, so |quotient| <= 8.5 and a non-integer quotient is at least
+        // 2^-17 away from an integer: the correctly rounded float quotient truncates to the exact result.
+        d16 += (int)__fdiv_rn((float)((Sm - Sq) * 16 + den2), (float)(2 * den2));
     }
     out[xc + a.minX1] = (int16_t)(d16 + a.minD * 16);
 }
 
-template <int LW, int NR>
-__global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
+#ifndef ROWS_MINB
+#define ROWS_MINB 5   // <= 102 registers: 5 CTAs (20 warps) per SM; measured best of 4/5/6 on B200
+#endif
+
+template <int LW, int NR, bool PAD>
+__global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
     constexpr int LINES = 128 / LW;                 // lines per CTA
     extern __shared__ __align__(16) uint4 rsm[];    // [LINES][ROW_K][NR/4][LW] uint4: L(<-) of the current chunk
@@ -180,6 +203,7 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
     const int gbase = (threadIdx.x & 31) / LW * LW;
     const bool active = gl * DPL < a.Dp;
     uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;
+    unsigned short* stash = (unsigned short*)(rsm + (size_t)LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * LW * DPL;
 
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
@@ -198,30 +222,45 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
         for (int x = gl; x < a.W; x += LW) { keys[x] = 0xffffffffu; out[x] = (int16_t)a.INV; }
     __syncwarp();
 
-    unsigned L[NR], Cq[NR];
+    unsigned L[NR];
     unsigned m;
+    // The three scans below are unrolled by two over a pair of register buffers (CA, CB): the load of column
+    // x -+ 1 is in flight while column x is processed, and no register-to-register copies are needed.
+    unsigned CA[NR], CB[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) { CA[j] = 0u; CB[j] = 0u; }
     // ---- pass 1: <- over the row, checkpoint L at every K-th column ------------------------------
     const int nchunks = (a.W1 + ROW_K - 1) / ROW_K;
     sgm_reset<NR>(L, m);
-    unsigned Cn[NR];
-#pragma unroll
-    for (int j = 0; j < NR; j++) Cn[j] = 0u;
-    if (active && a.W1 - 1 >= ROW_K) load_regs_nc<NR>(Crow + (size_t)(a.W1 - 1) * a.Dp, Cn);
-    for (int x = a.W1 - 1; x >= ROW_K; x--) {
-#pragma unroll
-        for (int j = 0; j < NR; j++) Cq[j] = Cn[j];
-        if (active) {
-            if (x - 1 >= ROW_K) load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, Cn);
-            if (x - ROW_PD >= ROW_K) prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
+    {
+        auto step1 = [&](const int x, const unsigned (&Cc)[NR]) {
+            sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
+            if ((x % ROW_K) == 0 && active && valid) store_regs<NR>(ck + (size_t)(x / ROW_K) * a.Dp, L);
+        };
+        int x = a.W1 - 1;
+        if (active && x >= ROW_K) load_regs_nc<NR>(Crow + (size_t)x * a.Dp, CA);
+        for (; x - 1 >= ROW_K; x -= 2) {
+            if (active) {
+                load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, CB);
+                if (x - ROW_PD - 1 >= ROW_K) {
+                    prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
+                    prefetch_l2(Crow + (size_t)(x - ROW_PD - 1) * a.Dp);
+                }
+            }
+            step1(x, CA);
+            if (active && x - 2 >= ROW_K) load_regs_nc<NR>(Crow + (size_t)(x - 2) * a.Dp, CA);
+            step1(x - 1, CB);
         }
-        sgm_step<LW, NR>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
-        if ((x % ROW_K) == 0 && active && valid) store_regs<NR>(ck + (size_t)(x / ROW_K) * a.Dp, L);
+        if (x >= ROW_K) step1(x, CA);
     }
     __syncwarp();
     // ---- pass 2: chunk by chunk, left to right ------------------------------------------------------
     unsigned Lr[NR];   // L(->)
     unsigned mr;
     sgm_reset<NR>(Lr, mr);
+    unsigned SA[NR], SB[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) { SA[j] = 0u; SB[j] = 0u; }
     for (int c = 0; c < nchunks; c++) {
         const int xs = c * ROW_K, xe = min(xs + ROW_K, a.W1);
         // re-run <- inside the chunk from the checkpoint at xe (or from the border)
@@ -235,7 +274,7 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
             sgm_reset<NR>(L, m);
         }
         if (active) {
-            load_regs_nc<NR>(Crow + (size_t)(xe - 1) * a.Dp, Cn);
+            load_regs_nc<NR>(Crow + (size_t)(xe - 1) * a.Dp, CA);
             // next chunk: bring C and Sv towards L2 while this chunk is processed
             if (xe + gl < a.W1 && gl < ROW_K) {
                 prefetch_l2(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL);
@@ -246,42 +285,55 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
                 }
             }
         }
-        for (int x = xe - 1; x >= xs; x--) {
+        {
+            auto stepb = [&](const int x, const unsigned (&Cc)[NR]) {
+                sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
 #pragma unroll
-            for (int j = 0; j < NR; j++) Cq[j] = Cn[j];
-            if (active && x - 1 >= xs) load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, Cn);
-            sgm_step<LW, NR>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
-#pragma unroll
-            for (int q = 0; q < NR / 4; q++)
-                Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+                for (int q = 0; q < NR / 4; q++)
+                    Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+            };
+            int x = xe - 1;
+            for (; x - 1 >= xs; x -= 2) {
+                if (active) load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, CB);
+                stepb(x, CA);
+                if (active && x - 2 >= xs) load_regs_nc<NR>(Crow + (size_t)(x - 2) * a.Dp, CA);
+                stepb(x - 1, CB);
+            }
+            if (x >= xs) stepb(x, CA);
         }
         __syncwarp();
         // -> over the chunk, S = Sv + L(->) + L(<-), winner selection
-        unsigned Sn[NR];
-#pragma unroll
-        for (int j = 0; j < NR; j++) { Cn[j] = 0u; Sn[j] = 0u; }
         if (active) {
-            load_regs_nc<NR>(Crow + (size_t)xs * a.Dp, Cn);
-            load_regs_nc<NR>(Srow + (size_t)xs * a.Dp, Sn);
+            load_regs_nc<NR>(Crow + (size_t)xs * a.Dp, CA);
+            load_regs_nc<NR>(Srow + (size_t)xs * a.Dp, SA);
         }
-        for (int x = xs; x < xe; x++) {
-            unsigned Sq[NR];
+        {
+            auto stepf = [&](const int x, const unsigned (&Cc)[NR], unsigned (&Sc)[NR]) {
+                sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
 #pragma unroll
-            for (int j = 0; j < NR; j++) { Cq[j] = Cn[j]; Sq[j] = Sn[j]; }
-            if (active && x + 1 < xe) {
-                load_regs_nc<NR>(Crow + (size_t)(x + 1) * a.Dp, Cn);
-                load_regs_nc<NR>(Srow + (size_t)(x + 1) * a.Dp, Sn);
+                for (int q = 0; q < NR / 4; q++) {
+                    const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
+                    Sc[4 * q] = uaddmin2(uaddmin2(Sc[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
+                    Sc[4 * q + 1] = uaddmin2(uaddmin2(Sc[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);
+                    Sc[4 * q + 2] = uaddmin2(uaddmin2(Sc[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
+                    Sc[4 * q + 3] = uaddmin2(uaddmin2(Sc[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
+                }
+                wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
+            };
+            int x = xs;
+            for (; x + 1 < xe; x += 2) {
+                if (active) {
+                    load_regs_nc<NR>(Crow + (size_t)(x + 1) * a.Dp, CB);
+                    load_regs_nc<NR>(Srow + (size_t)(x + 1) * a.Dp, SB);
+                }
+                stepf(x, CA, SA);
+                if (active && x + 2 < xe) {
+                    load_regs_nc<NR>(Crow + (size_t)(x + 2) * a.Dp, CA);
+                    load_regs_nc<NR>(Srow + (size_t)(x + 2) * a.Dp, SA);
+                }
+                stepf(x + 1, CB, SB);
             }
-            sgm_step<LW, NR>(Lr, mr, Cq, pm, gmask, gl, P1P1, P2mP1, 0, d0);
-#pragma unroll
-            for (int q = 0; q < NR / 4; q++) {
-                const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
-                Sq[4 * q] = uaddmin2(uaddmin2(Sq[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
-                Sq[4 * q + 1] = uaddmin2(uaddmin2(Sq[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);
-                Sq[4 * q + 2] = uaddmin2(uaddmin2(Sq[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
-                Sq[4 * q + 3] = uaddmin2(uaddmin2(Sq[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
-            }
-            wta_pixel<LW, NR>(Sq, pm, a, gmask, gl, gbase, x, keys, out, valid);
+            if (x < xe) stepf(x, CA, SA);
         }
         __syncwarp();
     }
@@ -294,12 +346,12 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
         const int _x = x - _d, x_ = x - d_;
         bool c1 = false, c2 = false;
         if (_x >= 0 && _x < a.W) {
-            unsigned k = keys[_x];
+            unsigned k = __ldcg(&keys[_x]);   // keys are updated by RED at L2: read them there
             int v2 = (k == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (k & 0xffffu)) + a.minD);
             c1 = v2 >= a.minD && abs(v2 - _d) > a.d12e;
         }
         if (x_ >= 0 && x_ < a.W) {
-            unsigned k = keys[x_];
+            unsigned k = __ldcg(&keys[x_]);
             int v2 = (k == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (k & 0xffffu)) + a.minD);
             c2 = v2 >= a.minD && abs(v2 - d_) > a.d12e;
         }
@@ -308,20 +360,32 @@ __global__ void __launch_bounds__(128) k_rows(const RowArgs a) {
 }
 
 template <int LW, int NR>
+static size_t rows_smem() {
+    constexpr int LINES = 128 / LW;
+    return (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * LW * 2 * NR * sizeof(unsigned short);
+}
+
+template <int LW, int NR>
 static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
     constexpr int LINES = 128 / LW;
-    size_t smem = (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4);
-    cudaFuncSetAttribute(k_rows<LW, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_rows<LW, NR><<<(a.nlines + LINES - 1) / LINES, 128, smem, st>>>(a);
+    const size_t smem = rows_smem<LW, NR>();
+    const int grid = (a.nlines + LINES - 1) / LINES;
+    if (a.D == LW * 2 * NR) {   // no padded disparities anywhere: drop the pad clamps
+        cudaFuncSetAttribute(k_rows<LW, NR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_rows<LW, NR, false><<<grid, 128, smem, st>>>(a);
+    } else {
+        cudaFuncSetAttribute(k_rows<LW, NR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_rows<LW, NR, true><<<grid, 128, smem, st>>>(a);
+    }
 }
 
 template <int LW, int NR>
 static int rows_capacity_t() {
     constexpr int LINES = 128 / LW;
-    size_t smem = (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4);
-    cudaFuncSetAttribute(k_rows<LW, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = rows_smem<LW, NR>();
+    cudaFuncSetAttribute(k_rows<LW, NR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0, dev = 0, sms = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     return nb * sms * LINES;

@@ -66,7 +66,8 @@ __device__ __forceinline__ void make_padmask(unsigned (&pm)[NR], int gl, int D) 
 
 // quirk: sgbm_3way D%8 tail artefact (A.7): 0 none, 1 "d-1 neighbour of d0 comes from the
 // already-updated current column", 2 "d-1 neighbour of d0 is ignored". d0 = 8*floor(D/8).
-template <int LW, int NR>
+// PAD = false: every lane of the group holds only real disparities (D == LW * 2 * NR), the pad clamp is dropped.
+template <int LW, int NR, bool PAD = true>
 __device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const unsigned (&Cq)[NR],
                                          const unsigned (&pm)[NR], const unsigned gmask, const int gl,
                                          const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
@@ -83,9 +84,9 @@ __device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const u
         unsigned cn = shift_pair(L[j], j == NR - 1 ? dn : L[j + 1]);       // (L[d+1], L[d+2])
         unsigned tt = umin3_2(bq, cn, dmp);
         tt = uaddmin2(tt, P1P1, L[j]);
-        Ln[j] = umax2(Cq[j] + tt - mm, pm[j]);
+        Ln[j] = PAD ? umax2(Cq[j] + tt - mm, pm[j]) : (Cq[j] + tt - mm);
     }
-    if (quirk) {
+    if (PAD && quirk) {
         // d0 is a multiple of 8, so it sits in register 0 or (NR == 8) register 4 of lane d0 / (2 NR)
         const unsigned upn = __shfl_up_sync(gmask, Ln[NR - 1], 1, LW);
         const int ql = d0 / (2 * NR), jq = (d0 % (2 * NR)) / 2;

@@ -47,7 +47,7 @@ __device__ __forceinline__ void sts_regs(uint4* p, int LW, const unsigned (&r)[N
 }
 
 // shared-memory column layout: [NR/4][LW] uint4 (16-byte chunk q of lane gl at q*LW + gl): conflict-free
-template <int LW, int NR>
+template <int LW, int NR, bool PAD>
 __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
     constexpr int DPL = 2 * NR;
     constexpr int G = VERT_THREADS / LW;      // column groups per CTA
@@ -125,9 +125,9 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
                 else { lds_regs<NR>(Bp + (size_t)(ic + 1) * COLQ + gl, LW, LB); mb = mBp[ic + 1]; }
                 if (t == 0) sgm_reset<NR>(LU, mu);
                 else { lds_regs<NR>(U + (size_t)ic * COLQ + gl, LW, LU); mu = mU[ic]; }
-                sgm_step<LW, NR>(LA, ma, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
-                sgm_step<LW, NR>(LB, mb, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
-                sgm_step<LW, NR>(LU, mu, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
+                sgm_step<LW, NR, PAD>(LA, ma, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
+                sgm_step<LW, NR, PAD>(LB, mb, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
+                sgm_step<LW, NR, PAD>(LU, mu, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
                 // C of the next row for this column slot: a whole row of work hides the latency
                 if (active && t + 1 < a.H)
                     load_regs_nc<NR>(a.C + frame + ((size_t)yn * a.W1 + x) * a.Dp + gl * DPL, Cb[k]);
@@ -197,7 +197,7 @@ static bool plan_vert(const Eff& e, VertPlan& best) {
         cudaLaunchAttribute attr[1];
         cudaLaunchConfig_t cfg = vert_cfg<LW, NR>(CS, 1, smem, 0, attr);
         int ncl = 0;
-        if (cudaOccupancyMaxActiveClusters(&ncl, k_vert<LW, NR>, &cfg) != cudaSuccess) { cudaGetLastError(); continue; }
+        if (cudaOccupancyMaxActiveClusters(&ncl, k_vert<LW, NR, true>, &cfg) != cudaSuccess) { cudaGetLastError(); continue; }
         if (ncl <= 0) continue;
         double score = (double)ncl * e.W1 / ((double)KIT * G);     // useful column slots in flight
         if (score > best_score) { best_score = score; best.CS = CS; best.NC = NC; best.smem = smem; best.clusters = ncl; }
@@ -210,8 +210,10 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
                          int* clusters_out) {
     static bool configured = false;
     if (!configured) {
-        if (cudaFuncSetAttribute(k_vert<LW, NR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return 1; }
-        if (cudaFuncSetAttribute(k_vert<LW, NR>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 1; }
+        if (cudaFuncSetAttribute(k_vert<LW, NR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return 1; }
+        if (cudaFuncSetAttribute(k_vert<LW, NR, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 1; }
+        if (cudaFuncSetAttribute(k_vert<LW, NR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return 1; }
+        if (cudaFuncSetAttribute(k_vert<LW, NR, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 1; }
         configured = true;
     }
     // the plan depends on (W1, Dp) only; cache the last one
@@ -230,7 +232,9 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     a.NC = cached.NC; a.CS = cached.CS; a.dy = dy; a.accumulate = accumulate;
     cudaLaunchAttribute attr[1];
     cudaLaunchConfig_t cfg = vert_cfg<LW, NR>(cached.CS, B, cached.smem, st, attr);
-    if (cudaLaunchKernelEx(&cfg, k_vert<LW, NR>, a) != cudaSuccess) { cudaGetLastError(); return 1; }
+    cudaError_t le = (e.D == LW * 2 * NR) ? cudaLaunchKernelEx(&cfg, k_vert<LW, NR, false>, a)
+                                          : cudaLaunchKernelEx(&cfg, k_vert<LW, NR, true>, a);
+    if (le != cudaSuccess) { cudaGetLastError(); return 1; }
     return 0;
 }
 
