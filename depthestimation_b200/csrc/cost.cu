@@ -83,13 +83,77 @@ enum { RA_VG = 0, RA_NVG, RA_LOG, RA_NHIG, RA_VR, RA_NVR, RA_LOR, RA_NHIR, RA_CO
 #ifndef COST_MINB
 #define COST_MINB 4
 #endif
-template <int BS, int XT>
-__global__ void __launch_bounds__(128, COST_MINB) k_cost(const CostArgs a) {
-    constexpr int NXI = XT + BS - 1;  // pixel-cost columns evaluated per row (with halo)
+#ifndef COST_XT
+#define COST_XT 16          // cost columns per strip; measured on B200: 16 beats 8 and 32 (tools/exp_cost.sh)
+#endif
+
+// Compile-time geometry of one CTA. NTS = stride of the per-thread shared-memory arrays (power of two >= Dp / 2);
+// every shared-memory and (when Dp / 2 == NTS) global offset inside the slide loop is then an immediate.
+template <int BS, int NTS>
+struct CostCfg {
+    static constexpr int XT = COST_XT;
+    static constexpr int NXI = XT + BS - 1;                              // pixel-cost columns per row (with halo)
+    static constexpr int RW = (((NXI + 2 * NTS + 3) / 2 + 1) + 1) & ~1;  // words per right array and alignment copy
+    static constexpr int RING = BS * XT * NTS;                           // [BS][XT][NTS] horizontal sums
+    static constexpr size_t SMEM = (size_t)(RING + NXI * 8 + 2 * RA_COUNT * RW) * 4;
+};
+
+// One source row of the strip: pixel cost -> horizontal box sum -> vertical running sum V[].
+// INTERIOR: no column of the strip (halo included) is clamped, so the reversed right index of column i is the
+// constant NXI - 1 - i.
+template <int BS, int NTS, bool INTERIOR>
+__device__ __forceinline__ void cost_row(const unsigned* __restrict__ sL, const unsigned* __restrict__ sRd,
+                                         unsigned* __restrict__ ringd, unsigned (&V)[COST_XT], const int xa,
+                                         const int W1, const int minX1, const int x_max) {
+    using G = CostCfg<BS, NTS>;
+    unsigned pr[BS];
+#pragma unroll
+    for (int j = 0; j < BS; j++) pr[j] = 0u;
+    unsigned hs = 0u;
+#pragma unroll
+    for (int i = 0; i < G::NXI; i++) {
+        int e;
+        if (INTERIOR) {
+            e = G::NXI - 1 - i;
+        } else {
+            const int xc = min(max(xa - BS / 2 + i, 0), W1 - 1);
+            e = x_max - (xc + minX1);                                 // uniform
+        }
+        const unsigned* base = sRd + (e & 1) * (RA_COUNT * G::RW) + (e >> 1);
+        const uint4 l0 = *(const uint4*)(sL + i * 8);                 // {u, -u, lo1, -hi1} gradient channel
+        const uint4 l1 = *(const uint4*)(sL + i * 8 + 4);             // raw channel
+        const unsigned vg = base[RA_VG * G::RW], nvg = base[RA_NVG * G::RW], log2_ = base[RA_LOG * G::RW],
+                       nhig = base[RA_NHIG * G::RW];
+        const unsigned vr = base[RA_VR * G::RW], nvr = base[RA_NVR * G::RW], lor = base[RA_LOR * G::RW],
+                       nhir = base[RA_NHIR * G::RW];
+        // c0 = max(0, u - hi2, lo2 - u); c1 = max(0, v - hi1, lo1 - v); cost = min(c0, c1)
+        unsigned c0 = __viaddmax_s16x2_relu(nhig, l0.x, __vadd2(log2_, l0.y));
+        unsigned c1 = __viaddmax_s16x2_relu(vg, l0.w, __vadd2(nvg, l0.z));
+        const unsigned cg = __vmins2(c0, c1);
+        c0 = __viaddmax_s16x2_relu(nhir, l1.x, __vadd2(lor, l1.y));
+        c1 = __viaddmax_s16x2_relu(vr, l1.w, __vadd2(nvr, l1.z));
+        const unsigned cr = (__vmins2(c0, c1) >> 2) & 0x3fff3fffu;
+        const unsigned pix = cg + cr;
+        hs = hs + pix - pr[i % BS];
+        pr[i % BS] = pix;
+        if (i >= BS - 1) {
+            const int xo = i - (BS - 1);
+            unsigned* rp = ringd + xo * NTS;
+            const unsigned old = *rp;
+            *rp = hs;
+            V[xo] = V[xo] + hs - old;
+        }
+    }
+}
+
+template <int BS, int NTS, bool FULL>
+__global__ void __launch_bounds__(NTS, (COST_MINB * 128 / NTS > 32 ? 32 : COST_MINB * 128 / NTS)) k_cost(const CostArgs a) {
+    using G = CostCfg<BS, NTS>;
+    constexpr int XT = G::XT, NXI = G::NXI, RW = G::RW;
     extern __shared__ __align__(16) unsigned smem[];
-    const int NT = blockDim.x;        // Dp / 2 threads, one disparity pair each
+    const int NT = FULL ? NTS : (int)blockDim.x;   // Dp / 2 threads, one disparity pair each
     const int dp = threadIdx.x;
-    const int xa = blockIdx.x * XT;   // first cost column of the strip
+    const int xa = blockIdx.x * XT;                // first cost column of the strip
     const int b = blockIdx.z;
 
     // ---- which rows does this CTA produce? -------------------------------------------------
@@ -114,12 +178,12 @@ __global__ void __launch_bounds__(128, COST_MINB) k_cost(const CostArgs a) {
     const int xc_max = min(max(xa + XT - 1 + BS / 2, 0), a.W1 - 1);
     const int x_min = xc_min + a.minX1, x_max = xc_max + a.minX1;      // left-image columns touched
     const int NR = (x_max - x_min) + 2 * NT + 2;                      // right-image samples (reversed)
-    const int NRW = (NR + 1) / 2 + 1;                                  // words per alignment copy
-    unsigned* ring = smem;                                             // [BS][XT][NT]
-    unsigned* sL = ring + BS * XT * NT;                                // [NXI][8]
-    unsigned* sR = sL + NXI * 8;                                       // [2][RA_COUNT][NRW]
+    const bool interior = (xa - BS / 2 >= 0) && (xa + XT - 1 + BS / 2 <= a.W1 - 1);
+    unsigned* ring = smem;                                             // [BS][XT][NTS]
+    unsigned* sL = ring + G::RING;                                     // [NXI][8]
+    unsigned* sR = sL + NXI * 8;                                       // [2][RA_COUNT][RW]
 
-    for (int i = threadIdx.x; i < BS * XT * NT; i += NT) ring[i] = 0u;
+    for (int i = threadIdx.x; i < G::RING; i += NT) ring[i] = 0u;
 
     unsigned V[XT];
 #pragma unroll
@@ -128,10 +192,11 @@ __global__ void __launch_bounds__(128, COST_MINB) k_cost(const CostArgs a) {
     const size_t frame = (size_t)b * a.H * a.W;
     const int xr_hi = x_max - a.minD;  // right x for d index 0 at the right-most left pixel
     const int s_begin = y0 - a.SH2, s_end = y1 - 1 + a.SH2;
+    const int ostride = FULL ? NTS : NT;                               // u32 words between cost columns
+    int slot = 0;
 
     for (int s = s_begin; s <= s_end; s++) {
         const int yc = min(max(s, ylo), a.H - 1);
-        const int slot = (s - s_begin) % BS;
         __syncthreads();  // previous row's readers are done with sL / sR
         // -- left pixels: replicated pairs {u, -u, lo1, -hi1} for g and r, indexed by halo column
         for (int i = threadIdx.x; i < NXI; i += NT) {
@@ -146,105 +211,81 @@ __global__ void __launch_bounds__(128, COST_MINB) k_cost(const CostArgs a) {
             *(uint4*)(sL + i * 8 + 4) = w1;
         }
         // -- right pixels, reversed: half index i <-> right x = xr_hi - i. Two alignment copies of packed
-        //    pairs are written directly: copy c, word k = (half[2k + c], half[2k + c + 1]), i.e. half i sits
-        //    at u16 position i of copy 0 and at u16 position i - 1 of copy 1
+        //    pairs: copy c, word k = (half[2k + c], half[2k + c + 1]). A thread owns the even half 2k and the
+        //    odd half 2k + 1: it writes word k of copy 0 whole, and one 16-bit half of words k and k - 1 ... of copy 1
         {
-            unsigned short* c0 = (unsigned short*)sR;
-            unsigned short* c1 = (unsigned short*)(sR + RA_COUNT * NRW);
-            const int P = 2 * NRW;   // u16 per array and copy
-            for (int i = threadIdx.x; i < NR + 2; i += NT) {
-                int xr = xr_hi - i;
-                unsigned g = 0, glo = 0, ghi = 0, rr = 0, rlo = 0, rhi = 0;
-                if (xr >= 0 && xr < a.W) {
-                    uint2 r = __ldg(a.recR + frame + (size_t)yc * a.W + xr);
-                    g = r.x & 255u; glo = (r.x >> 8) & 255u; ghi = (r.x >> 16) & 255u;
-                    rr = r.x >> 24; rlo = r.y & 255u; rhi = (r.y >> 8) & 255u;
+            unsigned short* c1 = (unsigned short*)(sR + RA_COUNT * RW);
+            for (int k = threadIdx.x; 2 * k < NR + 2; k += NT) {
+                unsigned v0[RA_COUNT], v1[RA_COUNT];
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    const int xr = xr_hi - (2 * k + q);
+                    unsigned g = 0, glo = 0, ghi = 0, rr = 0, rlo = 0, rhi = 0;
+                    if (xr >= 0 && xr < a.W) {
+                        uint2 r = __ldg(a.recR + frame + (size_t)yc * a.W + xr);
+                        g = r.x & 255u; glo = (r.x >> 8) & 255u; ghi = (r.x >> 16) & 255u;
+                        rr = r.x >> 24; rlo = r.y & 255u; rhi = (r.y >> 8) & 255u;
+                    }
+                    unsigned* v = q ? v1 : v0;
+                    v[RA_VG] = g; v[RA_NVG] = (0u - g) & 0xffffu; v[RA_LOG] = glo; v[RA_NHIG] = (0u - ghi) & 0xffffu;
+                    v[RA_VR] = rr; v[RA_NVR] = (0u - rr) & 0xffffu; v[RA_LOR] = rlo; v[RA_NHIR] = (0u - rhi) & 0xffffu;
                 }
-                const unsigned short v[RA_COUNT] = {(unsigned short)g, (unsigned short)(0u - g), (unsigned short)glo,
-                                                    (unsigned short)(0u - ghi), (unsigned short)rr, (unsigned short)(0u - rr),
-                                                    (unsigned short)rlo, (unsigned short)(0u - rhi)};
 #pragma unroll
                 for (int arr = 0; arr < RA_COUNT; arr++) {
-                    if (i < P) c0[arr * P + i] = v[arr];
-                    if (i >= 1 && i - 1 < P) c1[arr * P + i - 1] = v[arr];
+                    sR[arr * RW + k] = v0[arr] | (v1[arr] << 16);                    // copy 0, word k
+                    c1[arr * 2 * RW + 2 * k] = (unsigned short)v1[arr];              // copy 1, word k, low half
+                    if (k > 0) c1[arr * 2 * RW + 2 * k - 1] = (unsigned short)v0[arr]; // copy 1, word k - 1, high half
                 }
             }
         }
         __syncthreads();
 
-        // -- slide along the strip: pixel cost -> horizontal box sum -> vertical running sum
-        unsigned pr[BS];
-#pragma unroll
-        for (int j = 0; j < BS; j++) pr[j] = 0u;
-        unsigned hs = 0u;
-#pragma unroll
-        for (int i = 0; i < NXI; i++) {
-            const int xc = min(max(xa - BS / 2 + i, 0), a.W1 - 1);
-            const int e = x_max - (xc + a.minX1);            // uniform
-            const unsigned* base = sR + (e & 1) * RA_COUNT * NRW + (e >> 1) + dp;
-            const uint4 l0 = *(const uint4*)(sL + i * 8);     // {u, -u, lo1, -hi1} gradient channel
-            const uint4 l1 = *(const uint4*)(sL + i * 8 + 4); // raw channel
-            unsigned vg = base[RA_VG * NRW], nvg = base[RA_NVG * NRW], log2_ = base[RA_LOG * NRW],
-                     nhig = base[RA_NHIG * NRW];
-            unsigned vr = base[RA_VR * NRW], nvr = base[RA_NVR * NRW], lor = base[RA_LOR * NRW],
-                     nhir = base[RA_NHIR * NRW];
-            // c0 = max(0, u - hi2, lo2 - u); c1 = max(0, v - hi1, lo1 - v); cost = min(c0, c1)
-            unsigned c0 = __viaddmax_s16x2_relu(nhig, l0.x, __vadd2(log2_, l0.y));
-            unsigned c1 = __viaddmax_s16x2_relu(vg, l0.w, __vadd2(nvg, l0.z));
-            unsigned cg = __vmins2(c0, c1);
-            c0 = __viaddmax_s16x2_relu(nhir, l1.x, __vadd2(lor, l1.y));
-            c1 = __viaddmax_s16x2_relu(vr, l1.w, __vadd2(nvr, l1.z));
-            unsigned cr = (__vmins2(c0, c1) >> 2) & 0x3fff3fffu;
-            unsigned pix = cg + cr;
-            hs = hs + pix - pr[i % BS];
-            pr[i % BS] = pix;
-            if (i >= BS - 1) {
-                const int xo = i - (BS - 1);
-                unsigned* rp = ring + (slot * XT + xo) * NT + dp;
-                unsigned old = *rp;
-                *rp = hs;
-                V[xo] = V[xo] + hs - old;
-            }
-        }
+        // -- slide along the strip
+        unsigned* ringd = ring + slot * (XT * NTS) + dp;
+        if (interior) cost_row<BS, NTS, true>(sL, sR + dp, ringd, V, xa, a.W1, a.minX1, x_max);
+        else cost_row<BS, NTS, false>(sL, sR + dp, ringd, V, xa, a.W1, a.minX1, x_max);
+        slot = (slot + 1 == BS) ? 0 : slot + 1;
+
         // -- emit the output row whose window just completed
         if (s - s_begin >= BS - 1) {
             const int y = s - a.SH2;
             const bool flat = (a.mode == B200S_MODE_HH4) && (y > 0) && (y + a.SH2 >= a.H);
             unsigned* orow = (unsigned*)(out + ((size_t)y * a.W1 + xa) * a.Dp) + dp;
+            if (interior && !flat) {
 #pragma unroll
-            for (int xo = 0; xo < XT; xo++)
-                if (xa + xo < a.W1) orow[(size_t)xo * (a.Dp / 2)] = flat ? 0u : V[xo];
+                for (int xo = 0; xo < XT; xo++) orow[xo * ostride] = V[xo];
+            } else {
+#pragma unroll
+                for (int xo = 0; xo < XT; xo++)
+                    if (xa + xo < a.W1) orow[xo * ostride] = flat ? 0u : V[xo];
+            }
         }
     }
 }
 
-template <int BS, int XT>
+template <int BS, int NTS>
 static int launch_cost_t(const CostArgs& a, int B, int nseg, cudaStream_t st) {
+    using G = CostCfg<BS, NTS>;
     const int NT = a.Dp / 2;
-    const int NXI = XT + BS - 1;
-    const int NRmax = NXI + 2 * NT + 2;
-    const int NRW = (NRmax + 1) / 2 + 1;
-    size_t smem = (size_t)BS * XT * NT * 4 + (size_t)NXI * 8 * 4 + (size_t)2 * RA_COUNT * NRW * 4 + 64;
-    if (smem > 220 * 1024) return -1;
-    cudaFuncSetAttribute(k_cost<BS, XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    dim3 grid((a.W1 + XT - 1) / XT, nseg, B);
-    k_cost<BS, XT><<<grid, NT, smem, st>>>(a);
+    if (G::SMEM > 220 * 1024) return -1;
+    dim3 grid((a.W1 + G::XT - 1) / G::XT, nseg, B);
+    if (NT == NTS) {
+        cudaFuncSetAttribute(k_cost<BS, NTS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+        k_cost<BS, NTS, true><<<grid, NT, G::SMEM, st>>>(a);
+    } else {
+        cudaFuncSetAttribute(k_cost<BS, NTS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
+        k_cost<BS, NTS, false><<<grid, NT, G::SMEM, st>>>(a);
+    }
     return 0;
 }
 
 template <int BS>
 static int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
-    // wide strips amortise the horizontal halo; fall back to narrow strips when the hsum ring
-    // would not fit in shared memory (large D x large block size)
-    size_t ring32 = (size_t)BS * 32 * (a.Dp / 2) * 4;
-    static int xt_env = -1;
-    if (xt_env < 0) { const char* v = getenv("B200S_COST_XT"); xt_env = v ? atoi(v) : 0; }
-    int xt = xt_env ? xt_env : 16;   // measured on B200: 16-column strips + 64-row segments are fastest (tools/exp_cost.sh)
-    if (xt == 32 && ring32 > 96 * 1024) xt = 16;
-    if (xt == 16 && ring32 / 2 > 96 * 1024) xt = 8;
-    if (xt == 32) return launch_cost_t<BS, 32>(a, B, nseg, st);
-    if (xt == 16) return launch_cost_t<BS, 16>(a, B, nseg, st);
-    return launch_cost_t<BS, 8>(a, B, nseg, st);
+    const int NT = a.Dp / 2;
+    if (NT <= 16) return launch_cost_t<BS, 16>(a, B, nseg, st);
+    if (NT <= 32) return launch_cost_t<BS, 32>(a, B, nseg, st);
+    if (NT <= 64) return launch_cost_t<BS, 64>(a, B, nseg, st);
+    return launch_cost_t<BS, 128>(a, B, nseg, st);
 }
 
 int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uint2* recR, int B, uint16_t* C,
