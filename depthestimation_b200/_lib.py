@@ -3,6 +3,7 @@ shared library is missing this raises, and every compute call fails without a CU
 from __future__ import annotations
 
 import ctypes as C
+import os
 import subprocess
 from pathlib import Path
 
@@ -85,11 +86,12 @@ def load() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not LIB_PATH.exists():
+    path = Path(os.environ.get("B200S_LIB", LIB_PATH))   # B200S_LIB: a tuning build of the same engine (tools/)
+    if not path.exists():
         raise RuntimeError(
-            f"{LIB_PATH} not found: build the CUDA engine first (python -c 'import __graft_entry__ as g; "
+            f"{path} not found: build the CUDA engine first (python -c 'import __graft_entry__ as g; "
             f"g.build()' or make -C {CSRC}). There is no CPU fallback.")
-    lib = C.CDLL(str(LIB_PATH))
+    lib = C.CDLL(str(path))
     for name, (res, args) in SYMBOLS.items():
         fn = getattr(lib, name)  # AttributeError if the header and the library disagree
         fn.restype = res

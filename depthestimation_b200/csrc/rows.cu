@@ -14,7 +14,9 @@
 // 14 B/cell of two read-modify-write passes plus a selection pass.
 #include "sgm_step.cuh"
 
+#ifndef ROW_K
 #define ROW_K 8  // columns per chunk
+#endif
 
 struct RowArgs {
     const uint16_t* C;
@@ -26,7 +28,41 @@ struct RowArgs {
 };
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#ifndef ROW_PD
 #define ROW_PD 6  // L2 prefetch distance in columns
+#endif
+
+// L2 residency hints. The row kernel touches a chunk of C twice within a few microseconds (reverse re-scan, then
+// forward scan) while ~6000 lines stream 40+ MB of other data through L2 in between: the chunk is fetched
+// evict_last, everything that is used for the last time is read evict_first.
+#ifndef ROWS_HINTS
+#define ROWS_HINTS 1
+#endif
+__device__ __forceinline__ uint64_t l2_policy_first() {
+    uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_last() {
+    uint64_t p; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+__device__ __forceinline__ void prefetch_l2_keep(const void* p) {
+#if ROWS_HINTS
+    asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(p));
+#else
+    prefetch_l2(p);
+#endif
+}
+template <int NR>
+__device__ __forceinline__ void load_regs_pol(const uint16_t* p, unsigned (&r)[NR], const uint64_t pol) {
+#if ROWS_HINTS
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++)
+        asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+                     : "=r"(r[4 * q]), "=r"(r[4 * q + 1]), "=r"(r[4 * q + 2]), "=r"(r[4 * q + 3])
+                     : "l"(p + 8 * q), "l"(pol));
+#else
+    load_regs_nc<NR>(p, r);
+#endif
+}
 
 // ---- A.6 steps 1-4 for one pixel whose S(., d) sits in v[] across the lane group ------------------
 template <int LW, int NR, bool PAD>
@@ -230,6 +266,7 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
 #pragma unroll
     for (int j = 0; j < NR; j++) { CA[j] = 0u; CB[j] = 0u; }
     // ---- pass 1: <- over the row, checkpoint L at every K-th column ------------------------------
+    const uint64_t pol_first = l2_policy_first(), pol_last = l2_policy_last();
     const int nchunks = (a.W1 + ROW_K - 1) / ROW_K;
     sgm_reset<NR>(L, m);
     {
@@ -238,17 +275,17 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             if ((x % ROW_K) == 0 && active && valid) store_regs<NR>(ck + (size_t)(x / ROW_K) * a.Dp, L);
         };
         int x = a.W1 - 1;
-        if (active && x >= ROW_K) load_regs_nc<NR>(Crow + (size_t)x * a.Dp, CA);
+        if (active && x >= ROW_K) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_first);
         for (; x - 1 >= ROW_K; x -= 2) {
             if (active) {
-                load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, CB);
+                load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_first);
                 if (x - ROW_PD - 1 >= ROW_K) {
                     prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
                     prefetch_l2(Crow + (size_t)(x - ROW_PD - 1) * a.Dp);
                 }
             }
             step1(x, CA);
-            if (active && x - 2 >= ROW_K) load_regs_nc<NR>(Crow + (size_t)(x - 2) * a.Dp, CA);
+            if (active && x - 2 >= ROW_K) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_first);
             step1(x - 1, CB);
         }
         if (x >= ROW_K) step1(x, CA);
@@ -274,13 +311,13 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             sgm_reset<NR>(L, m);
         }
         if (active) {
-            load_regs_nc<NR>(Crow + (size_t)(xe - 1) * a.Dp, CA);
+            load_regs_pol<NR>(Crow + (size_t)(xe - 1) * a.Dp, CA, pol_last);
             // next chunk: bring C and Sv towards L2 while this chunk is processed
             if (xe + gl < a.W1 && gl < ROW_K) {
-                prefetch_l2(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL);
+                prefetch_l2_keep(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL);
                 prefetch_l2(Srow + (size_t)(xe + gl) * a.Dp - gl * DPL);
                 if (a.Dp > 64) {
-                    prefetch_l2(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL + 64);
+                    prefetch_l2_keep(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL + 64);
                     prefetch_l2(Srow + (size_t)(xe + gl) * a.Dp - gl * DPL + 64);
                 }
             }
@@ -294,9 +331,9 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             };
             int x = xe - 1;
             for (; x - 1 >= xs; x -= 2) {
-                if (active) load_regs_nc<NR>(Crow + (size_t)(x - 1) * a.Dp, CB);
+                if (active) load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_last);
                 stepb(x, CA);
-                if (active && x - 2 >= xs) load_regs_nc<NR>(Crow + (size_t)(x - 2) * a.Dp, CA);
+                if (active && x - 2 >= xs) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_last);
                 stepb(x - 1, CB);
             }
             if (x >= xs) stepb(x, CA);
@@ -304,8 +341,8 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
         __syncwarp();
         // -> over the chunk, S = Sv + L(->) + L(<-), winner selection
         if (active) {
-            load_regs_nc<NR>(Crow + (size_t)xs * a.Dp, CA);
-            load_regs_nc<NR>(Srow + (size_t)xs * a.Dp, SA);
+            load_regs_pol<NR>(Crow + (size_t)xs * a.Dp, CA, pol_first);
+            load_regs_pol<NR>(Srow + (size_t)xs * a.Dp, SA, pol_first);
         }
         {
             auto stepf = [&](const int x, const unsigned (&Cc)[NR], unsigned (&Sc)[NR]) {
@@ -323,13 +360,13 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             int x = xs;
             for (; x + 1 < xe; x += 2) {
                 if (active) {
-                    load_regs_nc<NR>(Crow + (size_t)(x + 1) * a.Dp, CB);
-                    load_regs_nc<NR>(Srow + (size_t)(x + 1) * a.Dp, SB);
+                    load_regs_pol<NR>(Crow + (size_t)(x + 1) * a.Dp, CB, pol_first);
+                    load_regs_pol<NR>(Srow + (size_t)(x + 1) * a.Dp, SB, pol_first);
                 }
                 stepf(x, CA, SA);
                 if (active && x + 2 < xe) {
-                    load_regs_nc<NR>(Crow + (size_t)(x + 2) * a.Dp, CA);
-                    load_regs_nc<NR>(Srow + (size_t)(x + 2) * a.Dp, SA);
+                    load_regs_pol<NR>(Crow + (size_t)(x + 2) * a.Dp, CA, pol_first);
+                    load_regs_pol<NR>(Srow + (size_t)(x + 2) * a.Dp, SA, pol_first);
                 }
                 stepf(x + 1, CB, SB);
             }

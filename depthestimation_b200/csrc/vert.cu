@@ -7,8 +7,13 @@
 // the previous row's L of all three directions in shared memory (ping-pong for the diagonals, in
 // place for the vertical path). The only data that crosses strips is one column of L per diagonal
 // per row: the group that computes a strip-edge column writes it straight from registers into the
-// neighbour CTA's shared memory (DSMEM, st.shared::cluster), then one cluster barrier per row.
-// No global-memory halo, no inter-CTA spin, co-scheduling guaranteed by the cluster launch.
+// neighbour CTA's shared memory with st.async (DSMEM), which also completes transaction bytes on an mbarrier in
+// the neighbour: the group that consumes the halo one row later waits on that mbarrier only. Inside a CTA one
+// __syncthreads per row orders the rows. There is NO cluster-wide barrier per row: barrier.cluster.arrive.release
+// would wait for every outstanding global store of S (measured: 40 % of all stall samples were membar waits).
+// Two halo slots per direction suffice: a CTA can only run one row ahead of its neighbour, because it needs the
+// neighbour's halo of row t to start row t + 1, and the neighbour sends that only after consuming ours of row t - 1.
+// No global-memory halo, co-scheduling guaranteed by the cluster launch.
 //
 // Replaces part of the aggregation inside cv2.StereoSGBM.compute (depthlib/stereo_core.py:231) for
 // MODE_SGBM (top-down family) and MODE_HH (top-down, then bottom-up with accumulate).
@@ -31,6 +36,32 @@ struct VertArgs {
 
 #define VERT_THREADS 512
 #define VERT_KMAX 4
+
+// ---- mbarrier / st.async helpers (sm_90+ PTX) ---------------------------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned map_cluster(unsigned addr, unsigned rank) {
+    unsigned r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
+}
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void st_async_v4(unsigned raddr, const uint4 v, unsigned rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
+                 ::"r"(raddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void st_async_b32(unsigned raddr, const unsigned v, unsigned rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];"
+                 ::"r"(raddr), "r"(v), "r"(rbar) : "memory");
+}
 
 template <int NR>
 __device__ __forceinline__ void lds_regs(const uint4* p, int LW, unsigned (&r)[NR]) {
@@ -71,11 +102,29 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
     unsigned* mA = (unsigned*)(U + (size_t)a.NC * COLQ);
     unsigned* mB = mA + 2 * (a.NC + 1);
     unsigned* mU = mB + 2 * (a.NC + 1);
+    unsigned long long* bars = (unsigned long long*)(mU + a.NC + (a.NC & 1));   // [4]: halo A slot 0/1, halo B slot 0/1
 
-    uint4* A_right = nullptr; unsigned* mA_right = nullptr;   // neighbour CTA r+1
-    uint4* B_left = nullptr;  unsigned* mB_left = nullptr;    // neighbour CTA r-1
-    if (r + 1 < a.CS) { A_right = cluster.map_shared_rank(A, r + 1); mA_right = cluster.map_shared_rank(mA, r + 1); }
-    if (r > 0) { B_left = cluster.map_shared_rank(Bd, r - 1); mB_left = cluster.map_shared_rank(mB, r - 1); }
+    const bool has_right = r + 1 < a.CS, has_left = r > 0;
+    constexpr unsigned HALO_BYTES = (unsigned)COLQ * 16u + 4u;          // one column of L plus its minimum
+    const unsigned barA = smem_u32(bars), barB = smem_u32(bars + 2);    // + 8 * slot
+    // shared::cluster addresses of the neighbours' halo slots and barriers
+    unsigned A_right = 0, mA_right = 0, barA_right = 0, B_left = 0, mB_left = 0, barB_left = 0;
+    if (has_right) {
+        A_right = map_cluster(smem_u32(A), r + 1); mA_right = map_cluster(smem_u32(mA), r + 1);
+        barA_right = map_cluster(barA, r + 1);
+    }
+    if (has_left) {
+        B_left = map_cluster(smem_u32(Bd), r - 1); mB_left = map_cluster(smem_u32(mB), r - 1);
+        barB_left = map_cluster(barB, r - 1);
+    }
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) mbar_init(smem_u32(bars + i), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // arm both slots of each direction that will receive data (rows 0 and 1 of the neighbour)
+        if (has_left && a.H > 1) { mbar_expect_tx(barA, HALO_BYTES); if (a.H > 2) mbar_expect_tx(barA + 8, HALO_BYTES); }
+        if (has_right && a.H > 1) { mbar_expect_tx(barB, HALO_BYTES); if (a.H > 2) mbar_expect_tx(barB + 8, HALO_BYTES); }
+    }
 
     const bool active = gl * DPL < a.Dp;
     unsigned pm[NR];
@@ -118,6 +167,19 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
                 const int x = x0 + ic;
                 const unsigned (&Cq)[NR] = Cb[k];
                 unsigned LA[NR], LB[NR], LU[NR], ma, mb, mu;
+                // halo of row t-1 from the neighbours: only the warps that own a strip-edge column wait
+                if (t > 0) {
+                    const unsigned ph = (unsigned)((t - 1) >> 1) & 1u;   // slot p is in its ((t-1)/2)-th use
+                    if (__any_sync(0xffffffffu, ic == 0 && has_left)) {
+                        while (!mbar_try_wait(barA + 8 * p, ph)) {}
+                        // re-arm the slot for row t+1 of the neighbour (rows H-1 are never sent)
+                        if (ic == 0 && gl == 0 && valid && t + 1 < a.H - 1) mbar_expect_tx(barA + 8 * p, HALO_BYTES);
+                    }
+                    if (__any_sync(0xffffffffu, ic == NCr - 1 && has_right)) {
+                        while (!mbar_try_wait(barB + 8 * p, ph)) {}
+                        if (ic == NCr - 1 && gl == 0 && valid && t + 1 < a.H - 1) mbar_expect_tx(barB + 8 * p, HALO_BYTES);
+                    }
+                }
                 // predecessor outside the cost domain (first row, or x-1 / x+1 off the edge): L = 0, m = 0
                 if (t == 0 || x == 0) sgm_reset<NR>(LA, ma);
                 else { lds_regs<NR>(Ap + (size_t)ic * COLQ + gl, LW, LA); ma = mAp[ic]; }
@@ -136,14 +198,24 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
                     sts_regs<NR>(Bq + (size_t)ic * COLQ + gl, LW, LB);
                     sts_regs<NR>(U + (size_t)ic * COLQ + gl, LW, LU);
                     if (gl == 0) { mAq[ic + 1] = ma; mBq[ic] = mb; mU[ic] = mu; }
-                    // strip-edge columns go straight to the neighbour CTA's halo slots (DSMEM)
-                    if (ic == NCr - 1 && A_right != nullptr) {
-                        sts_regs<NR>(A_right + (size_t)q * (a.NC + 1) * COLQ + gl, LW, LA);
-                        if (gl == 0) mA_right[q * (a.NC + 1)] = ma;
-                    }
-                    if (ic == 0 && B_left != nullptr) {
-                        sts_regs<NR>(B_left + ((size_t)q * (a.NC + 1) + a.NC) * COLQ + gl, LW, LB);
-                        if (gl == 0) mB_left[q * (a.NC + 1) + a.NC] = mb;
+                    // strip-edge columns go straight to the neighbour CTA's halo slots (DSMEM, st.async + tx bytes)
+                    if (t + 1 < a.H) {
+                        if (ic == NCr - 1 && has_right) {
+                            const unsigned dst = A_right + (unsigned)((q * (a.NC + 1)) * COLQ + gl) * 16u;
+#pragma unroll
+                            for (int c = 0; c < NR / 4; c++)
+                                st_async_v4(dst + (unsigned)(c * LW) * 16u,
+                                            make_uint4(LA[4 * c], LA[4 * c + 1], LA[4 * c + 2], LA[4 * c + 3]), barA_right + 8 * q);
+                            if (gl == 0) st_async_b32(mA_right + (unsigned)(q * (a.NC + 1)) * 4u, ma, barA_right + 8 * q);
+                        }
+                        if (ic == 0 && has_left) {
+                            const unsigned dst = B_left + (unsigned)((q * (a.NC + 1) + a.NC) * COLQ + gl) * 16u;
+#pragma unroll
+                            for (int c = 0; c < NR / 4; c++)
+                                st_async_v4(dst + (unsigned)(c * LW) * 16u,
+                                            make_uint4(LB[4 * c], LB[4 * c + 1], LB[4 * c + 2], LB[4 * c + 3]), barB_left + 8 * q);
+                            if (gl == 0) st_async_b32(mB_left + (unsigned)(q * (a.NC + 1) + a.NC) * 4u, mb, barB_left + 8 * q);
+                        }
                     }
                     if (active) {
                         uint16_t* sp = a.S + frame + ((size_t)y * a.W1 + x) * a.Dp + gl * DPL;
@@ -161,8 +233,9 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
                 }
             }
         }
-        cluster.sync();   // row t complete everywhere: halos delivered, ping-pong buffers may flip
+        __syncthreads();   // row t complete in this CTA: ping-pong buffers may flip (halos are ordered by the mbarriers)
     }
+    cluster.sync();        // nobody leaves while a neighbour could still address its shared memory
 }
 
 // ---- launcher ------------------------------------------------------------------------------------
@@ -191,7 +264,7 @@ static bool plan_vert(const Eff& e, VertPlan& best) {
     for (int CS = 1; CS <= 16; CS++) {
         int NC = (e.W1 + CS - 1) / CS;
         if ((CS - 1) * NC >= e.W1) continue;                       // last strip would be empty
-        size_t smem = ((size_t)4 * (NC + 1) + NC) * COLQ * sizeof(uint4) + ((size_t)4 * (NC + 1) + NC) * sizeof(unsigned) + 64;
+        size_t smem = ((size_t)4 * (NC + 1) + NC) * COLQ * sizeof(uint4) + ((size_t)4 * (NC + 1) + NC + 1) * sizeof(unsigned) + 4 * sizeof(unsigned long long) + 64;
         int KIT = (NC + G - 1) / G;
         if (smem > 225 * 1024 || KIT > VERT_KMAX) continue;
         cudaLaunchAttribute attr[1];
