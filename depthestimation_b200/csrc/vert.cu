@@ -20,6 +20,8 @@
 #include <cooperative_groups.h>
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "sgm_step.cuh"
 
 namespace cg = cooperative_groups;
@@ -29,6 +31,7 @@ struct VertArgs {
     uint16_t* S;
     int H, W1, D, Dp, P1, P2;
     int NC;          // columns per CTA (last CTA of the cluster may own fewer)
+    int KIT, nrec;   // column slots per thread group, shared-memory records (KIT * G + 1)
     int CS;          // cluster size = strips per frame
     int dy;          // +1: top-down (predecessor row y-1), -1: bottom-up (predecessor row y+1)
     int accumulate;  // 0: S = sum, 1: S = sat(S + sum)
@@ -63,26 +66,28 @@ __device__ __forceinline__ void st_async_b32(unsigned raddr, const unsigned v, u
                  ::"r"(raddr), "r"(v), "r"(rbar) : "memory");
 }
 
-template <int NR>
-__device__ __forceinline__ void lds_regs(const uint4* p, int LW, unsigned (&r)[NR]) {
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++) {
-        const uint4 t = p[q * LW];
-        r[4 * q] = t.x; r[4 * q + 1] = t.y; r[4 * q + 2] = t.z; r[4 * q + 3] = t.w;
-    }
-}
-template <int NR>
-__device__ __forceinline__ void sts_regs(uint4* p, int LW, const unsigned (&r)[NR]) {
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++) p[q * LW] = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
-}
+// Shared memory: one RECORD per column index 0..nrec-1, all offsets compile-time:
+//   A[2]  L of the (x-1) diagonal, ping-pong by row parity; record i holds own column i-1 (record 0 = halo from the left CTA)
+//   B[2]  L of the (x+1) diagonal, ping-pong; record i holds own column i (record NC = halo from the right CTA)
+//   U     L of the vertical path, in place; record i holds own column i
+//   m[5]  the minima of A[0], A[1], B[0], B[1], U
+// A field is [NR/4][LW] uint4 (16-byte chunk c of lane gl at c*LW + gl): conflict-free for LDS.128 / STS.128.
+// Everything starts zeroed, which IS the reset state (L = 0, m = 0) of the first row and of the predecessors
+// outside the cost domain (x-1 < 0, x+1 >= W1): those slots are never written, so no special cases remain.
+template <int LW, int NR>
+struct VertLayout {
+    static constexpr int COLQ = (NR / 4) * LW;       // uint4 per field
+    static constexpr int FLD = COLQ * 16;            // bytes per field
+    static constexpr int OFF_A = 0, OFF_B = 2 * FLD, OFF_U = 4 * FLD, OFF_M = 5 * FLD;
+    static constexpr int REC = 5 * FLD + 32;         // bytes per record
+    static constexpr int G = VERT_THREADS / LW;      // column groups per CTA
+};
 
-// shared-memory column layout: [NR/4][LW] uint4 (16-byte chunk q of lane gl at q*LW + gl): conflict-free
 template <int LW, int NR, bool PAD>
 __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
-    constexpr int DPL = 2 * NR;
-    constexpr int G = VERT_THREADS / LW;      // column groups per CTA
-    constexpr int COLQ = (NR / 4) * LW;       // uint4 per column
+    using VL = VertLayout<LW, NR>;
+    constexpr int DPL = 2 * NR, G = VL::G, FLD = VL::FLD, REC = VL::REC;
+    constexpr int OFF_A = VL::OFF_A, OFF_B = VL::OFF_B, OFF_U = VL::OFF_U, OFF_M = VL::OFF_M;
     cg::cluster_group cluster = cg::this_cluster();
     const int r = (int)cluster.block_rank();
     const int b = blockIdx.x / a.CS;
@@ -90,33 +95,21 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
     const unsigned gmask = 0xffffffffu;
     const int x0 = r * a.NC;
     const int NCr = min(a.NC, a.W1 - x0);     // >= 1 by construction of CS / NC
-    const int KIT = (a.NC + G - 1) / G;
+    const int KIT = a.KIT;
 
-    extern __shared__ __align__(16) uint4 vsm[];
-    // A[par][0..NC]  : L of the (x-1) diagonal; index c+1 = own column c, index 0 = halo from the left CTA
-    // Bd[par][0..NC] : L of the (x+1) diagonal; index c = own column c, index NC = halo from the right CTA
-    // U[0..NC-1]     : L of the vertical path, in place
-    uint4* A = vsm;
-    uint4* Bd = A + (size_t)2 * (a.NC + 1) * COLQ;
-    uint4* U = Bd + (size_t)2 * (a.NC + 1) * COLQ;
-    unsigned* mA = (unsigned*)(U + (size_t)a.NC * COLQ);
-    unsigned* mB = mA + 2 * (a.NC + 1);
-    unsigned* mU = mB + 2 * (a.NC + 1);
-    unsigned long long* bars = (unsigned long long*)(mU + a.NC + (a.NC & 1));   // [4]: halo A slot 0/1, halo B slot 0/1
+    extern __shared__ __align__(16) unsigned char vsm[];
+    unsigned long long* bars = (unsigned long long*)(vsm + (size_t)a.nrec * REC);   // [4]: halo A slot 0/1, halo B slot 0/1
+    for (int i = threadIdx.x; i < a.nrec * (REC / 16); i += VERT_THREADS) ((uint4*)vsm)[i] = make_uint4(0u, 0u, 0u, 0u);
+    unsigned char* const tb = vsm + g * REC + gl * 16;   // this thread's chunk 0 of field 0 of record g
+    unsigned char* const tm = vsm + g * REC + OFF_M;     // minima of record g
 
     const bool has_right = r + 1 < a.CS, has_left = r > 0;
-    constexpr unsigned HALO_BYTES = (unsigned)COLQ * 16u + 4u;          // one column of L plus its minimum
+    constexpr unsigned HALO_BYTES = (unsigned)FLD + 4u;                 // one column of L plus its minimum
     const unsigned barA = smem_u32(bars), barB = smem_u32(bars + 2);    // + 8 * slot
-    // shared::cluster addresses of the neighbours' halo slots and barriers
-    unsigned A_right = 0, mA_right = 0, barA_right = 0, B_left = 0, mB_left = 0, barB_left = 0;
-    if (has_right) {
-        A_right = map_cluster(smem_u32(A), r + 1); mA_right = map_cluster(smem_u32(mA), r + 1);
-        barA_right = map_cluster(barA, r + 1);
-    }
-    if (has_left) {
-        B_left = map_cluster(smem_u32(Bd), r - 1); mB_left = map_cluster(smem_u32(mB), r - 1);
-        barB_left = map_cluster(barB, r - 1);
-    }
+    // shared::cluster addresses of the neighbours' halo records and barriers
+    unsigned rec_right = 0, barA_right = 0, rec_left = 0, barB_left = 0;
+    if (has_right) { rec_right = map_cluster(smem_u32(vsm), r + 1); barA_right = map_cluster(barA, r + 1); }
+    if (has_left) { rec_left = map_cluster(smem_u32(vsm) + (unsigned)a.NC * REC, r - 1); barB_left = map_cluster(barB, r - 1); }
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int i = 0; i < 4; i++) mbar_init(smem_u32(bars + i), 1);
@@ -126,13 +119,17 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
         if (has_right && a.H > 1) { mbar_expect_tx(barB, HALO_BYTES); if (a.H > 2) mbar_expect_tx(barB + 8, HALO_BYTES); }
     }
 
-    const bool active = gl * DPL < a.Dp;
+    const bool active = PAD ? (gl * DPL < a.Dp) : true;
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
     const unsigned P1P1 = pk2((unsigned)a.P1), P2mP1 = (unsigned)(a.P2 - a.P1);
-    const size_t frame = (size_t)b * a.H * a.W1 * a.Dp;
+    const uint16_t* const Cf = a.C + (size_t)b * a.H * a.W1 * a.Dp;
+    uint16_t* const Sf = a.S + (size_t)b * a.H * a.W1 * a.Dp;
+    const unsigned rowstep = (unsigned)(a.dy * a.W1 * a.Dp);           // wraps for dy < 0; offsets are modulo 2^32
 
-    // C of the next row, one register set per column iteration (software pipeline across the row barrier)
+    // element offset (within the frame) of this thread's 16-byte chunk 0, per column slot; C of the next row is
+    // held in one register set per column slot (software pipeline across the row boundary)
+    unsigned off[VERT_KMAX];
     unsigned Cb[VERT_KMAX][NR];
     {
         const int y = (a.dy > 0) ? 0 : a.H - 1;
@@ -140,85 +137,92 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
         for (int k = 0; k < VERT_KMAX; k++) {
 #pragma unroll
             for (int j = 0; j < NR; j++) Cb[k][j] = 0u;
-            const int ic = min(k * G + g, NCr - 1);
-            if (k < KIT && active) load_regs_nc<NR>(a.C + frame + ((size_t)y * a.W1 + x0 + ic) * a.Dp + gl * DPL, Cb[k]);
+            const int ic = min(k * G + g, NCr - 1);                      // surplus groups shadow the last column
+            off[k] = (unsigned)((y * a.W1 + x0 + ic) * a.Dp + gl * DPL);
+            if (k < KIT && active) load_regs_nc<NR>(Cf + off[k], Cb[k]);
         }
     }
-    cluster.sync();   // every CTA of the cluster is running before anyone writes remote shared memory
+    __syncthreads();
+    cluster.sync();   // every CTA of the cluster is running, zeroed and armed before anyone writes remote shared memory
 
-    for (int t = 0; t < a.H; t++) {
-        const int y = (a.dy > 0) ? t : a.H - 1 - t;
-        const int yn = (a.dy > 0) ? y + 1 : y - 1;          // next row (for the prefetch)
-        const int q = t & 1, p = q ^ 1;
-        const uint4* Ap = A + (size_t)p * (a.NC + 1) * COLQ;
-        const uint4* Bp = Bd + (size_t)p * (a.NC + 1) * COLQ;
-        uint4* Aq = A + (size_t)q * (a.NC + 1) * COLQ;
-        uint4* Bq = Bd + (size_t)q * (a.NC + 1) * COLQ;
-        const unsigned* mAp = mA + p * (a.NC + 1);
-        const unsigned* mBp = mB + p * (a.NC + 1);
-        unsigned* mAq = mA + q * (a.NC + 1);
-        unsigned* mBq = mB + q * (a.NC + 1);
+    // one row; Q = parity of t (written slot), P = 1 - Q (slot of the previous row)
+    auto row = [&](auto Qc, const int t) {
+        constexpr int Q = decltype(Qc)::value, P = Q ^ 1;
 #pragma unroll
         for (int k = 0; k < VERT_KMAX; k++) {
             if (k < KIT) {
                 const int i = k * G + g;
                 const bool valid = i < NCr;
-                const int ic = valid ? i : NCr - 1;           // surplus groups shadow the last column (uniform flow)
-                const int x = x0 + ic;
+                unsigned char* const rb = tb + k * G * REC;
+                unsigned char* const rm = tm + k * G * REC;
                 const unsigned (&Cq)[NR] = Cb[k];
-                unsigned LA[NR], LB[NR], LU[NR], ma, mb, mu;
+                unsigned LA[NR], LB[NR], LU[NR];
                 // halo of row t-1 from the neighbours: only the warps that own a strip-edge column wait
                 if (t > 0) {
-                    const unsigned ph = (unsigned)((t - 1) >> 1) & 1u;   // slot p is in its ((t-1)/2)-th use
-                    if (__any_sync(0xffffffffu, ic == 0 && has_left)) {
-                        while (!mbar_try_wait(barA + 8 * p, ph)) {}
-                        // re-arm the slot for row t+1 of the neighbour (rows H-1 are never sent)
-                        if (ic == 0 && gl == 0 && valid && t + 1 < a.H - 1) mbar_expect_tx(barA + 8 * p, HALO_BYTES);
+                    const unsigned ph = (unsigned)((t - 1) >> 1) & 1u;   // slot P is in its ((t-1)/2)-th use
+                    const bool eL = (i == 0) && has_left, eR = (i == NCr - 1) && has_right;
+                    if (__any_sync(0xffffffffu, eL)) {
+                        while (!mbar_try_wait(barA + 8 * P, ph)) {}
+                        // re-arm the slot for row t+1 of the neighbour (row H-1 is never sent)
+                        if (eL && gl == 0 && t + 1 < a.H - 1) mbar_expect_tx(barA + 8 * P, HALO_BYTES);
                     }
-                    if (__any_sync(0xffffffffu, ic == NCr - 1 && has_right)) {
-                        while (!mbar_try_wait(barB + 8 * p, ph)) {}
-                        if (ic == NCr - 1 && gl == 0 && valid && t + 1 < a.H - 1) mbar_expect_tx(barB + 8 * p, HALO_BYTES);
+                    if (__any_sync(0xffffffffu, eR)) {
+                        while (!mbar_try_wait(barB + 8 * P, ph)) {}
+                        if (eR && gl == 0 && t + 1 < a.H - 1) mbar_expect_tx(barB + 8 * P, HALO_BYTES);
                     }
                 }
-                // predecessor outside the cost domain (first row, or x-1 / x+1 off the edge): L = 0, m = 0
-                if (t == 0 || x == 0) sgm_reset<NR>(LA, ma);
-                else { lds_regs<NR>(Ap + (size_t)ic * COLQ + gl, LW, LA); ma = mAp[ic]; }
-                if (t == 0 || x == a.W1 - 1) sgm_reset<NR>(LB, mb);
-                else { lds_regs<NR>(Bp + (size_t)(ic + 1) * COLQ + gl, LW, LB); mb = mBp[ic + 1]; }
-                if (t == 0) sgm_reset<NR>(LU, mu);
-                else { lds_regs<NR>(U + (size_t)ic * COLQ + gl, LW, LU); mu = mU[ic]; }
+#pragma unroll
+                for (int c = 0; c < NR / 4; c++) {
+                    const uint4 va = *(const uint4*)(rb + OFF_A + P * FLD + c * LW * 16);
+                    const uint4 vb = *(const uint4*)(rb + REC + OFF_B + P * FLD + c * LW * 16);
+                    const uint4 vu = *(const uint4*)(rb + OFF_U + c * LW * 16);
+                    LA[4 * c] = va.x; LA[4 * c + 1] = va.y; LA[4 * c + 2] = va.z; LA[4 * c + 3] = va.w;
+                    LB[4 * c] = vb.x; LB[4 * c + 1] = vb.y; LB[4 * c + 2] = vb.z; LB[4 * c + 3] = vb.w;
+                    LU[4 * c] = vu.x; LU[4 * c + 1] = vu.y; LU[4 * c + 2] = vu.z; LU[4 * c + 3] = vu.w;
+                }
+                unsigned ma = *(const unsigned*)(rm + P * 4);
+                unsigned mb = *(const unsigned*)(rm + REC + 8 + P * 4);
+                unsigned mu = *(const unsigned*)(rm + 16);
                 sgm_step<LW, NR, PAD>(LA, ma, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
                 sgm_step<LW, NR, PAD>(LB, mb, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
                 sgm_step<LW, NR, PAD>(LU, mu, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
+                const unsigned o = off[k];
+                off[k] = o + rowstep;
                 // C of the next row for this column slot: a whole row of work hides the latency
-                if (active && t + 1 < a.H)
-                    load_regs_nc<NR>(a.C + frame + ((size_t)yn * a.W1 + x) * a.Dp + gl * DPL, Cb[k]);
+                if (active && t + 1 < a.H) load_regs_nc<NR>(Cf + off[k], Cb[k]);
                 if (valid) {
-                    sts_regs<NR>(Aq + (size_t)(ic + 1) * COLQ + gl, LW, LA);
-                    sts_regs<NR>(Bq + (size_t)ic * COLQ + gl, LW, LB);
-                    sts_regs<NR>(U + (size_t)ic * COLQ + gl, LW, LU);
-                    if (gl == 0) { mAq[ic + 1] = ma; mBq[ic] = mb; mU[ic] = mu; }
-                    // strip-edge columns go straight to the neighbour CTA's halo slots (DSMEM, st.async + tx bytes)
+#pragma unroll
+                    for (int c = 0; c < NR / 4; c++) {
+                        *(uint4*)(rb + REC + OFF_A + Q * FLD + c * LW * 16) = make_uint4(LA[4 * c], LA[4 * c + 1], LA[4 * c + 2], LA[4 * c + 3]);
+                        *(uint4*)(rb + OFF_B + Q * FLD + c * LW * 16) = make_uint4(LB[4 * c], LB[4 * c + 1], LB[4 * c + 2], LB[4 * c + 3]);
+                        *(uint4*)(rb + OFF_U + c * LW * 16) = make_uint4(LU[4 * c], LU[4 * c + 1], LU[4 * c + 2], LU[4 * c + 3]);
+                    }
+                    if (gl == 0) {
+                        *(unsigned*)(rm + REC + Q * 4) = ma;
+                        *(unsigned*)(rm + 8 + Q * 4) = mb;
+                        *(unsigned*)(rm + 16) = mu;
+                    }
+                    // strip-edge columns go straight to the neighbour CTA's halo records (DSMEM, st.async + tx bytes)
                     if (t + 1 < a.H) {
-                        if (ic == NCr - 1 && has_right) {
-                            const unsigned dst = A_right + (unsigned)((q * (a.NC + 1)) * COLQ + gl) * 16u;
+                        if (i == NCr - 1 && has_right) {     // -> record 0, field A[Q] of the right neighbour
+                            const unsigned dst = rec_right + (unsigned)(OFF_A + Q * FLD + gl * 16);
 #pragma unroll
                             for (int c = 0; c < NR / 4; c++)
-                                st_async_v4(dst + (unsigned)(c * LW) * 16u,
-                                            make_uint4(LA[4 * c], LA[4 * c + 1], LA[4 * c + 2], LA[4 * c + 3]), barA_right + 8 * q);
-                            if (gl == 0) st_async_b32(mA_right + (unsigned)(q * (a.NC + 1)) * 4u, ma, barA_right + 8 * q);
+                                st_async_v4(dst + (unsigned)(c * LW * 16),
+                                            make_uint4(LA[4 * c], LA[4 * c + 1], LA[4 * c + 2], LA[4 * c + 3]), barA_right + 8 * Q);
+                            if (gl == 0) st_async_b32(rec_right + (unsigned)(OFF_M + Q * 4), ma, barA_right + 8 * Q);
                         }
-                        if (ic == 0 && has_left) {
-                            const unsigned dst = B_left + (unsigned)((q * (a.NC + 1) + a.NC) * COLQ + gl) * 16u;
+                        if (i == 0 && has_left) {            // -> record NC, field B[Q] of the left neighbour
+                            const unsigned dst = rec_left + (unsigned)(OFF_B + Q * FLD + gl * 16);
 #pragma unroll
                             for (int c = 0; c < NR / 4; c++)
-                                st_async_v4(dst + (unsigned)(c * LW) * 16u,
-                                            make_uint4(LB[4 * c], LB[4 * c + 1], LB[4 * c + 2], LB[4 * c + 3]), barB_left + 8 * q);
-                            if (gl == 0) st_async_b32(mB_left + (unsigned)(q * (a.NC + 1) + a.NC) * 4u, mb, barB_left + 8 * q);
+                                st_async_v4(dst + (unsigned)(c * LW * 16),
+                                            make_uint4(LB[4 * c], LB[4 * c + 1], LB[4 * c + 2], LB[4 * c + 3]), barB_left + 8 * Q);
+                            if (gl == 0) st_async_b32(rec_left + (unsigned)(OFF_M + 8 + Q * 4), mb, barB_left + 8 * Q);
                         }
                     }
                     if (active) {
-                        uint16_t* sp = a.S + frame + ((size_t)y * a.W1 + x) * a.Dp + gl * DPL;
+                        uint16_t* sp = Sf + o;
                         unsigned So[NR];
 #pragma unroll
                         for (int j = 0; j < NR; j++) So[j] = uaddmin2(uaddmin2(LA[j], LU[j], 0x7fff7fffu), LB[j], 0x7fff7fffu);
@@ -233,7 +237,11 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
                 }
             }
         }
-        __syncthreads();   // row t complete in this CTA: ping-pong buffers may flip (halos are ordered by the mbarriers)
+        __syncthreads();   // row t complete in this CTA: ping-pong fields may flip (halos are ordered by the mbarriers)
+    };
+    for (int t = 0; t < a.H; t += 2) {
+        row(std::integral_constant<int, 0>{}, t);
+        if (t + 1 < a.H) row(std::integral_constant<int, 1>{}, t + 1);
     }
     cluster.sync();        // nobody leaves while a neighbour could still address its shared memory
 }
@@ -259,13 +267,12 @@ static cudaLaunchConfig_t vert_cfg(int CS, int B, size_t smem, cudaStream_t st, 
 template <int LW, int NR>
 static bool plan_vert(const Eff& e, VertPlan& best) {
     constexpr int G = VERT_THREADS / LW;
-    constexpr int COLQ = (NR / 4) * LW;
     double best_score = 0.0;
     for (int CS = 1; CS <= 16; CS++) {
         int NC = (e.W1 + CS - 1) / CS;
         if ((CS - 1) * NC >= e.W1) continue;                       // last strip would be empty
-        size_t smem = ((size_t)4 * (NC + 1) + NC) * COLQ * sizeof(uint4) + ((size_t)4 * (NC + 1) + NC + 1) * sizeof(unsigned) + 4 * sizeof(unsigned long long) + 64;
         int KIT = (NC + G - 1) / G;
+        size_t smem = (size_t)(KIT * G + 1) * VertLayout<LW, NR>::REC + 4 * sizeof(unsigned long long);
         if (smem > 225 * 1024 || KIT > VERT_KMAX) continue;
         cudaLaunchAttribute attr[1];
         cudaLaunchConfig_t cfg = vert_cfg<LW, NR>(CS, 1, smem, 0, attr);
@@ -303,6 +310,7 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     VertArgs a;
     a.C = C; a.S = S; a.H = e.H; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e;
     a.NC = cached.NC; a.CS = cached.CS; a.dy = dy; a.accumulate = accumulate;
+    a.KIT = (cached.NC + VertLayout<LW, NR>::G - 1) / VertLayout<LW, NR>::G; a.nrec = a.KIT * VertLayout<LW, NR>::G + 1;
     cudaLaunchAttribute attr[1];
     cudaLaunchConfig_t cfg = vert_cfg<LW, NR>(cached.CS, B, cached.smem, st, attr);
     cudaError_t le = (e.D == LW * 2 * NR) ? cudaLaunchKernelEx(&cfg, k_vert<LW, NR, false>, a)
@@ -319,6 +327,7 @@ int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int 
     if (disabled < 0) { const char* v = getenv("B200S_NO_VERT"); disabled = (v && v[0] == '1') ? 1 : 0; }
     if (disabled) return 1;
     if (e.Dp % 8 != 0 || e.Dp > 512) return 1;
+    if ((size_t)e.H * e.W1 * e.Dp >= (1ull << 31)) return 1;   // 32-bit element offsets inside a frame
     if (e.Dp > 64) {               // 16 disparities per lane
         int LW = 8;
         while (LW * 16 < e.Dp) LW *= 2;
