@@ -48,6 +48,17 @@ struct B200sHandle {
     DevBuf maps;  // 4 x H x W float
     // scratch
     DevBuf imgL, imgR, rectL, rectR, recL, recR, C, S, Calt, raw, med, labels, sizes, f0, f1, s16c, hostio, ck, keys;
+    // asynchronous host-batch pipeline: two slots, copies on their own streams so that the H2D of chunk k+1 and
+    // the D2H of chunk k-1 overlap the kernels of chunk k
+    enum { NSLOT = 2 };
+    struct Slot {
+        DevBuf inL, inR, out;
+        cudaEvent_t in_done = nullptr, compute_done = nullptr, out_done = nullptr;
+        bool busy = false;
+        int rc = 0;
+    } slot[NSLOT];
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    unsigned next_ticket = 0;
     bool debug_flow = false;  // materialise the full S volume with the generic per-direction kernels (stage taps)
     // geometry of the last sgbm call (for debug taps)
     Eff last_eff;
@@ -65,6 +76,7 @@ struct B200sHandle {
         DevBuf* all[] = {&maps, &imgL, &imgR, &rectL, &rectR, &recL, &recR, &C, &S, &Calt, &raw, &med,
                          &labels, &sizes, &f0, &f1, &s16c, &hostio, &ck, &keys};
         for (DevBuf* b : all) b->release();
+        for (Slot& sl : slot) { sl.inL.release(); sl.inR.release(); sl.out.release(); }
     }
 };
 
@@ -128,6 +140,13 @@ int b200s_create(int device, const B200sParams* p, B200sHandle** out) {
     h->stream = h->own_stream;
     cudaEventCreate(&h->ev0);
     cudaEventCreate(&h->ev1);
+    cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking);
+    for (B200sHandle::Slot& sl : h->slot) {
+        cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&sl.compute_done, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&sl.out_done, cudaEventDisableTiming);
+    }
     *out = h;
     return B200S_OK;
 }
@@ -145,7 +164,16 @@ int b200s_destroy(B200sHandle* h) {
     if (!h) return B200S_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    if (h->s_in) cudaStreamSynchronize(h->s_in);
+    if (h->s_out) cudaStreamSynchronize(h->s_out);
     h->release_all();
+    for (B200sHandle::Slot& sl : h->slot) {
+        if (sl.in_done) cudaEventDestroy(sl.in_done);
+        if (sl.compute_done) cudaEventDestroy(sl.compute_done);
+        if (sl.out_done) cudaEventDestroy(sl.out_done);
+    }
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -598,29 +626,67 @@ int b200s_reset_stage_times(B200sHandle* h) {
     return B200S_OK;
 }
 
-int b200s_pipeline_batch(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W, int use_maps,
-                         const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth) {
+int b200s_pipeline_batch_submit(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W, int use_maps,
+                                const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth,
+                                int* ticket) {
     if (!h) return B200S_E_INVALID;
-    if (!L || !R || !pp || !dp || !disp || B <= 0 || H <= 0 || W <= 0) { h->set_error(B200S_E_INVALID, "pipeline_batch: bad arguments"); return B200S_E_INVALID; }
+    if (!L || !R || !pp || !dp || !disp || !ticket || B <= 0 || H <= 0 || W <= 0) { h->set_error(B200S_E_INVALID, "pipeline_batch: bad arguments"); return B200S_E_INVALID; }
     CUDA_TRY(h, cudaSetDevice(h->device));
     const int Wc = W - h->params.numDisparities;
     if (Wc <= 0) { h->set_error(B200S_E_INVALID, "pipeline_batch: numDisparities >= image width"); return B200S_E_INVALID; }
     const size_t npx = (size_t)B * H * W, nc = (size_t)B * H * Wc;
-    CUDA_TRY(h, h->imgL.ensure(npx));
-    CUDA_TRY(h, h->imgR.ensure(npx));
-    CUDA_TRY(h, h->hostio.ensure(2 * nc * sizeof(float)));
-    CUDA_TRY(h, cudaMemcpyAsync(h->imgL.p, L, npx, cudaMemcpyHostToDevice, h->stream));
-    CUDA_TRY(h, cudaMemcpyAsync(h->imgR.p, R, npx, cudaMemcpyHostToDevice, h->stream));
-    float* dDisp = h->hostio.as<float>();
+    const unsigned tk = h->next_ticket;
+    B200sHandle::Slot& sl = h->slot[tk % B200sHandle::NSLOT];
+    if (sl.busy) { h->set_error(B200S_E_STATE, "pipeline_batch_submit: ticket %u of this slot has not been waited for", tk - B200sHandle::NSLOT); return B200S_E_STATE; }
+    // growing a buffer frees device memory: nothing of this handle may still be running on it
+    if (npx > sl.inL.cap || npx > sl.inR.cap || 2 * nc * sizeof(float) > sl.out.cap) {
+        CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+        CUDA_TRY(h, cudaStreamSynchronize(h->s_out));
+        CUDA_TRY(h, sl.inL.ensure(npx));
+        CUDA_TRY(h, sl.inR.ensure(npx));
+        CUDA_TRY(h, sl.out.ensure(2 * nc * sizeof(float)));
+    }
+    // H2D on the copy-in stream (the slot's previous user has been waited for, so its kernels are done)
+    CUDA_TRY(h, cudaMemcpyAsync(sl.inL.p, L, npx, cudaMemcpyHostToDevice, h->s_in));
+    CUDA_TRY(h, cudaMemcpyAsync(sl.inR.p, R, npx, cudaMemcpyHostToDevice, h->s_in));
+    CUDA_TRY(h, cudaEventRecord(sl.in_done, h->s_in));
+    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.in_done, 0));
+    float* dDisp = sl.out.as<float>();
     float* dDepth = dDisp + nc;
-    Timed t(h);
-    int rc = dev_pipeline(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), B, H, W, use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
-    if (rc) return rc;
-    t.stop();
-    CUDA_TRY(h, cudaMemcpyAsync(disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
-    if (dp->enabled && depth) CUDA_TRY(h, cudaMemcpyAsync(depth, dDepth, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    {
+        Timed t(h);
+        int rc = dev_pipeline(h, sl.inL.as<uint8_t>(), sl.inR.as<uint8_t>(), B, H, W, use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
+        if (rc) return rc;
+        t.stop();
+    }
+    CUDA_TRY(h, cudaEventRecord(sl.compute_done, h->stream));
+    CUDA_TRY(h, cudaStreamWaitEvent(h->s_out, sl.compute_done, 0));
+    CUDA_TRY(h, cudaMemcpyAsync(disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
+    if (dp->enabled && depth) CUDA_TRY(h, cudaMemcpyAsync(depth, dDepth, nc * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
+    CUDA_TRY(h, cudaEventRecord(sl.out_done, h->s_out));
+    sl.busy = true;
+    *ticket = (int)tk;
+    h->next_ticket = tk + 1;
+    return B200S_OK;
+}
+
+int b200s_pipeline_batch_wait(B200sHandle* h, int ticket) {
+    if (!h) return B200S_E_INVALID;
+    B200sHandle::Slot& sl = h->slot[(unsigned)ticket % B200sHandle::NSLOT];
+    const unsigned tk = (unsigned)ticket;
+    if (!sl.busy || tk >= h->next_ticket || h->next_ticket - tk > B200sHandle::NSLOT) { h->set_error(B200S_E_STATE, "pipeline_batch_wait: ticket %d is not in flight", ticket); return B200S_E_STATE; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    sl.busy = false;
+    CUDA_TRY(h, cudaEventSynchronize(sl.out_done));
     return check_launch(h, "pipeline_batch");
+}
+
+int b200s_pipeline_batch(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W, int use_maps,
+                         const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth) {
+    int ticket = 0;
+    int rc = b200s_pipeline_batch_submit(h, L, R, B, H, W, use_maps, pp, dp, disp, depth, &ticket);
+    if (rc) return rc;
+    return b200s_pipeline_batch_wait(h, ticket);
 }
 
 }  // extern "C"

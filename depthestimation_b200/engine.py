@@ -74,6 +74,7 @@ class StereoEngine:
     def __init__(self, device: int = 0, **sgbm_kw):
         self._lib = _lib.load()
         self._h = C.c_void_p()
+        self._inflight = {}
         self.params = make_params(**sgbm_kw)
         rc = self._lib.b200s_create(int(device), C.byref(self.params), C.byref(self._h))
         if rc == _lib.E_INVALID:
@@ -239,6 +240,33 @@ class StereoEngine:
         self._check(self._lib.b200s_pipeline_batch(
             self._h, lefts.ctypes.data, rights.ctypes.data, B, H, W, int(bool(use_maps)), C.byref(pp), C.byref(dp),
             disp.ctypes.data, depth.ctypes.data if depth is not None else None), "b200s_pipeline_batch")
+        return disp, depth
+
+    def pipeline_batch_submit(self, lefts, rights, pp, dp, use_maps=False, out_disp=None, out_depth=None):
+        """Asynchronous pipeline_batch: enqueue H2D -> kernels -> D2H for one chunk and return a ticket at once.
+        At most two chunks in flight; the arrays (pinned for real overlap) must not be touched until
+        pipeline_batch_wait(ticket) returns (disp, depth)."""
+        lefts, rights = np.asarray(lefts), np.asarray(rights)
+        if lefts.dtype != np.uint8 or rights.dtype != np.uint8 or lefts.ndim != 3 or lefts.shape != rights.shape:
+            raise ValueError("pipeline_batch expects two uint8 [B,H,W] arrays of equal shape")
+        lefts, rights = np.ascontiguousarray(lefts), np.ascontiguousarray(rights)
+        B, H, W = lefts.shape
+        Wc = W - self.params.numDisparities
+        if Wc <= 0:
+            raise ValueError("num_disp must be smaller than the image width")
+        disp = out_disp if out_disp is not None else np.empty((B, H, Wc), np.float32)
+        depth = (out_depth if out_depth is not None else np.empty((B, H, Wc), np.float32)) if dp.enabled else None
+        ticket = C.c_int(0)
+        self._check(self._lib.b200s_pipeline_batch_submit(
+            self._h, lefts.ctypes.data, rights.ctypes.data, B, H, W, int(bool(use_maps)), C.byref(pp), C.byref(dp),
+            disp.ctypes.data, depth.ctypes.data if depth is not None else None, C.byref(ticket)),
+            "b200s_pipeline_batch_submit")
+        self._inflight[ticket.value] = (lefts, rights, disp, depth, pp, dp)   # keep the buffers alive
+        return ticket.value
+
+    def pipeline_batch_wait(self, ticket: int):
+        self._check(self._lib.b200s_pipeline_batch_wait(self._h, int(ticket)), "b200s_pipeline_batch_wait")
+        _, _, disp, depth, _, _ = self._inflight.pop(int(ticket))
         return disp, depth
 
     def stage_times(self, reset=False):

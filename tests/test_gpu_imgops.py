@@ -154,3 +154,36 @@ def test_batch_dev_matches_single(engine):
         d1, z1, _, _ = engine.pipeline(pairs[k][0], pairs[k][1], pp, dp)
         assert np.array_equal(disp[k].cpu().numpy(), d1)
         assert np.array_equal(depth[k].cpu().numpy(), z1)
+
+
+def test_batch_submit_wait_overlapped_chunks(engine):
+    """Two chunks in flight through b200s_pipeline_batch_submit/_wait give, chunk by chunk, exactly what the
+    blocking call gives; ticket misuse is a call-order error, not a crash."""
+    from depthestimation_b200.engine import make_post_params, make_depth_params, EngineError
+    H, W, D = 48, 160, 32
+    engine.configure(num_disp=D, sgbm_mode="sgbm")
+    pp = make_post_params(False, 100, 1.0, 2.5)
+    dp = make_depth_params(0.8 * W, 0.54, 0.0, eps=0, max_depth=None)
+    chunks = []
+    for c, B in enumerate((3, 2, 4, 1)):          # ragged chunk sizes: the slots regrow
+        prs = [make_pair(H, W, D, seed=2000 + 10 * c + k)[:2] for k in range(B)]
+        chunks.append((np.stack([p[0] for p in prs]), np.stack([p[1] for p in prs])))
+    want = [engine.pipeline_batch(l, r, pp, dp) for l, r in chunks]
+    got = []
+    tk = engine.pipeline_batch_submit(*chunks[0], pp, dp)
+    for i in range(1, len(chunks)):
+        nxt = engine.pipeline_batch_submit(*chunks[i], pp, dp)
+        got.append(engine.pipeline_batch_wait(tk))
+        tk = nxt
+    got.append(engine.pipeline_batch_wait(tk))
+    for (d0, z0), (d1, z1) in zip(want, got):
+        assert np.array_equal(d0, d1) and np.array_equal(z0, z1)
+    # a third submit without waiting, and a wait on a ticket that is not in flight
+    t0 = engine.pipeline_batch_submit(*chunks[0], pp, dp)
+    t1 = engine.pipeline_batch_submit(*chunks[1], pp, dp)
+    with pytest.raises(EngineError):
+        engine.pipeline_batch_submit(*chunks[2], pp, dp)
+    engine.pipeline_batch_wait(t0)
+    engine.pipeline_batch_wait(t1)
+    with pytest.raises((EngineError, KeyError)):
+        engine.pipeline_batch_wait(t1)
