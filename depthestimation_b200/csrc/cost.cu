@@ -93,9 +93,9 @@ template <int BS, int NTS>
 struct CostCfg {
     static constexpr int XT = COST_XT;
     static constexpr int NXI = XT + BS - 1;                              // pixel-cost columns per row (with halo)
-    static constexpr int RW = (((NXI + 2 * NTS + 3) / 2 + 1) + 1) & ~1;  // words per right array and alignment copy
+    static constexpr int RW = (((NXI + 2 * NTS + 3) / 2 + 1) + 1) & ~1;  // words per right-image array
     static constexpr int RING = BS * XT * NTS;                           // [BS][XT][NTS] horizontal sums
-    static constexpr size_t SMEM = (size_t)(RING + NXI * 8 + 2 * RA_COUNT * RW) * 4;
+    static constexpr size_t SMEM = (size_t)(RING + 2 * (NXI * 8 + RA_COUNT * RW)) * 4;   // ring + two staging buffers
 };
 
 // One source row of the strip: pixel cost -> horizontal box sum -> vertical running sum V[].
@@ -110,22 +110,46 @@ __device__ __forceinline__ void cost_row(const unsigned* __restrict__ sL, const 
 #pragma unroll
     for (int j = 0; j < BS; j++) pr[j] = 0u;
     unsigned hs = 0u;
+    // right-image words: word k of an array = (half[2k], half[2k+1]); the thread needs the pair starting at half
+    // e + 2 dp. Interior strips walk e = NXI-1 .. 0, so consecutive columns share a word: one LDS per array every
+    // second column plus a byte permute on the odd ones (instead of two alignment copies and one LDS per column).
+    unsigned wlo[RA_COUNT], whi[RA_COUNT];
 #pragma unroll
     for (int i = 0; i < G::NXI; i++) {
-        int e;
+        unsigned rv[RA_COUNT];
         if (INTERIOR) {
-            e = G::NXI - 1 - i;
+            const int e = G::NXI - 1 - i;                                  // compile-time after unrolling
+            if (e & 1) {
+                if (i == 0) {
+#pragma unroll
+                    for (int arr = 0; arr < RA_COUNT; arr++) whi[arr] = sRd[arr * G::RW + (e + 1) / 2];
+                }
+#pragma unroll
+                for (int arr = 0; arr < RA_COUNT; arr++) {
+                    wlo[arr] = sRd[arr * G::RW + (e - 1) / 2];
+                    rv[arr] = __byte_perm(wlo[arr], whi[arr], 0x5432);     // (half[e], half[e+1])
+                }
+            } else {
+                if (i == 0) {
+#pragma unroll
+                    for (int arr = 0; arr < RA_COUNT; arr++) wlo[arr] = sRd[arr * G::RW + e / 2];
+                }
+#pragma unroll
+                for (int arr = 0; arr < RA_COUNT; arr++) { rv[arr] = wlo[arr]; whi[arr] = wlo[arr]; }
+            }
         } else {
             const int xc = min(max(xa - BS / 2 + i, 0), W1 - 1);
-            e = x_max - (xc + minX1);                                 // uniform
+            const int e = x_max - (xc + minX1);                            // uniform, run time
+            const unsigned* base = sRd + (e >> 1);
+            const unsigned sh = (unsigned)(e & 1) * 16u;
+#pragma unroll
+            for (int arr = 0; arr < RA_COUNT; arr++)
+                rv[arr] = __funnelshift_r(base[arr * G::RW], base[arr * G::RW + 1], sh);
         }
-        const unsigned* base = sRd + (e & 1) * (RA_COUNT * G::RW) + (e >> 1);
         const uint4 l0 = *(const uint4*)(sL + i * 8);                 // {u, -u, lo1, -hi1} gradient channel
         const uint4 l1 = *(const uint4*)(sL + i * 8 + 4);             // raw channel
-        const unsigned vg = base[RA_VG * G::RW], nvg = base[RA_NVG * G::RW], log2_ = base[RA_LOG * G::RW],
-                       nhig = base[RA_NHIG * G::RW];
-        const unsigned vr = base[RA_VR * G::RW], nvr = base[RA_NVR * G::RW], lor = base[RA_LOR * G::RW],
-                       nhir = base[RA_NHIR * G::RW];
+        const unsigned vg = rv[RA_VG], nvg = rv[RA_NVG], log2_ = rv[RA_LOG], nhig = rv[RA_NHIG];
+        const unsigned vr = rv[RA_VR], nvr = rv[RA_NVR], lor = rv[RA_LOR], nhir = rv[RA_NHIR];
         // c0 = max(0, u - hi2, lo2 - u); c1 = max(0, v - hi1, lo1 - v); cost = min(c0, c1)
         unsigned c0 = __viaddmax_s16x2_relu(nhig, l0.x, __vadd2(log2_, l0.y));
         unsigned c1 = __viaddmax_s16x2_relu(vg, l0.w, __vadd2(nvg, l0.z));
@@ -147,7 +171,7 @@ __device__ __forceinline__ void cost_row(const unsigned* __restrict__ sL, const 
 }
 
 template <int BS, int NTS, bool FULL>
-__global__ void __launch_bounds__(NTS, (COST_MINB * 128 / NTS > 32 ? 32 : COST_MINB * 128 / NTS)) k_cost(const CostArgs a) {
+__global__ void __launch_bounds__(NTS, COST_MINB * 4 / ((NTS + 31) / 32)) k_cost(const CostArgs a) {   // COST_MINB * 4 warps per SM
     using G = CostCfg<BS, NTS>;
     constexpr int XT = G::XT, NXI = G::NXI, RW = G::RW;
     extern __shared__ __align__(16) unsigned smem[];
@@ -180,8 +204,7 @@ __global__ void __launch_bounds__(NTS, (COST_MINB * 128 / NTS > 32 ? 32 : COST_M
     const int NR = (x_max - x_min) + 2 * NT + 2;                      // right-image samples (reversed)
     const bool interior = (xa - BS / 2 >= 0) && (xa + XT - 1 + BS / 2 <= a.W1 - 1);
     unsigned* ring = smem;                                             // [BS][XT][NTS]
-    unsigned* sL = ring + G::RING;                                     // [NXI][8]
-    unsigned* sR = sL + NXI * 8;                                       // [2][RA_COUNT][RW]
+    unsigned* sL = ring + G::RING;                                     // 2 x { [NXI][8] left, [RA_COUNT][RW] right }
 
     for (int i = threadIdx.x; i < G::RING; i += NT) ring[i] = 0u;
 
@@ -195,55 +218,92 @@ __global__ void __launch_bounds__(NTS, (COST_MINB * 128 / NTS > 32 ? 32 : COST_M
     const int ostride = FULL ? NTS : NT;                               // u32 words between cost columns
     int slot = 0;
 
-    for (int s = s_begin; s <= s_end; s++) {
+    // Staging is double-buffered and software-pipelined: the records of row s+1 are fetched from global memory
+    // into registers before the slide over row s starts, and unpacked into the other sL/sR buffer after it, so
+    // one barrier per row suffices and the global latency hides behind the slide.
+    constexpr int STG = NXI * 8 + RA_COUNT * RW;                       // words per staging buffer (sL + sR)
+    uint2 pfL = make_uint2(0u, 0u), pfR[2][2];
+    auto fetch = [&](const int s) {                                    // first NT left columns, first 2 NT right words
         const int yc = min(max(s, ylo), a.H - 1);
-        __syncthreads();  // previous row's readers are done with sL / sR
-        // -- left pixels: replicated pairs {u, -u, lo1, -hi1} for g and r, indexed by halo column
-        for (int i = threadIdx.x; i < NXI; i += NT) {
-            int xc = min(max(xa - BS / 2 + i, 0), a.W1 - 1);
-            uint2 r = a.recL[frame + (size_t)yc * a.W + xc + a.minX1];
-            unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
-            unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
-            uint4 w0, w1;
-            w0.x = pk2(g); w0.y = pk2(0u - g); w0.z = pk2(glo); w0.w = pk2(0u - ghi);
-            w1.x = pk2(rr); w1.y = pk2(0u - rr); w1.z = pk2(rlo); w1.w = pk2(0u - rhi);
-            *(uint4*)(sL + i * 8) = w0;
-            *(uint4*)(sL + i * 8 + 4) = w1;
+        const size_t row = frame + (size_t)yc * a.W;
+        if ((int)threadIdx.x < NXI) {
+            const int xc = min(max(xa - BS / 2 + (int)threadIdx.x, 0), a.W1 - 1);
+            pfL = __ldg(a.recL + row + xc + a.minX1);
         }
-        // -- right pixels, reversed: half index i <-> right x = xr_hi - i. Two alignment copies of packed
-        //    pairs: copy c, word k = (half[2k + c], half[2k + c + 1]). A thread owns the even half 2k and the
-        //    odd half 2k + 1: it writes word k of copy 0 whole, and one 16-bit half of words k and k - 1 ... of copy 1
-        {
-            unsigned short* c1 = (unsigned short*)(sR + RA_COUNT * RW);
-            for (int k = threadIdx.x; 2 * k < NR + 2; k += NT) {
-                unsigned v0[RA_COUNT], v1[RA_COUNT];
+#pragma unroll
+        for (int it = 0; it < 2; it++) {
+            const int k = threadIdx.x + it * NT;
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+                const int xr = xr_hi - (2 * k + q);
+                pfR[it][q] = make_uint2(0u, 0u);
+                if (2 * k < NR + 2 && xr >= 0 && xr < a.W) pfR[it][q] = __ldg(a.recR + row + xr);
+            }
+        }
+    };
+    auto put_left = [&](unsigned* bL, const int i, const uint2 r) {    // replicated pairs {u, -u, lo1, -hi1} for g and r
+        const unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
+        const unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
+        uint4 w0, w1;
+        w0.x = pk2(g); w0.y = pk2(0u - g); w0.z = pk2(glo); w0.w = pk2(0u - ghi);
+        w1.x = pk2(rr); w1.y = pk2(0u - rr); w1.z = pk2(rlo); w1.w = pk2(0u - rhi);
+        *(uint4*)(bL + i * 8) = w0;
+        *(uint4*)(bL + i * 8 + 4) = w1;
+    };
+    auto put_right = [&](unsigned* bR, const int k, const uint2 r0, const uint2 r1) {   // word k = halves 2k, 2k+1
+        unsigned v0[RA_COUNT], v1[RA_COUNT];
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            const uint2 r = q ? r1 : r0;                                // an absent pixel is the all-zero record
+            const unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
+            const unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
+            unsigned* v = q ? v1 : v0;
+            v[RA_VG] = g; v[RA_NVG] = (0u - g) & 0xffffu; v[RA_LOG] = glo; v[RA_NHIG] = (0u - ghi) & 0xffffu;
+            v[RA_VR] = rr; v[RA_NVR] = (0u - rr) & 0xffffu; v[RA_LOR] = rlo; v[RA_NHIR] = (0u - rhi) & 0xffffu;
+        }
+#pragma unroll
+        for (int arr = 0; arr < RA_COUNT; arr++) bR[arr * RW + k] = v0[arr] | (v1[arr] << 16);
+    };
+    auto stage = [&](const int s, unsigned* bL) {                      // registers (and, for tiny D, global) -> shared
+        unsigned* bR = bL + NXI * 8;
+        if ((int)threadIdx.x < NXI) put_left(bL, threadIdx.x, pfL);
+#pragma unroll
+        for (int it = 0; it < 2; it++) {
+            const int k = threadIdx.x + it * NT;
+            if (2 * k < NR + 2) put_right(bR, k, pfR[it][0], pfR[it][1]);
+        }
+        // strips wider than the thread count (very small D): the rest comes straight from global memory
+        if (NT < NXI || 4 * NT < NR + 2) {
+            const int yc = min(max(s, ylo), a.H - 1);
+            const size_t row = frame + (size_t)yc * a.W;
+            for (int i = threadIdx.x + NT; i < NXI; i += NT) {
+                const int xc = min(max(xa - BS / 2 + i, 0), a.W1 - 1);
+                put_left(bL, i, a.recL[row + xc + a.minX1]);
+            }
+            for (int k = threadIdx.x + 2 * NT; 2 * k < NR + 2; k += NT) {
+                uint2 r[2];
 #pragma unroll
                 for (int q = 0; q < 2; q++) {
                     const int xr = xr_hi - (2 * k + q);
-                    unsigned g = 0, glo = 0, ghi = 0, rr = 0, rlo = 0, rhi = 0;
-                    if (xr >= 0 && xr < a.W) {
-                        uint2 r = __ldg(a.recR + frame + (size_t)yc * a.W + xr);
-                        g = r.x & 255u; glo = (r.x >> 8) & 255u; ghi = (r.x >> 16) & 255u;
-                        rr = r.x >> 24; rlo = r.y & 255u; rhi = (r.y >> 8) & 255u;
-                    }
-                    unsigned* v = q ? v1 : v0;
-                    v[RA_VG] = g; v[RA_NVG] = (0u - g) & 0xffffu; v[RA_LOG] = glo; v[RA_NHIG] = (0u - ghi) & 0xffffu;
-                    v[RA_VR] = rr; v[RA_NVR] = (0u - rr) & 0xffffu; v[RA_LOR] = rlo; v[RA_NHIR] = (0u - rhi) & 0xffffu;
+                    r[q] = (xr >= 0 && xr < a.W) ? __ldg(a.recR + row + xr) : make_uint2(0u, 0u);
                 }
-#pragma unroll
-                for (int arr = 0; arr < RA_COUNT; arr++) {
-                    sR[arr * RW + k] = v0[arr] | (v1[arr] << 16);                    // copy 0, word k
-                    c1[arr * 2 * RW + 2 * k] = (unsigned short)v1[arr];              // copy 1, word k, low half
-                    if (k > 0) c1[arr * 2 * RW + 2 * k - 1] = (unsigned short)v0[arr]; // copy 1, word k - 1, high half
-                }
+                put_right(bR, k, r[0], r[1]);
             }
         }
-        __syncthreads();
+    };
+
+    fetch(s_begin);
+    stage(s_begin, sL);
+    __syncthreads();
+    for (int s = s_begin; s <= s_end; s++) {
+        const int par = (s - s_begin) & 1;
+        const unsigned* cL = sL + par * STG;
+        if (s < s_end) fetch(s + 1);
 
         // -- slide along the strip
         unsigned* ringd = ring + slot * (XT * NTS) + dp;
-        if (interior) cost_row<BS, NTS, true>(sL, sR + dp, ringd, V, xa, a.W1, a.minX1, x_max);
-        else cost_row<BS, NTS, false>(sL, sR + dp, ringd, V, xa, a.W1, a.minX1, x_max);
+        if (interior) cost_row<BS, NTS, true>(cL, cL + NXI * 8 + dp, ringd, V, xa, a.W1, a.minX1, x_max);
+        else cost_row<BS, NTS, false>(cL, cL + NXI * 8 + dp, ringd, V, xa, a.W1, a.minX1, x_max);
         slot = (slot + 1 == BS) ? 0 : slot + 1;
 
         // -- emit the output row whose window just completed
@@ -260,6 +320,8 @@ __global__ void __launch_bounds__(NTS, (COST_MINB * 128 / NTS > 32 ? 32 : COST_M
                     if (xa + xo < a.W1) orow[xo * ostride] = flat ? 0u : V[xo];
             }
         }
+        if (s < s_end) stage(s + 1, sL + (par ^ 1) * STG);
+        __syncthreads();   // row s+1 is staged, and everybody is done reading row s
     }
 }
 
