@@ -197,7 +197,7 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
     // ---- neighbours of the winner for the parabola fit -------------------------------------------
     // S(., d) of this pixel goes through a per-line shared-memory stash so that lane 0 can read the two
     // neighbours of the winner by address (cheaper than a dynamic register select + shuffle)
-    __syncwarp();   // lane 0 is done with the previous pixel's stash
+    stash += (xc & 1) * (LW * DPL);   // two stashes alternate: lane 0 may still be reading the previous pixel's
 #pragma unroll
     for (int q = 0; q < NR / 4; q++)
         *(uint4*)(stash + (gl * DPL + 8 * q)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     const int gbase = (threadIdx.x & 31) / LW * LW;
     const bool active = gl * DPL < a.Dp;
     uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;
-    unsigned short* stash = (unsigned short*)(rsm + (size_t)LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * LW * DPL;
+    unsigned short* stash = (unsigned short*)(rsm + (size_t)LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * 2 * LW * DPL;
 
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
@@ -260,35 +260,38 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
 
     unsigned L[NR];
     unsigned m;
-    // The three scans below are unrolled by two over a pair of register buffers (CA, CB): the load of column
-    // x -+ 1 is in flight while column x is processed, and no register-to-register copies are needed.
+    // Chunks: chunk 0 = [0, r0) with r0 in [1, K] (the ragged one, handled by a short prologue), then full chunks of
+    // K columns. Checkpoint j (j >= 1) is L(<-) after column r0 + (j-1) K, i.e. the state a re-scan of chunk j-1 starts from.
+    static_assert(ROW_K % 2 == 0 && (ROW_K & (ROW_K - 1)) == 0, "ROW_K must be an even power of two");
+    const int r0 = a.W1 - ROW_K * ((a.W1 - 1) / ROW_K);
+    // The scans are unrolled by two over a pair of register buffers: the load of the next column is in flight while
+    // the current one is processed, also across the phase and chunk boundaries of pass 2.
     unsigned CA[NR], CB[NR];
 #pragma unroll
     for (int j = 0; j < NR; j++) { CA[j] = 0u; CB[j] = 0u; }
-    // ---- pass 1: <- over the row, checkpoint L at every K-th column ------------------------------
+    // ---- pass 1: <- over the row down to column r0, checkpoint L at every chunk start -------------------
     const uint64_t pol_first = l2_policy_first(), pol_last = l2_policy_last();
-    const int nchunks = (a.W1 + ROW_K - 1) / ROW_K;
     sgm_reset<NR>(L, m);
     {
         auto step1 = [&](const int x, const unsigned (&Cc)[NR]) {
             sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
-            if ((x % ROW_K) == 0 && active && valid) store_regs<NR>(ck + (size_t)(x / ROW_K) * a.Dp, L);
+            if (((x - r0) & (ROW_K - 1)) == 0 && active && valid) store_regs<NR>(ck + (size_t)((x - r0) / ROW_K + 1) * a.Dp, L);
         };
         int x = a.W1 - 1;
-        if (active && x >= ROW_K) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_first);
-        for (; x - 1 >= ROW_K; x -= 2) {
+        if (active && x >= r0) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_first);
+        for (; x - 1 >= r0; x -= 2) {
             if (active) {
                 load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_first);
-                if (x - ROW_PD - 1 >= ROW_K) {
+                if (x - ROW_PD - 1 >= r0) {
                     prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
                     prefetch_l2(Crow + (size_t)(x - ROW_PD - 1) * a.Dp);
                 }
             }
             step1(x, CA);
-            if (active && x - 2 >= ROW_K) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_first);
+            if (active && x - 2 >= r0) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_first);
             step1(x - 1, CB);
         }
-        if (x >= ROW_K) step1(x, CA);
+        if (x >= r0) step1(x, CA);
     }
     __syncwarp();
     // ---- pass 2: chunk by chunk, left to right ------------------------------------------------------
@@ -298,108 +301,159 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     unsigned SA[NR], SB[NR];
 #pragma unroll
     for (int j = 0; j < NR; j++) { SA[j] = 0u; SB[j] = 0u; }
-    for (int c = 0; c < nchunks; c++) {
-        const int xs = c * ROW_K, xe = min(xs + ROW_K, a.W1);
-        // re-run <- inside the chunk from the checkpoint at xe (or from the border)
-        if (xe < a.W1) {
+    auto stepb = [&](const int x, const int xs, const unsigned (&Cc)[NR]) {     // one <- step, L kept for the -> scan
+        sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
 #pragma unroll
-            for (int j = 0; j < NR; j++) L[j] = 0x7fff7fffu;
-            if (active) load_regs<NR>(ck + (size_t)(c + 1) * a.Dp, L);
+        for (int q = 0; q < NR / 4; q++)
+            Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+    };
+    auto stepf = [&](const int x, const int xs, const unsigned (&Cc)[NR], unsigned (&Sc)[NR]) {   // one -> step + winner
+        sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+#pragma unroll
+        for (int q = 0; q < NR / 4; q++) {
+            const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
+            Sc[4 * q] = uaddmin2(uaddmin2(Sc[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
+            Sc[4 * q + 1] = uaddmin2(uaddmin2(Sc[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);
+            Sc[4 * q + 2] = uaddmin2(uaddmin2(Sc[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
+            Sc[4 * q + 3] = uaddmin2(uaddmin2(Sc[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
+        }
+        wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
+    };
+    // checkpoint of the chunk that ends at xe -> L (in flight while other work runs); nothing to load at the row end
+    auto fetch_ck = [&](const int xe) {
+#pragma unroll
+        for (int j = 0; j < NR; j++) L[j] = 0x7fff7fffu;
+        if (active && xe < a.W1) load_regs<NR>(ck + (size_t)((xe - r0) / ROW_K + 1) * a.Dp, L);
+    };
+    auto start_from_ck = [&](const int xe) {
+        if (xe < a.W1) {
             const unsigned mn = group_min2<LW>(local_min2<NR>(L), gmask);
             m = min(mn & 0xffffu, mn >> 16);
         } else {
             sgm_reset<NR>(L, m);
         }
-        if (active) {
-            load_regs_pol<NR>(Crow + (size_t)(xe - 1) * a.Dp, CA, pol_last);
-            // next chunk: bring C and Sv towards L2 while this chunk is processed
-            if (xe + gl < a.W1 && gl < ROW_K) {
-                prefetch_l2_keep(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL);
-                prefetch_l2(Srow + (size_t)(xe + gl) * a.Dp - gl * DPL);
-                if (a.Dp > 64) {
-                    prefetch_l2_keep(Crow + (size_t)(xe + gl) * a.Dp - gl * DPL + 64);
-                    prefetch_l2(Srow + (size_t)(xe + gl) * a.Dp - gl * DPL + 64);
-                }
+    };
+    auto prefetch_chunk = [&](const int xs) {    // bring C and Sv of chunk [xs, xs+K) towards L2
+        if (active && xs + gl < a.W1 && gl < ROW_K) {
+            prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL);
+            prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL);
+            if (a.Dp > 64) {
+                prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
+                prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
             }
         }
-        {
-            auto stepb = [&](const int x, const unsigned (&Cc)[NR]) {
-                sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
-#pragma unroll
-                for (int q = 0; q < NR / 4; q++)
-                    Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
-            };
-            int x = xe - 1;
-            for (; x - 1 >= xs; x -= 2) {
-                if (active) load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_last);
-                stepb(x, CA);
-                if (active && x - 2 >= xs) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_last);
-                stepb(x - 1, CB);
-            }
-            if (x >= xs) stepb(x, CA);
+    };
+    {   // chunk 0 = [0, r0): short and ragged, simple loops (once per row)
+        fetch_ck(r0);
+        prefetch_chunk(r0);
+        start_from_ck(r0);
+        for (int x = r0 - 1; x >= 0; x--) {
+            if (active) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_last);
+            stepb(x, 0, CA);
         }
         __syncwarp();
-        // -> over the chunk, S = Sv + L(->) + L(<-), winner selection
-        if (active) {
-            load_regs_pol<NR>(Crow + (size_t)xs * a.Dp, CA, pol_first);
-            load_regs_pol<NR>(Srow + (size_t)xs * a.Dp, SA, pol_first);
+        if (r0 < a.W1) {   // set up chunk 1: its checkpoint and its first <- column
+            fetch_ck(r0 + ROW_K);
+            if (active) load_regs_pol<NR>(Crow + (size_t)(r0 + ROW_K - 1) * a.Dp, CB, pol_last);
         }
-        {
-            auto stepf = [&](const int x, const unsigned (&Cc)[NR], unsigned (&Sc)[NR]) {
-                sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+        for (int x = 0; x < r0; x++) {
+            if (active) {
+                load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_first);
+                load_regs_pol<NR>(Srow + (size_t)x * a.Dp, SA, pol_first);
+            }
+            stepf(x, 0, CA, SA);
+        }
+        __syncwarp();
 #pragma unroll
-                for (int q = 0; q < NR / 4; q++) {
-                    const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
-                    Sc[4 * q] = uaddmin2(uaddmin2(Sc[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
-                    Sc[4 * q + 1] = uaddmin2(uaddmin2(Sc[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);
-                    Sc[4 * q + 2] = uaddmin2(uaddmin2(Sc[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
-                    Sc[4 * q + 3] = uaddmin2(uaddmin2(Sc[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
-                }
-                wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
-            };
-            int x = xs;
-            for (; x + 1 < xe; x += 2) {
-                if (active) {
-                    load_regs_pol<NR>(Crow + (size_t)(x + 1) * a.Dp, CB, pol_first);
-                    load_regs_pol<NR>(Srow + (size_t)(x + 1) * a.Dp, SB, pol_first);
-                }
-                stepf(x, CA, SA);
-                if (active && x + 2 < xe) {
+        for (int j = 0; j < NR; j++) CA[j] = CB[j];
+    }
+    for (int xs = r0; xs < a.W1; xs += ROW_K) {
+        // full chunk [xs, xe): CA = C(xe-1) and L = checkpoint(xe) were requested one phase ago
+        const int xe = xs + ROW_K;
+        start_from_ck(xe);
+        prefetch_chunk(xe);
+#pragma unroll 1   // keep the code small: the body inlines two full steps already
+        for (int i = 0; i < ROW_K; i += 2) {
+            const int x = xe - 1 - i;
+            if (active) load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_last);
+            stepb(x, xs, CA);
+            if (active) {
+                if (i + 2 < ROW_K) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_last);
+                else load_regs_pol<NR>(Srow + (size_t)xs * a.Dp, SA, pol_first);   // first -> column: Sv; its C is CB
+            }
+            stepb(x - 1, xs, CB);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < NR; j++) CA[j] = CB[j];                      // C(xs), reused by the -> scan
+        if (xe < a.W1) fetch_ck(xe + ROW_K);                             // L is dead until the next chunk
+#pragma unroll 1
+        for (int i = 0; i < ROW_K; i += 2) {
+            const int x = xs + i;
+            if (active) {
+                load_regs_pol<NR>(Crow + (size_t)(x + 1) * a.Dp, CB, pol_first);
+                load_regs_pol<NR>(Srow + (size_t)(x + 1) * a.Dp, SB, pol_first);
+            }
+            stepf(x, xs, CA, SA);
+            if (active) {
+                if (i + 2 < ROW_K) {
                     load_regs_pol<NR>(Crow + (size_t)(x + 2) * a.Dp, CA, pol_first);
                     load_regs_pol<NR>(Srow + (size_t)(x + 2) * a.Dp, SA, pol_first);
+                } else if (xe < a.W1) {
+                    load_regs_pol<NR>(Crow + (size_t)(xe + ROW_K - 1) * a.Dp, CA, pol_last);   // next chunk's first <- column
                 }
-                stepf(x + 1, CB, SB);
             }
-            if (x < xe) stepf(x, CA, SA);
+            stepf(x + 1, xs, CB, SB);
         }
         __syncwarp();
     }
-    // ---- A.6 step 5: left-right check on the finished row ---------------------------------------------
+    // ---- A.6 step 5: left-right check on the finished row, four pixels per lane in flight ------------------
     __syncwarp();
-    for (int x = a.minX1 + gl; x < a.maxX1 && valid; x += LW) {
-        int d1 = out[x];
-        if (d1 == a.INV) continue;
-        const int _d = d1 >> 4, d_ = (d1 + 15) >> 4;
-        const int _x = x - _d, x_ = x - d_;
-        bool c1 = false, c2 = false;
-        if (_x >= 0 && _x < a.W) {
-            unsigned k = __ldcg(&keys[_x]);   // keys are updated by RED at L2: read them there
-            int v2 = (k == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (k & 0xffffu)) + a.minD);
-            c1 = v2 >= a.minD && abs(v2 - _d) > a.d12e;
+    if (valid) {
+        constexpr int UB = 4;
+        for (int xb = a.minX1 + gl; xb < a.maxX1; xb += UB * LW) {
+            int d1[UB];
+            unsigned ka[UB], kb[UB];
+#pragma unroll
+            for (int u = 0; u < UB; u++) {
+                const int x = xb + u * LW;
+                d1[u] = (x < a.maxX1) ? (int)__ldcg(&out[x]) : a.INV;
+            }
+#pragma unroll
+            for (int u = 0; u < UB; u++) {
+                const int x = xb + u * LW;
+                const int _x = x - (d1[u] >> 4), x_ = x - ((d1[u] + 15) >> 4);
+                ka[u] = kb[u] = 0xffffffffu;
+                if (d1[u] != a.INV) {
+                    if (_x >= 0 && _x < a.W) ka[u] = __ldcg(&keys[_x]);   // keys are updated by RED at L2: read them there
+                    if (x_ >= 0 && x_ < a.W) kb[u] = __ldcg(&keys[x_]);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UB; u++) {
+                const int x = xb + u * LW;
+                if (d1[u] == a.INV) continue;
+                const int _d = d1[u] >> 4, d_ = (d1[u] + 15) >> 4;
+                const int _x = x - _d, x_ = x - d_;
+                bool c1 = false, c2 = false;
+                if (_x >= 0 && _x < a.W) {
+                    const int v2 = (ka[u] == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (ka[u] & 0xffffu)) + a.minD);
+                    c1 = v2 >= a.minD && abs(v2 - _d) > a.d12e;
+                }
+                if (x_ >= 0 && x_ < a.W) {
+                    const int v2 = (kb[u] == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (kb[u] & 0xffffu)) + a.minD);
+                    c2 = v2 >= a.minD && abs(v2 - d_) > a.d12e;
+                }
+                if (c1 && c2) out[x] = (int16_t)a.INV;
+            }
         }
-        if (x_ >= 0 && x_ < a.W) {
-            unsigned k = __ldcg(&keys[x_]);
-            int v2 = (k == 0xffffffffu) ? (int)(short)a.INV : (int)(short)((0xffffu - (k & 0xffffu)) + a.minD);
-            c2 = v2 >= a.minD && abs(v2 - d_) > a.d12e;
-        }
-        if (c1 && c2) out[x] = (int16_t)a.INV;
     }
 }
 
 template <int LW, int NR>
 static size_t rows_smem() {
     constexpr int LINES = 128 / LW;
-    return (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * LW * 2 * NR * sizeof(unsigned short);
+    return (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * 2 * LW * 2 * NR * sizeof(unsigned short);
 }
 
 template <int LW, int NR>
