@@ -31,6 +31,12 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 #ifndef ROW_PD
 #define ROW_PD 6  // L2 prefetch distance in columns
 #endif
+#ifndef ROW_PBLK
+#define ROW_PBLK 0
+#endif
+#ifndef ROWS_STASH2
+#define ROWS_STASH2 1   // two alternating sub-pixel stashes per line (no write-after-read sync)
+#endif
 
 // L2 residency hints. The row kernel touches a chunk of C twice within a few microseconds (reverse re-scan, then
 // forward scan) while ~6000 lines stream 40+ MB of other data through L2 in between: the chunk is fetched
@@ -197,7 +203,11 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
     // ---- neighbours of the winner for the parabola fit -------------------------------------------
     // S(., d) of this pixel goes through a per-line shared-memory stash so that lane 0 can read the two
     // neighbours of the winner by address (cheaper than a dynamic register select + shuffle)
+#if ROWS_STASH2
     stash += (xc & 1) * (LW * DPL);   // two stashes alternate: lane 0 may still be reading the previous pixel's
+#else
+    __syncwarp();                     // lane 0 is done with the previous pixel's stash
+#endif
 #pragma unroll
     for (int q = 0; q < NR / 4; q++)
         *(uint4*)(stash + (gl * DPL + 8 * q)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
@@ -239,7 +249,7 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     const int gbase = (threadIdx.x & 31) / LW * LW;
     const bool active = gl * DPL < a.Dp;
     uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;
-    unsigned short* stash = (unsigned short*)(rsm + (size_t)LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * 2 * LW * DPL;
+    unsigned short* stash = (unsigned short*)(rsm + (size_t)LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * (ROWS_STASH2 ? 2 : 1) * LW * DPL;
 
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
@@ -282,10 +292,21 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
         for (; x - 1 >= r0; x -= 2) {
             if (active) {
                 load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_first);
+#if ROW_PBLK
+                // whole 8-column blocks (2 KB of one DRAM page for D = 128) are requested at once, ROW_PD columns ahead
+                if (((x - r0) & 7) == 7 && gl < 8) {
+                    const int xp = x - ROW_PD - gl;
+                    if (xp >= r0) {
+                        prefetch_l2(Crow + (size_t)xp * a.Dp - gl * DPL);
+                        if (a.Dp > 64) prefetch_l2(Crow + (size_t)xp * a.Dp - gl * DPL + 64);
+                    }
+                }
+#else
                 if (x - ROW_PD - 1 >= r0) {
                     prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
                     prefetch_l2(Crow + (size_t)(x - ROW_PD - 1) * a.Dp);
                 }
+#endif
             }
             step1(x, CA);
             if (active && x - 2 >= r0) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_first);
@@ -453,7 +474,7 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
 template <int LW, int NR>
 static size_t rows_smem() {
     constexpr int LINES = 128 / LW;
-    return (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * 2 * LW * 2 * NR * sizeof(unsigned short);
+    return (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * (ROWS_STASH2 ? 2 : 1) * LW * 2 * NR * sizeof(unsigned short);
 }
 
 template <int LW, int NR>

@@ -37,7 +37,10 @@ struct VertArgs {
     int accumulate;  // 0: S = sum, 1: S = sat(S + sum)
 };
 
-#define VERT_THREADS 512
+// threads per CTA: 512 (one CTA per SM, wide strips) or 288 (two CTAs per SM, narrow strips: two row pipelines per SM
+// that drift against each other and fill each other's barrier / latency gaps); picked by the planner
+#define VERT_THREADS_WIDE 512
+#define VERT_THREADS_NARROW 288
 #define VERT_KMAX 4
 
 // ---- mbarrier / st.async helpers (sm_90+ PTX) ---------------------------------------------------------
@@ -74,18 +77,18 @@ __device__ __forceinline__ void st_async_b32(unsigned raddr, const unsigned v, u
 // A field is [NR/4][LW] uint4 (16-byte chunk c of lane gl at c*LW + gl): conflict-free for LDS.128 / STS.128.
 // Everything starts zeroed, which IS the reset state (L = 0, m = 0) of the first row and of the predecessors
 // outside the cost domain (x-1 < 0, x+1 >= W1): those slots are never written, so no special cases remain.
-template <int LW, int NR>
+template <int LW, int NR, int VT>
 struct VertLayout {
     static constexpr int COLQ = (NR / 4) * LW;       // uint4 per field
     static constexpr int FLD = COLQ * 16;            // bytes per field
     static constexpr int OFF_A = 0, OFF_B = 2 * FLD, OFF_U = 4 * FLD, OFF_M = 5 * FLD;
     static constexpr int REC = 5 * FLD + 32;         // bytes per record
-    static constexpr int G = VERT_THREADS / LW;      // column groups per CTA
+    static constexpr int G = VT / LW;                // column groups per CTA
 };
 
-template <int LW, int NR, bool PAD>
-__global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
-    using VL = VertLayout<LW, NR>;
+template <int LW, int NR, bool PAD, int VT>
+__global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs a) {
+    using VL = VertLayout<LW, NR, VT>;
     constexpr int DPL = 2 * NR, G = VL::G, FLD = VL::FLD, REC = VL::REC;
     constexpr int OFF_A = VL::OFF_A, OFF_B = VL::OFF_B, OFF_U = VL::OFF_U, OFF_M = VL::OFF_M;
     cg::cluster_group cluster = cg::this_cluster();
@@ -99,7 +102,7 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
 
     extern __shared__ __align__(16) unsigned char vsm[];
     unsigned long long* bars = (unsigned long long*)(vsm + (size_t)a.nrec * REC);   // [4]: halo A slot 0/1, halo B slot 0/1
-    for (int i = threadIdx.x; i < a.nrec * (REC / 16); i += VERT_THREADS) ((uint4*)vsm)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = threadIdx.x; i < a.nrec * (REC / 16); i += VT) ((uint4*)vsm)[i] = make_uint4(0u, 0u, 0u, 0u);
     unsigned char* const tb = vsm + g * REC + gl * 16;   // this thread's chunk 0 of field 0 of record g
     unsigned char* const tm = vsm + g * REC + OFF_M;     // minima of record g
 
@@ -247,13 +250,12 @@ __global__ void __launch_bounds__(VERT_THREADS, 1) k_vert(const VertArgs a) {
 }
 
 // ---- launcher ------------------------------------------------------------------------------------
-struct VertPlan { int CS, NC, clusters; size_t smem; };
+struct VertPlan { int CS, NC, KIT, clusters, threads; size_t smem; double score; };
 
-template <int LW, int NR>
-static cudaLaunchConfig_t vert_cfg(int CS, int B, size_t smem, cudaStream_t st, cudaLaunchAttribute* attr) {
+static cudaLaunchConfig_t vert_cfg(int threads, int CS, int B, size_t smem, cudaStream_t st, cudaLaunchAttribute* attr) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(CS * B), 1, 1);
-    cfg.blockDim = dim3(VERT_THREADS, 1, 1);
+    cfg.blockDim = dim3((unsigned)threads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -262,47 +264,65 @@ static cudaLaunchConfig_t vert_cfg(int CS, int B, size_t smem, cudaStream_t st, 
     return cfg;
 }
 
-// Pick the cluster size (strips per frame) that keeps most of the chip busy: co-resident clusters (asked
-// from the driver) x cluster size x fill of the column slots, among the sizes whose strip state fits.
-template <int LW, int NR>
+// Pick the cluster size (strips per frame) for one CTA width: frames in flight (co-resident clusters, asked from the
+// driver) per column iteration of a thread, among the sizes whose strip state fits; ties go to the fuller column slots.
+template <int LW, int NR, int VT>
 static bool plan_vert(const Eff& e, VertPlan& best) {
-    constexpr int G = VERT_THREADS / LW;
-    double best_score = 0.0;
+    using VL = VertLayout<LW, NR, VT>;
+    constexpr int G = VL::G;
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute(k_vert<LW, NR, true, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return false; }
+        if (cudaFuncSetAttribute(k_vert<LW, NR, true, VT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return false; }
+        if (cudaFuncSetAttribute(k_vert<LW, NR, false, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return false; }
+        if (cudaFuncSetAttribute(k_vert<LW, NR, false, VT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return false; }
+        configured = true;
+    }
+    static int cs_env = -1;
+    if (cs_env < 0) { const char* v = getenv("B200S_VERT_CS"); cs_env = v ? atoi(v) : 0; }
+    best.score = 0.0;
     for (int CS = 1; CS <= 16; CS++) {
+        if (cs_env > 0 && CS != cs_env) continue;
         int NC = (e.W1 + CS - 1) / CS;
         if ((CS - 1) * NC >= e.W1) continue;                       // last strip would be empty
         int KIT = (NC + G - 1) / G;
-        size_t smem = (size_t)(KIT * G + 1) * VertLayout<LW, NR>::REC + 4 * sizeof(unsigned long long);
+        size_t smem = (size_t)(KIT * G + 1) * VL::REC + 4 * sizeof(unsigned long long);
         if (smem > 225 * 1024 || KIT > VERT_KMAX) continue;
         cudaLaunchAttribute attr[1];
-        cudaLaunchConfig_t cfg = vert_cfg<LW, NR>(CS, 1, smem, 0, attr);
+        cudaLaunchConfig_t cfg = vert_cfg(VT, CS, 1, smem, 0, attr);
         int ncl = 0;
-        if (cudaOccupancyMaxActiveClusters(&ncl, k_vert<LW, NR, true>, &cfg) != cudaSuccess) { cudaGetLastError(); continue; }
+        if (cudaOccupancyMaxActiveClusters(&ncl, k_vert<LW, NR, true, VT>, &cfg) != cudaSuccess) { cudaGetLastError(); continue; }
         if (ncl <= 0) continue;
-        double score = (double)ncl * e.W1 / ((double)KIT * G);     // useful column slots in flight
-        if (score > best_score) { best_score = score; best.CS = CS; best.NC = NC; best.smem = smem; best.clusters = ncl; }
+        double score = (double)ncl / KIT + 1e-3 * (double)e.W1 / ((double)CS * KIT * G);
+        if (score > best.score) { best.score = score; best.CS = CS; best.NC = NC; best.KIT = KIT; best.smem = smem; best.clusters = ncl; best.threads = VT; }
     }
-    return best_score > 0.0;
+    return best.score > 0.0;
+}
+
+template <int LW, int NR, int VT>
+static cudaError_t launch_vert_vt(const VertPlan& pl, const VertArgs& a, int B, bool pad, cudaStream_t st) {
+    cudaLaunchAttribute attr[1];
+    cudaLaunchConfig_t cfg = vert_cfg(VT, pl.CS, B, pl.smem, st, attr);
+    return pad ? cudaLaunchKernelEx(&cfg, k_vert<LW, NR, true, VT>, a) : cudaLaunchKernelEx(&cfg, k_vert<LW, NR, false, VT>, a);
 }
 
 template <int LW, int NR>
 static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, int accumulate, cudaStream_t st,
                          int* clusters_out) {
-    static bool configured = false;
-    if (!configured) {
-        if (cudaFuncSetAttribute(k_vert<LW, NR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return 1; }
-        if (cudaFuncSetAttribute(k_vert<LW, NR, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 1; }
-        if (cudaFuncSetAttribute(k_vert<LW, NR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return 1; }
-        if (cudaFuncSetAttribute(k_vert<LW, NR, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 1; }
-        configured = true;
-    }
     // the plan depends on (W1, Dp) only; cache the last one
     static VertPlan cached; static int cW1 = -1, cDp = -1; static bool cok = false;
     if (cW1 != e.W1 || cDp != e.Dp) {
-        cok = plan_vert<LW, NR>(e, cached); cW1 = e.W1; cDp = e.Dp;
+        static int vt_env = -1;
+        if (vt_env < 0) { const char* v = getenv("B200S_VERT_VT"); vt_env = v ? atoi(v) : 0; }
+        VertPlan wide, narrow;
+        const bool okw = (vt_env == 0 || vt_env == VERT_THREADS_WIDE) && plan_vert<LW, NR, VERT_THREADS_WIDE>(e, wide);
+        const bool okn = (vt_env == 0 || vt_env == VERT_THREADS_NARROW) && plan_vert<LW, NR, VERT_THREADS_NARROW>(e, narrow);
+        cok = okw || okn;
+        if (cok) cached = (okn && (!okw || narrow.score > wide.score)) ? narrow : wide;
+        cW1 = e.W1; cDp = e.Dp;
         if (getenv("B200S_VERBOSE") && cok)
-            fprintf(stderr, "[b200s] k_vert<%d,%d>: W1=%d Dp=%d -> cluster %d x %d cols, %zu B smem, %d clusters co-resident\n",
-                    LW, NR, e.W1, e.Dp, cached.CS, cached.NC, cached.smem, cached.clusters);
+            fprintf(stderr, "[b200s] k_vert<%d,%d>: W1=%d Dp=%d -> %d threads, cluster %d x %d cols (%d per thread group), %zu B smem, %d clusters co-resident\n",
+                    LW, NR, e.W1, e.Dp, cached.threads, cached.CS, cached.NC, cached.KIT, cached.smem, cached.clusters);
     }
     if (!cok) return 1;                                            // does not fit: caller falls back to k_path
     if (clusters_out) *clusters_out = cached.clusters;
@@ -310,11 +330,10 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     VertArgs a;
     a.C = C; a.S = S; a.H = e.H; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e;
     a.NC = cached.NC; a.CS = cached.CS; a.dy = dy; a.accumulate = accumulate;
-    a.KIT = (cached.NC + VertLayout<LW, NR>::G - 1) / VertLayout<LW, NR>::G; a.nrec = a.KIT * VertLayout<LW, NR>::G + 1;
-    cudaLaunchAttribute attr[1];
-    cudaLaunchConfig_t cfg = vert_cfg<LW, NR>(cached.CS, B, cached.smem, st, attr);
-    cudaError_t le = (e.D == LW * 2 * NR) ? cudaLaunchKernelEx(&cfg, k_vert<LW, NR, false>, a)
-                                          : cudaLaunchKernelEx(&cfg, k_vert<LW, NR, true>, a);
+    a.KIT = cached.KIT; a.nrec = cached.KIT * (cached.threads / LW) + 1;
+    const bool pad = e.D != LW * 2 * NR;
+    cudaError_t le = (cached.threads == VERT_THREADS_WIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_WIDE>(cached, a, B, pad, st)
+                                                           : launch_vert_vt<LW, NR, VERT_THREADS_NARROW>(cached, a, B, pad, st);
     if (le != cudaSuccess) { cudaGetLastError(); return 1; }
     return 0;
 }
