@@ -342,48 +342,61 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
 }
 
 // postprocess_disparity (hole filling off) / fast-mode median on a dense device batch, result in `out`
-static int dev_post(B200sHandle* h, const float* dIn, int B, int H, int W, const B200sPostParams& pp, float* out) {
+// postprocess_disparity (depthlib/postprocess.py:86-124). The input is either float disparity (dIn) or, inside the
+// fused pipeline, the matcher's own int16 x16 disparity (dIn16: (d*16).astype(int16) of d = v/16 is v itself, so
+// the float round trip is skipped). When dp/depthOut are given and the last stage is the 3x3 median, depth is
+// produced by that same kernel. Returns 1 in *depth_done when it was.
+static int dev_post_impl(B200sHandle* h, const float* dIn, const int16_t* dIn16, int B, int H, int W,
+                         const B200sPostParams& pp, float* out, const B200sDepthParams* dp, float* depthOut,
+                         bool* depth_done) {
     const size_t n = (size_t)B * H * W;
     const int mode = pp.fastMode;   // B200S_POST_*
-    if (mode == B200S_POST_MEDIAN_ONLY) {
-        launch_median3_f32(dIn, out, B, H, W, h->stream);
-        h->launches++;
-        return check_launch(h, "post(fast)");
-    }
-    if (mode == B200S_POST_OUTLIERS_ONLY) {
-        launch_outliers(dIn, out, B, H, W, pp.outlierThreshold, h->stream);
-        h->launches++;
-        return check_launch(h, "post(outliers)");
-    }
+    if (depth_done) *depth_done = false;
     if (mode < 0 || mode > B200S_POST_NO_MEDIAN) { h->set_error(B200S_E_INVALID, "postprocess: bad fastMode/stage selector %d", mode); return B200S_E_INVALID; }
-    CUDA_TRY(h, h->s16c.ensure(n * 2));
+    const bool fuse_depth = dp && dp->enabled && depthOut;
+    CUDA_TRY(h, h->f1.ensure(n * sizeof(float)));
+    float* t = h->f1.as<float>();
+    if (mode == B200S_POST_MEDIAN_ONLY || mode == B200S_POST_OUTLIERS_ONLY) {
+        const float* src = dIn;
+        if (!src) {   // int16 input: make the float view first
+            launch_s16_to_f32_div16(dIn16, n, t, h->stream);
+            h->launches++;
+            src = t;
+        }
+        if (mode == B200S_POST_OUTLIERS_ONLY) launch_outliers(src, out, B, H, W, pp.outlierThreshold, h->stream);
+        else if (fuse_depth) { launch_median3_f32_depth(src, out, B, H, W, *dp, depthOut, h->stream); if (depth_done) *depth_done = true; }
+        else launch_median3_f32(src, out, B, H, W, h->stream);
+        h->launches++;
+        return check_launch(h, "post(single stage)");
+    }
     CUDA_TRY(h, h->labels.ensure(n * sizeof(int)));
     CUDA_TRY(h, h->sizes.ensure(n * sizeof(int)));
-    CUDA_TRY(h, h->f1.ensure(n * sizeof(float)));
-    int16_t* s16 = h->s16c.as<int16_t>();
-    float* t = h->f1.as<float>();
-    launch_f32_to_s16x16(dIn, n, s16, h->stream);
+    int16_t* s16;
+    if (dIn16) {
+        s16 = const_cast<int16_t*>(dIn16);          // filtered in place: the caller hands over a scratch copy
+    } else {
+        CUDA_TRY(h, h->s16c.ensure(n * 2));
+        s16 = h->s16c.as<int16_t>();
+        launch_f32_to_s16x16(dIn, n, s16, h->stream);
+        h->launches++;
+    }
     launch_speckle(s16, B, H, W, 0, pp.maxSpeckleSize, pp.maxDiff16, h->labels.as<int>(), h->sizes.as<int>(), h->stream, &h->launches);
-    h->launches += 2;
     const bool outl = pp.applyOutlierRemoval && mode != B200S_POST_SPECKLE_ONLY;
     const bool med = (mode == B200S_POST_FULL);
-    if (outl && med) {
-        launch_s16_to_f32_div16(s16, n, out, h->stream);       // out used as temp
-        launch_outliers(out, t, B, H, W, pp.outlierThreshold, h->stream);
-        launch_median3_f32(t, out, B, H, W, h->stream);
-        h->launches += 2;
-    } else if (outl) {
-        launch_s16_to_f32_div16(s16, n, t, h->stream);
-        launch_outliers(t, out, B, H, W, pp.outlierThreshold, h->stream);
-        h->launches += 1;
-    } else if (med) {
-        launch_s16_to_f32_div16(s16, n, t, h->stream);
-        launch_median3_f32(t, out, B, H, W, h->stream);
-        h->launches += 1;
-    } else {
-        launch_s16_to_f32_div16(s16, n, out, h->stream);
+    float* pre = med ? t : out;                     // what the median (if any) reads
+    if (outl) launch_outliers_s16(s16, pre, B, H, W, pp.outlierThreshold, h->stream);
+    else launch_s16_to_f32_div16(s16, n, pre, h->stream);
+    h->launches++;
+    if (med) {
+        if (fuse_depth) { launch_median3_f32_depth(t, out, B, H, W, *dp, depthOut, h->stream); if (depth_done) *depth_done = true; }
+        else launch_median3_f32(t, out, B, H, W, h->stream);
+        h->launches++;
     }
     return check_launch(h, "post");
+}
+
+static int dev_post(B200sHandle* h, const float* dIn, int B, int H, int W, const B200sPostParams& pp, float* out) {
+    return dev_post_impl(h, dIn, nullptr, B, H, W, pp, out, nullptr, nullptr, nullptr);
 }
 
 static int dev_pipeline(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int H, int W, int use_maps,
@@ -413,13 +426,15 @@ static int dev_pipeline(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, in
     int rc = dev_sgbm(h, mL, mR, B, H, W, h->med.as<int16_t>());
     if (rc) return rc;
     const size_t nc = (size_t)B * H * Wc;
-    CUDA_TRY(h, h->f0.ensure(nc * sizeof(float)));
-    launch_disp16_to_f32_crop(h->med.as<int16_t>(), B, H, W, x0, h->f0.as<float>(), h->stream);
+    // crop [:, num_disp:] in int16; everything after it works on the cropped frame (stereo_core.py:168-196)
+    CUDA_TRY(h, h->s16c.ensure(nc * 2));
+    launch_crop_s16(h->med.as<int16_t>(), B, H, W, x0, h->s16c.as<int16_t>(), h->stream);
     h->launches++;
-    rc = dev_post(h, h->f0.as<float>(), B, H, Wc, pp, dDisp);
+    bool depth_done = false;
+    rc = dev_post_impl(h, nullptr, h->s16c.as<int16_t>(), B, H, Wc, pp, dDisp, &dp, dDepth, &depth_done);
     if (rc) return rc;
     mark(h, B200S_STAGE_POST);
-    if (dp.enabled && dDepth) {
+    if (dp.enabled && dDepth && !depth_done) {
         launch_depth(dDisp, nc, dp, dDepth, h->stream);
         h->launches++;
         mark(h, B200S_STAGE_DEPTH);

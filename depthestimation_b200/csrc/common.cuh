@@ -112,6 +112,9 @@ void launch_disp16_to_f32_crop(const int16_t* d16, int B, int H, int W, int x0, 
 void launch_f32_to_s16x16(const float* d, size_t n, int16_t* out, cudaStream_t st);
 void launch_s16_to_f32_div16(const int16_t* d, size_t n, float* out, cudaStream_t st);
 void launch_outliers(const float* d, float* out, int B, int H, int W, float thr, cudaStream_t st);
+void launch_outliers_s16(const int16_t* d16, float* out, int B, int H, int W, float thr, cudaStream_t st);
+void launch_crop_s16(const int16_t* d16, int B, int H, int W, int x0, int16_t* out, cudaStream_t st);
+void launch_median3_f32_depth(const float* src, float* dst, int B, int H, int W, const B200sDepthParams& dp, float* Z, cudaStream_t st);
 void launch_median3_f32(const float* src, float* dst, int B, int H, int W, cudaStream_t st);
 void launch_depth(const float* disp, size_t n, const B200sDepthParams& dp, float* Z, cudaStream_t st);
 void launch_debug_volume(const uint16_t* V, int H, int W1, int Dp, int D, int add, int16_t* out, cudaStream_t st);

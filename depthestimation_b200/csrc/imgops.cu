@@ -104,6 +104,17 @@ void launch_disp16_to_f32_crop(const int16_t* d16, int B, int H, int W, int x0, 
     dim3 grid((W - x0 + 255) / 256, H, B);
     k_d16_to_f32_crop<<<grid, 256, 0, st>>>(d16, H, W, x0, out);
 }
+__global__ void __launch_bounds__(256) k_crop_s16(const int16_t* __restrict__ d16, int H, int W, int x0, int16_t* __restrict__ out) {
+    int Wc = W - x0;
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= Wc) return;
+    size_t row = (size_t)blockIdx.z * H + blockIdx.y;
+    out[row * Wc + x] = d16[row * W + x0 + x];
+}
+void launch_crop_s16(const int16_t* d16, int B, int H, int W, int x0, int16_t* out, cudaStream_t st) {
+    dim3 grid((W - x0 + 255) / 256, H, B);
+    k_crop_s16<<<grid, 256, 0, st>>>(d16, H, W, x0, out);
+}
 // (d * 16).astype(int16): C truncation toward zero, then wrap to 16 bits (numpy behaviour for in-range values)
 __global__ void __launch_bounds__(256) k_f32_to_s16x16(const float* __restrict__ d, size_t n, int16_t* __restrict__ out) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -128,37 +139,62 @@ __device__ __forceinline__ int reflect101(int p, int n) {
     while (p < 0 || p >= n) p = (p < 0) ? -p : 2 * (n - 1) - p;
     return p;
 }
-__global__ void __launch_bounds__(256) k_outliers(const float* __restrict__ d, float* __restrict__ out, int H, int W, float thr) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y;
-    if (x >= W) return;
-    const float* s = d + (size_t)blockIdx.z * H * W;
-    double sum = 0.0, sumsq = 0.0;
-#pragma unroll
-    for (int dy = -2; dy <= 2; dy++) {
-        const float* r = s + (size_t)reflect101(y + dy, H) * W;
-        double rs = 0.0, rq = 0.0;
-#pragma unroll
-        for (int dx = -2; dx <= 2; dx++) {
-            float v = r[reflect101(x + dx, W)];
-            rs = __dadd_rn(rs, (double)v);
-            rq = __dadd_rn(rq, (double)__fmul_rn(v, v));
-        }
-        sum = __dadd_rn(sum, rs);
-        sumsq = __dadd_rn(sumsq, rq);
+// Separable form with the reference's exact summation order: per row the five taps are added left to right in
+// double (row sum of d and of fl(d*d)), then the five row sums top to bottom; a CTA computes each row sum of its
+// (64+0) x (16+4) halo tile once instead of five times. TIn = float, or int16 holding 16 * d (d = v / 16 exactly).
+#define OT_W 64
+#define OT_H 16
+template <typename TIn> __device__ __forceinline__ float outl_val(TIn v);
+template <> __device__ __forceinline__ float outl_val<float>(float v) { return v; }
+template <> __device__ __forceinline__ float outl_val<int16_t>(int16_t v) { return __fdiv_rn((float)v, 16.0f); }
+
+template <typename TIn>
+__global__ void __launch_bounds__(256) k_outliers(const TIn* __restrict__ d, float* __restrict__ out, int H, int W, float thr) {
+    __shared__ float tile[OT_H + 4][OT_W + 4];
+    __shared__ double rs[OT_H + 4][OT_W], rq[OT_H + 4][OT_W];
+    const int x0 = blockIdx.x * OT_W, y0 = blockIdx.y * OT_H;
+    const TIn* s = d + (size_t)blockIdx.z * H * W;
+    for (int p = threadIdx.x; p < (OT_H + 4) * (OT_W + 4); p += 256) {
+        const int ly = p / (OT_W + 4), lx = p % (OT_W + 4);
+        const int y = reflect101(min(y0 + ly - 2, H + 1), H), x = reflect101(min(x0 + lx - 2, W + 1), W);
+        tile[ly][lx] = outl_val<TIn>(s[(size_t)y * W + x]);
     }
-    const float mean = (float)__dmul_rn(sum, 1.0 / 25.0);
-    const float msq = (float)__dmul_rn(sumsq, 1.0 / 25.0);
-    const float var = __fsub_rn(msq, __fmul_rn(mean, mean));
-    const float sd = __fsqrt_rn(fmaxf(var, 0.0f));
-    const float v = s[(size_t)y * W + x];
-    const float diff = fabsf(__fsub_rn(v, mean));
-    const bool outl = (diff > __fmul_rn(thr, sd)) && (v > 0.0f);
-    out[(size_t)blockIdx.z * H * W + (size_t)y * W + x] = outl ? 0.0f : v;
+    __syncthreads();
+    for (int p = threadIdx.x; p < (OT_H + 4) * OT_W; p += 256) {
+        const int ly = p / OT_W, lx = p % OT_W;
+        double a = 0.0, q = 0.0;
+#pragma unroll
+        for (int dx = 0; dx < 5; dx++) {
+            const float v = tile[ly][lx + dx];
+            a = __dadd_rn(a, (double)v);
+            q = __dadd_rn(q, (double)__fmul_rn(v, v));
+        }
+        rs[ly][lx] = a; rq[ly][lx] = q;
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < OT_H * OT_W; p += 256) {
+        const int ly = p / OT_W, lx = p % OT_W, x = x0 + lx, y = y0 + ly;
+        if (x >= W || y >= H) continue;
+        double sum = 0.0, sumsq = 0.0;
+#pragma unroll
+        for (int dy = 0; dy < 5; dy++) { sum = __dadd_rn(sum, rs[ly + dy][lx]); sumsq = __dadd_rn(sumsq, rq[ly + dy][lx]); }
+        const float mean = (float)__dmul_rn(sum, 1.0 / 25.0);
+        const float msq = (float)__dmul_rn(sumsq, 1.0 / 25.0);
+        const float var = __fsub_rn(msq, __fmul_rn(mean, mean));
+        const float sd = __fsqrt_rn(fmaxf(var, 0.0f));
+        const float v = tile[ly + 2][lx + 2];
+        const float diff = fabsf(__fsub_rn(v, mean));
+        const bool outl = (diff > __fmul_rn(thr, sd)) && (v > 0.0f);
+        out[(size_t)blockIdx.z * H * W + (size_t)y * W + x] = outl ? 0.0f : v;
+    }
 }
 void launch_outliers(const float* d, float* out, int B, int H, int W, float thr, cudaStream_t st) {
-    dim3 grid((W + 255) / 256, H, B);
-    k_outliers<<<grid, 256, 0, st>>>(d, out, H, W, thr);
+    dim3 grid((W + OT_W - 1) / OT_W, (H + OT_H - 1) / OT_H, B);
+    k_outliers<float><<<grid, 256, 0, st>>>(d, out, H, W, thr);
+}
+void launch_outliers_s16(const int16_t* d16, float* out, int B, int H, int W, float thr, cudaStream_t st) {
+    dim3 grid((W + OT_W - 1) / OT_W, (H + OT_H - 1) / OT_H, B);
+    k_outliers<int16_t><<<grid, 256, 0, st>>>(d16, out, H, W, thr);
 }
 
 // ---- B.4 depth ------------------------------------------------------------------------------------------------
@@ -171,6 +207,31 @@ __global__ void __launch_bounds__(256) k_depth(const float* __restrict__ disp, s
     if (adj > eps) z = __fdiv_rn(fB, adj);
     if (hasMax && z > maxDepth) z = maxDepth;
     Z[i] = z;
+}
+// 3x3 median of the float disparity and, from its result, the depth of the same pixel in one pass (pipeline tail)
+__global__ void __launch_bounds__(256) k_median3_f32_depth(const float* __restrict__ src, float* __restrict__ dst, int H, int W,
+                                                           float fB, float doffs, float eps, float maxDepth, int hasMax,
+                                                           float* __restrict__ Z) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    if (x >= W) return;
+    const float* s = src + (size_t)blockIdx.z * H * W;
+    int xm = max(x - 1, 0), xp = min(x + 1, W - 1);
+    const float* r0 = s + (size_t)max(y - 1, 0) * W;
+    const float* r1 = s + (size_t)y * W;
+    const float* r2 = s + (size_t)min(y + 1, H - 1) * W;
+    const float m = median9<float>(r0[xm], r0[x], r0[xp], r1[xm], r1[x], r1[xp], r2[xm], r2[x], r2[xp]);
+    const size_t i = (size_t)blockIdx.z * H * W + (size_t)y * W + x;
+    dst[i] = m;
+    float adj = __fadd_rn(m, doffs);
+    float z = __int_as_float(0x7f800000);
+    if (adj > eps) z = __fdiv_rn(fB, adj);
+    if (hasMax && z > maxDepth) z = maxDepth;
+    Z[i] = z;
+}
+void launch_median3_f32_depth(const float* src, float* dst, int B, int H, int W, const B200sDepthParams& dp, float* Z, cudaStream_t st) {
+    dim3 grid((W + 255) / 256, H, B);
+    k_median3_f32_depth<<<grid, 256, 0, st>>>(src, dst, H, W, dp.fB, dp.doffs, dp.eps, dp.maxDepth, dp.hasMaxDepth, Z);
 }
 void launch_depth(const float* disp, size_t n, const B200sDepthParams& dp, float* Z, cudaStream_t st) {
     k_depth<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(disp, n, dp.fB, dp.doffs, dp.eps, dp.maxDepth, dp.hasMaxDepth, Z);
