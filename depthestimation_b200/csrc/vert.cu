@@ -42,6 +42,9 @@ struct VertArgs {
 #define VERT_THREADS_WIDE 512
 #define VERT_THREADS_NARROW 288
 #define VERT_KMAX 4
+#ifndef VERT_UREG
+#define VERT_UREG 1   // 1: keep the vertical path's L in registers instead of shared memory
+#endif
 
 // ---- mbarrier / st.async helpers (sm_90+ PTX) ---------------------------------------------------------
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -134,6 +137,15 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
     // held in one register set per column slot (software pipeline across the row boundary)
     unsigned off[VERT_KMAX];
     unsigned Cb[VERT_KMAX][NR];
+#if VERT_UREG
+    unsigned Ur[VERT_KMAX][NR], mUr[VERT_KMAX];   // L and minimum of the vertical path never leave the thread
+#pragma unroll
+    for (int k = 0; k < VERT_KMAX; k++) {
+        mUr[k] = 0u;
+#pragma unroll
+        for (int j = 0; j < NR; j++) Ur[k][j] = 0u;
+    }
+#endif
     {
         const int y = (a.dy > 0) ? 0 : a.H - 1;
 #pragma unroll
@@ -178,14 +190,24 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
                 for (int c = 0; c < NR / 4; c++) {
                     const uint4 va = *(const uint4*)(rb + OFF_A + P * FLD + c * LW * 16);
                     const uint4 vb = *(const uint4*)(rb + REC + OFF_B + P * FLD + c * LW * 16);
+#if !VERT_UREG
                     const uint4 vu = *(const uint4*)(rb + OFF_U + c * LW * 16);
+#endif
                     LA[4 * c] = va.x; LA[4 * c + 1] = va.y; LA[4 * c + 2] = va.z; LA[4 * c + 3] = va.w;
                     LB[4 * c] = vb.x; LB[4 * c + 1] = vb.y; LB[4 * c + 2] = vb.z; LB[4 * c + 3] = vb.w;
+#if !VERT_UREG
                     LU[4 * c] = vu.x; LU[4 * c + 1] = vu.y; LU[4 * c + 2] = vu.z; LU[4 * c + 3] = vu.w;
+#endif
                 }
                 unsigned ma = *(const unsigned*)(rm + P * 4);
                 unsigned mb = *(const unsigned*)(rm + REC + 8 + P * 4);
+#if VERT_UREG
+                unsigned mu = mUr[k];
+#pragma unroll
+                for (int j = 0; j < NR; j++) LU[j] = Ur[k][j];
+#else
                 unsigned mu = *(const unsigned*)(rm + 16);
+#endif
                 sgm_step<LW, NR, PAD>(LA, ma, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
                 sgm_step<LW, NR, PAD>(LB, mb, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
                 sgm_step<LW, NR, PAD>(LU, mu, Cq, pm, gmask, gl, P1P1, P2mP1, 0, 0);
@@ -193,17 +215,26 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
                 off[k] = o + rowstep;
                 // C of the next row for this column slot: a whole row of work hides the latency
                 if (active && t + 1 < a.H) load_regs_nc<NR>(Cf + off[k], Cb[k]);
+#if VERT_UREG
+                mUr[k] = mu;
+#pragma unroll
+                for (int j = 0; j < NR; j++) Ur[k][j] = LU[j];
+#endif
                 if (valid) {
 #pragma unroll
                     for (int c = 0; c < NR / 4; c++) {
                         *(uint4*)(rb + REC + OFF_A + Q * FLD + c * LW * 16) = make_uint4(LA[4 * c], LA[4 * c + 1], LA[4 * c + 2], LA[4 * c + 3]);
                         *(uint4*)(rb + OFF_B + Q * FLD + c * LW * 16) = make_uint4(LB[4 * c], LB[4 * c + 1], LB[4 * c + 2], LB[4 * c + 3]);
+#if !VERT_UREG
                         *(uint4*)(rb + OFF_U + c * LW * 16) = make_uint4(LU[4 * c], LU[4 * c + 1], LU[4 * c + 2], LU[4 * c + 3]);
+#endif
                     }
                     if (gl == 0) {
                         *(unsigned*)(rm + REC + Q * 4) = ma;
                         *(unsigned*)(rm + 8 + Q * 4) = mb;
+#if !VERT_UREG
                         *(unsigned*)(rm + 16) = mu;
+#endif
                     }
                     // strip-edge columns go straight to the neighbour CTA's halo records (DSMEM, st.async + tx bytes)
                     if (t + 1 < a.H) {
