@@ -27,6 +27,8 @@ struct Eff {
     int speckleWindowSize, speckleRange;
 };
 
+struct Eff;
+static inline bool sum_cannot_saturate(const Eff& e);
 static inline int h_imax(int a, int b) { return a > b ? a : b; }
 static inline int h_imin(int a, int b) { return a < b ? a : b; }
 
@@ -54,6 +56,14 @@ static inline Eff make_eff(const B200sParams& p, int H, int W) {
     e.speckleWindowSize = p.speckleWindowSize;
     e.speckleRange = p.speckleRange;
     return e;
+}
+
+// L(p,d) <= blockcost + P2 and blockcost <= bs^2 (2 ftzero + 63) (A.2-A.4), so the sum over all paths of a mode is
+// bounded; when the bound is below 32768 the saturating adds of S never saturate and plain adds are exact.
+static inline bool sum_cannot_saturate(const Eff& e) {
+    const int npaths = (e.mode == B200S_MODE_HH) ? 8 : (e.mode == B200S_MODE_SGBM) ? 5 : (e.mode == B200S_MODE_HH4) ? 4 : 3;
+    const long long lmax = (long long)e.bs * e.bs * (2 * e.ftzero + 63) + e.P2e;
+    return npaths * lmax <= 32767;
 }
 
 // ---- packed 16x2 helpers (all single SASS instructions on sm_100a) --------------------------

@@ -24,7 +24,7 @@ struct RowArgs {
     uint16_t* ck;      // checkpoints [B*H][nck][Dp]
     unsigned* keys;    // right-view candidates [B*H][W]
     int16_t* raw;      // [B*H][W]
-    int H, W, W1, D, Dp, P1, P2, minD, minX1, maxX1, INV, ue, d12e, mode, nck, nlines;
+    int H, W, W1, D, Dp, P1, P2, minD, minX1, maxX1, INV, ue, d12e, mode, nck, nlines, nosat;
 };
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -33,6 +33,9 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 #endif
 #ifndef ROW_PBLK
 #define ROW_PBLK 0
+#endif
+#ifndef ROWS_PF2
+#define ROWS_PF2 3   // pass-2 L2 prefetch of the next chunk: bit 0 = C, bit 1 = Sv
 #endif
 #ifndef ROWS_STASH2
 #define ROWS_STASH2 1   // two alternating sub-pixel stashes per line (no write-after-read sync)
@@ -82,6 +85,17 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
     const int d0 = 8 * (a.D / 8);
     const bool simd3 = (a.mode == B200S_MODE_SGBM_3WAY) && d0 > 0;
     const unsigned gbits = (LW == 32) ? 0xffffffffu : ((1u << LW) - 1u);
+    // S(., d) of this pixel goes through a per-line shared-memory stash: lane 0 reads the two neighbours of the
+    // winner by address, and the winner's neighbourhood is knocked out there for the uniqueness test (dynamic
+    // indexing costs one store in shared memory, but ~8 ALU operations per register when done on registers)
+#if ROWS_STASH2
+    stash += (xc & 1) * (LW * DPL);   // two stashes alternate: lane 0 may still be reading the previous pixel's
+#else
+    __syncwarp();                     // lane 0 is done with the previous pixel's stash
+#endif
+#pragma unroll
+    for (int q = 0; q < NR / 4; q++)
+        *(uint4*)(stash + (gl * DPL + 8 * q)) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
     int minS, best;
     if (!simd3) {
         // binary min tree over the lane's registers; the winner's position is found by walking it down
@@ -161,13 +175,20 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
 
     // ---- uniqueness: smallest S outside [best-1, best+1] ------------------------------------------
     unsigned e[NR];
-    const int rel = best - gl * DPL;  // position of the winner relative to this lane's first d
+    __syncwarp();                                                   // the stash is complete
+    int Sm = 0, Sq = 0;
+    if (gl == 0) {
+        Sm = stash[max(best - 1, 0)];
+        Sq = stash[min(best + 1, LW * DPL - 1)];
+        if (best > 0) stash[best - 1] = 0xffffu;
+        stash[best] = 0xffffu;
+        if (best + 1 < LW * DPL) stash[best + 1] = 0xffffu;
+    }
+    __syncwarp();
 #pragma unroll
-    for (int j = 0; j < NR; j++) {
-        unsigned x = w[j];
-        if (rel >= 2 * j - 1 && rel <= 2 * j + 1) x |= 0x0000ffffu;       // d = 2j     excluded
-        if (rel >= 2 * j && rel <= 2 * j + 2) x |= 0xffff0000u;           // d = 2j + 1 excluded
-        e[j] = x;
+    for (int q = 0; q < NR / 4; q++) {
+        const uint4 t = *(const uint4*)(stash + (gl * DPL + 8 * q));
+        e[4 * q] = t.x; e[4 * q + 1] = t.y; e[4 * q + 2] = t.z; e[4 * q + 3] = t.w;
     }
     bool reject;
     const int nexcl = 1 + (best > 0) + (best < a.D - 1);
@@ -200,20 +221,7 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
             }
         }
     }
-    // ---- neighbours of the winner for the parabola fit -------------------------------------------
-    // S(., d) of this pixel goes through a per-line shared-memory stash so that lane 0 can read the two
-    // neighbours of the winner by address (cheaper than a dynamic register select + shuffle)
-#if ROWS_STASH2
-    stash += (xc & 1) * (LW * DPL);   // two stashes alternate: lane 0 may still be reading the previous pixel's
-#else
-    __syncwarp();                     // lane 0 is done with the previous pixel's stash
-#endif
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++)
-        *(uint4*)(stash + (gl * DPL + 8 * q)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-    __syncwarp();
     if (reject || gl != 0 || !valid) return;
-    const int Sm = stash[max(best - 1, 0)], Sq = stash[min(best + 1, LW * DPL - 1)];
     const int x2 = xc + a.minX1 - best - a.minD;
     if (minS < 32767) {
         const unsigned nk = ((unsigned)minS << 16) | (0xffffu - (unsigned)best);
@@ -333,10 +341,15 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
             const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
-            Sc[4 * q] = uaddmin2(uaddmin2(Sc[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
-            Sc[4 * q + 1] = uaddmin2(uaddmin2(Sc[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);
-            Sc[4 * q + 2] = uaddmin2(uaddmin2(Sc[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
-            Sc[4 * q + 3] = uaddmin2(uaddmin2(Sc[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
+            if (a.nosat) {   // the sum of all paths provably stays below 32768: plain adds on the packed halves
+                Sc[4 * q] += Lr[4 * q] + t.x; Sc[4 * q + 1] += Lr[4 * q + 1] + t.y;
+                Sc[4 * q + 2] += Lr[4 * q + 2] + t.z; Sc[4 * q + 3] += Lr[4 * q + 3] + t.w;
+            } else {
+                Sc[4 * q] = uaddmin2(uaddmin2(Sc[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
+                Sc[4 * q + 1] = uaddmin2(uaddmin2(Sc[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);
+                Sc[4 * q + 2] = uaddmin2(uaddmin2(Sc[4 * q + 2], Lr[4 * q + 2], 0x7fff7fffu), t.z, 0x7fff7fffu);
+                Sc[4 * q + 3] = uaddmin2(uaddmin2(Sc[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
+            }
         }
         wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
     };
@@ -355,14 +368,16 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
         }
     };
     auto prefetch_chunk = [&](const int xs) {    // bring C and Sv of chunk [xs, xs+K) towards L2
+#if ROWS_PF2
         if (active && xs + gl < a.W1 && gl < ROW_K) {
-            prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL);
-            prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL);
+            if (ROWS_PF2 & 1) prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL);
+            if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL);
             if (a.Dp > 64) {
-                prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
-                prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
+                if (ROWS_PF2 & 1) prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
+                if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
             }
         }
+#endif
     };
     {   // chunk 0 = [0, r0): short and ragged, simple loops (once per row)
         fetch_ck(r0);
@@ -486,8 +501,10 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
         cudaFuncSetAttribute(k_rows<LW, NR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         k_rows<LW, NR, false><<<grid, 128, smem, st>>>(a);
     } else {
+        RowArgs b = a;
+        b.nosat = 0;            // padded halves hold 0x7fff: their sums must keep saturating
         cudaFuncSetAttribute(k_rows<LW, NR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_rows<LW, NR, true><<<grid, 128, smem, st>>>(a);
+        k_rows<LW, NR, true><<<grid, 128, smem, st>>>(b);
     }
 }
 
@@ -527,6 +544,7 @@ int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint
     a.H = e.H; a.W = e.W; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e; a.minD = e.minD;
     a.minX1 = e.minX1; a.maxX1 = e.maxX1; a.INV = e.INV; a.ue = e.ue; a.d12e = e.d12e; a.mode = e.mode;
     a.nck = (e.W1 + ROW_K - 1) / ROW_K + 1;
+    a.nosat = sum_cannot_saturate(e) ? 1 : 0;
     a.nlines = B * e.H;
     if (e.Dp > 512) return -2;
     if (e.Dp > 64) {             // 16 disparities per lane

@@ -35,6 +35,7 @@ struct VertArgs {
     int CS;          // cluster size = strips per frame
     int dy;          // +1: top-down (predecessor row y-1), -1: bottom-up (predecessor row y+1)
     int accumulate;  // 0: S = sum, 1: S = sat(S + sum)
+    int nosat;       // the sum of all paths cannot reach 32768: plain adds
 };
 
 // threads per CTA: 512 (one CTA per SM, wide strips) or 288 (two CTAs per SM, narrow strips: two row pipelines per SM
@@ -259,12 +260,13 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
                         uint16_t* sp = Sf + o;
                         unsigned So[NR];
 #pragma unroll
-                        for (int j = 0; j < NR; j++) So[j] = uaddmin2(uaddmin2(LA[j], LU[j], 0x7fff7fffu), LB[j], 0x7fff7fffu);
+                        for (int j = 0; j < NR; j++)
+                            So[j] = a.nosat ? LA[j] + LU[j] + LB[j] : uaddmin2(uaddmin2(LA[j], LU[j], 0x7fff7fffu), LB[j], 0x7fff7fffu);
                         if (a.accumulate) {
                             unsigned Sold[NR];
                             load_regs<NR>(sp, Sold);
 #pragma unroll
-                            for (int j = 0; j < NR; j++) So[j] = uaddmin2(So[j], Sold[j], 0x7fff7fffu);
+                            for (int j = 0; j < NR; j++) So[j] = a.nosat ? So[j] + Sold[j] : uaddmin2(So[j], Sold[j], 0x7fff7fffu);
                         }
                         store_regs<NR>(sp, So);
                     }
@@ -360,7 +362,7 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     if (B <= 0) return 0;                                          // plan query only
     VertArgs a;
     a.C = C; a.S = S; a.H = e.H; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e;
-    a.NC = cached.NC; a.CS = cached.CS; a.dy = dy; a.accumulate = accumulate;
+    a.NC = cached.NC; a.CS = cached.CS; a.dy = dy; a.accumulate = accumulate; a.nosat = (sum_cannot_saturate(e) && e.D == LW * 2 * NR) ? 1 : 0;   // padded halves (0x7fff) must keep saturating
     a.KIT = cached.KIT; a.nrec = cached.KIT * (cached.threads / LW) + 1;
     const bool pad = e.D != LW * 2 * NR;
     cudaError_t le = (cached.threads == VERT_THREADS_WIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_WIDE>(cached, a, B, pad, st)
