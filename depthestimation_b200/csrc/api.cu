@@ -205,12 +205,13 @@ int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch) {
     int granule = 0;
     if (e.mode == B200S_MODE_SGBM || e.mode == B200S_MODE_HH)
         if (launch_vert_family(e, 0, nullptr, nullptr, +1, 0, h->stream, &granule) != 0) granule = 0;
-    // measured on B200: two waves of the row kernel run ~25 % faster per frame than one (the second wave
-    // de-synchronises the read-only and read-write phases of the CTAs); beyond that the gain is < 5 %
-    int cap = 2 * rows_capacity_lines(e) / H;
+    // measured on B200: the row kernel wants whole waves (a partly filled last wave costs up to 10 % per frame) and
+    // more than one of them (the second wave de-synchronises the phases of the CTAs: ~25 % faster per frame than a
+    // single wave); beyond three waves the gain is < 3 %
+    int cap = 3 * rows_capacity_lines(e) / H;
     if (granule <= 0) { *batch = cap > 0 ? cap : 16; return B200S_OK; }
     int b = granule;
-    while (b + granule <= cap) b += granule;   // largest multiple of the cluster granule within two row-kernel waves
+    while (b + granule <= cap) b += granule;   // largest multiple of the cluster granule within three row-kernel waves
     *batch = b;
     return B200S_OK;
 }

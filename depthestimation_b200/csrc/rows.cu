@@ -15,7 +15,7 @@
 #include "sgm_step.cuh"
 
 #ifndef ROW_K
-#define ROW_K 8  // columns per chunk
+#define ROW_K 6  // columns per chunk (a multiple of 3, the depth of the load ring)
 #endif
 
 struct RowArgs {
@@ -238,10 +238,11 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
 }
 
 #ifndef ROWS_MINB
-#define ROWS_MINB 5   // <= 102 registers: 5 CTAs (20 warps) per SM; measured best of 4/5/6 on B200
+#define ROWS_MINB 4   // 4 CTAs (16 warps) per SM: 57 KB of shared memory each, <= 128 registers
 #endif
 
-template <int LW, int NR, bool PAD>
+// W3 = true: sgbm_3way (its 8-wide SIMD winner rule keeps the monolithic wta_pixel); false: pipelined winner search
+template <int LW, int NR, bool PAD, bool W3>
 __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
     constexpr int LINES = 128 / LW;                 // lines per CTA
@@ -256,8 +257,9 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     const unsigned gmask = 0xffffffffu;
     const int gbase = (threadIdx.x & 31) / LW * LW;
     const bool active = gl * DPL < a.Dp;
-    uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;
-    unsigned short* stash = (unsigned short*)(rsm + (size_t)LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * (ROWS_STASH2 ? 2 : 1) * LW * DPL;
+    uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;                                  // L(<-) of the current chunk
+    uint4* Cb = rsm + (size_t)(LINES + lic) * ROW_K * (NR / 4) * LW;                        // C of the current chunk
+    unsigned short* stash = (unsigned short*)(rsm + (size_t)2 * LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * (ROWS_STASH2 ? 2 : 1) * LW * DPL;
 
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
@@ -280,64 +282,96 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     unsigned m;
     // Chunks: chunk 0 = [0, r0) with r0 in [1, K] (the ragged one, handled by a short prologue), then full chunks of
     // K columns. Checkpoint j (j >= 1) is L(<-) after column r0 + (j-1) K, i.e. the state a re-scan of chunk j-1 starts from.
-    static_assert(ROW_K % 2 == 0 && (ROW_K & (ROW_K - 1)) == 0, "ROW_K must be an even power of two");
+    static_assert(ROW_K % 3 == 0, "ROW_K must be a multiple of the prefetch ring (3 buffers)");
     const int r0 = a.W1 - ROW_K * ((a.W1 - 1) / ROW_K);
-    // The scans are unrolled by two over a pair of register buffers: the load of the next column is in flight while
-    // the current one is processed, also across the phase and chunk boundaries of pass 2.
-    unsigned CA[NR], CB[NR];
+    // A step takes as long as the memory system needs to deliver its operands (~1600 cycles measured with one column
+    // of look-ahead), so every scan runs over a ring of THREE register buffers: the loads of columns x+1 and x+2 are
+    // in flight while column x is processed, also across the phase and chunk boundaries of pass 2.
+    unsigned X0[NR], X1[NR], X2[NR];
 #pragma unroll
-    for (int j = 0; j < NR; j++) { CA[j] = 0u; CB[j] = 0u; }
+    for (int j = 0; j < NR; j++) { X0[j] = 0u; X1[j] = 0u; X2[j] = 0u; }
+    const uint64_t pol_first = l2_policy_first();
+    auto ldC = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, dst, pol_first); };
+    auto ldS = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Srow + (size_t)x * a.Dp, dst, pol_first); };
     // ---- pass 1: <- over the row down to column r0, checkpoint L at every chunk start -------------------
-    const uint64_t pol_first = l2_policy_first(), pol_last = l2_policy_last();
     sgm_reset<NR>(L, m);
     {
         auto step1 = [&](const int x, const unsigned (&Cc)[NR]) {
             sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
-            if (((x - r0) & (ROW_K - 1)) == 0 && active && valid) store_regs<NR>(ck + (size_t)((x - r0) / ROW_K + 1) * a.Dp, L);
+            if ((x - r0) % ROW_K == 0 && active && valid) store_regs<NR>(ck + (size_t)((x - r0) / ROW_K + 1) * a.Dp, L);
         };
         int x = a.W1 - 1;
-        if (active && x >= r0) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_first);
-        for (; x - 1 >= r0; x -= 2) {
-            if (active) {
-                load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_first);
-#if ROW_PBLK
-                // whole 8-column blocks (2 KB of one DRAM page for D = 128) are requested at once, ROW_PD columns ahead
-                if (((x - r0) & 7) == 7 && gl < 8) {
-                    const int xp = x - ROW_PD - gl;
-                    if (xp >= r0) {
-                        prefetch_l2(Crow + (size_t)xp * a.Dp - gl * DPL);
-                        if (a.Dp > 64) prefetch_l2(Crow + (size_t)xp * a.Dp - gl * DPL + 64);
-                    }
-                }
-#else
-                if (x - ROW_PD - 1 >= r0) {
-                    prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
-                    prefetch_l2(Crow + (size_t)(x - ROW_PD - 1) * a.Dp);
-                }
-#endif
+        if (x >= r0) ldC(x, X0);
+        if (x - 1 >= r0) ldC(x - 1, X1);
+        for (; x - 2 >= r0; x -= 3) {
+            ldC(x - 2, X2);
+            if (active && x - ROW_PD - 2 >= r0) {
+                prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
+                prefetch_l2(Crow + (size_t)(x - ROW_PD - 1) * a.Dp);
+                prefetch_l2(Crow + (size_t)(x - ROW_PD - 2) * a.Dp);
             }
-            step1(x, CA);
-            if (active && x - 2 >= r0) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_first);
-            step1(x - 1, CB);
+            step1(x, X0);
+            if (x - 3 >= r0) ldC(x - 3, X0);
+            step1(x - 1, X1);
+            if (x - 4 >= r0) ldC(x - 4, X1);
+            step1(x - 2, X2);
         }
-        if (x >= r0) step1(x, CA);
+        if (x >= r0) step1(x, X0);
+        if (x - 1 >= r0) step1(x - 1, X1);
     }
     __syncwarp();
     // ---- pass 2: chunk by chunk, left to right ------------------------------------------------------
     unsigned Lr[NR];   // L(->)
     unsigned mr;
     sgm_reset<NR>(Lr, mr);
-    unsigned SA[NR], SB[NR];
-#pragma unroll
-    for (int j = 0; j < NR; j++) { SA[j] = 0u; SB[j] = 0u; }
-    auto stepb = [&](const int x, const int xs, const unsigned (&Cc)[NR]) {     // one <- step, L kept for the -> scan
+    auto stepb = [&](const int x, const int xs, const unsigned (&Cc)[NR]) {     // one <- step; L and C kept for the -> scan
         sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
 #pragma unroll
-        for (int q = 0; q < NR / 4; q++)
+        for (int q = 0; q < NR / 4; q++) {
             Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+            Cb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(Cc[4 * q], Cc[4 * q + 1], Cc[4 * q + 2], Cc[4 * q + 3]);
+        }
     };
-    auto stepf = [&](const int x, const int xs, const unsigned (&Cc)[NR], unsigned (&Sc)[NR]) {   // one -> step + winner
-        sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+    // pixel whose uniqueness test and output are still pending (x < 0: none); Sm / Sq are meaningful on lane 0
+    int pn_best = 0, pn_minS = 0, pn_Sm = 0, pn_Sq = 0, pn_x = -1;
+    auto finish_pending = [&](const int min2) {
+        const int nexcl = 1 + (pn_best > 0) + (pn_best < a.D - 1);
+        const bool reject = (a.D > nexcl) && (min2 * (100 - a.ue) < pn_minS * 100);
+        if (!reject && gl == 0 && valid) {
+            const int x2 = pn_x + a.minX1 - pn_best - a.minD;
+            if (pn_minS < 32767) atomicMin(&keys[x2], ((unsigned)pn_minS << 16) | (0xffffu - (unsigned)pn_best));
+            int d16 = pn_best * 16;
+            if (pn_best > 0 && pn_best < a.D - 1) {
+                const int den2 = max(pn_Sm + pn_Sq - 2 * pn_minS, 1);
+                d16 += (int)__fdiv_rn((float)((pn_Sm - pn_Sq) * 16 + den2), (float)(2 * den2));   // exact, see wta_pixel
+            }
+            out[pn_x + a.minX1] = (int16_t)(d16 + a.minD * 16);
+        }
+    };
+    auto pending_local_min = [&]() -> unsigned {   // lane-local minimum of the pending pixel's S with the winner knocked out
+        __syncwarp();                               // lane 0's knock-out stores are visible
+        const unsigned short* sp = stash + (pn_x & 1) * (LW * DPL);
+        unsigned e[NR];
+#pragma unroll
+        for (int q = 0; q < NR / 4; q++) {
+            const uint4 t = *(const uint4*)(sp + (gl * DPL + 8 * q));
+            e[4 * q] = t.x; e[4 * q + 1] = t.y; e[4 * q + 2] = t.z; e[4 * q + 3] = t.w;
+        }
+        const unsigned me = local_min2<NR>(e);
+        return min(me & 0xffffu, me >> 16);
+    };
+    auto stepf = [&](const int x, const int xs, unsigned (&Sc)[NR]) {   // one -> step + winner; Sc holds Sv on entry
+        unsigned Cc[NR];
+#pragma unroll
+        for (int q = 0; q < NR / 4; q++) {
+            const uint4 t = Cb[((x - xs) * (NR / 4) + q) * LW + gl];
+            Cc[4 * q] = t.x; Cc[4 * q + 1] = t.y; Cc[4 * q + 2] = t.z; Cc[4 * q + 3] = t.w;
+        }
+        if constexpr (W3) {
+            sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+        }
+        unsigned mlL = 0u;
+        if constexpr (!W3) mlL = sgm_step_core<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
             const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
@@ -351,7 +385,73 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
                 Sc[4 * q + 3] = uaddmin2(uaddmin2(Sc[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
             }
         }
-        wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
+        if constexpr (W3) {
+            wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
+        } else {
+            // Winner search, software-pipelined by one pixel so that ONE lane-group reduction per step serves three
+            // minima: min_d L(->) (needed by the next column), min_d S of this pixel, and the second minimum of the
+            // previous pixel (its winner's neighbourhood was knocked out in the stash one step ago).
+            unsigned w[NR];
+#pragma unroll
+            for (int j = 0; j < NR; j++) w[j] = PAD ? umax2(Sc[j], pm[j]) : Sc[j];
+            unsigned short* st = stash + (x & 1) * (LW * DPL);
+#pragma unroll
+            for (int q = 0; q < NR / 4; q++)
+                *(uint4*)(st + (gl * DPL + 8 * q)) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+            unsigned t1[NR / 2 > 0 ? NR / 2 : 1], t2[NR / 4 > 0 ? NR / 4 : 1];
+#pragma unroll
+            for (int j = 0; j < NR / 2; j++) t1[j] = umin2(w[2 * j], w[2 * j + 1]);
+#pragma unroll
+            for (int j = 0; j < NR / 4; j++) t2[j] = umin2(t1[2 * j], t1[2 * j + 1]);
+            const unsigned mlS = (NR == 8) ? umin2(t2[0], t2[1]) : t2[0];
+            const unsigned lm = min(mlS & 0xffffu, mlS >> 16);
+            unsigned r0 = min(mlL & 0xffffu, mlL >> 16) | (lm << 16);
+            unsigned r1 = (pn_x >= 0) ? pending_local_min() : 0xffffu;
+#pragma unroll
+            for (int o = LW / 2; o > 0; o >>= 1) {
+                r0 = umin2(r0, __shfl_xor_sync(gmask, r0, o, LW));
+                r1 = min(r1, __shfl_xor_sync(gmask, r1, o, LW));
+            }
+            mr = r0 & 0xffffu;
+            const int minS = (int)(r0 >> 16);
+            if (pn_x >= 0) finish_pending((int)r1);
+            // position of the winner: walk the min tree down, lowest index wins at every level
+            auto has = [&](unsigned v) { return (int)min(v & 0xffffu, v >> 16) == minS; };
+            int j4 = 0;
+            if (NR == 8 && !has(t2[0])) j4 = 1;
+            const unsigned a0 = (NR == 8 && j4) ? t1[2] : t1[0];
+            const int j2 = 2 * j4 + (has(a0) ? 0 : 1);
+            unsigned b0 = w[0], b1 = w[1];
+#pragma unroll
+            for (int j = 1; j < NR / 2; j++) { b0 = (j2 == j) ? w[2 * j] : b0; b1 = (j2 == j) ? w[2 * j + 1] : b1; }
+            const int j1 = 2 * j2 + (has(b0) ? 0 : 1);
+            const unsigned c0 = has(b0) ? b0 : b1;
+            const int cand = 2 * j1 + (((int)(c0 & 0xffffu) == minS) ? 0 : 1);
+            const unsigned gbits = (LW == 32) ? 0xffffffffu : ((1u << LW) - 1u);
+            const unsigned bits = (__ballot_sync(gmask, (int)lm == minS) >> gbase) & gbits;
+            const int fl = __ffs(bits) - 1;                                   // lowest lane reaching the minimum
+            const int best = fl * DPL + __shfl_sync(gmask, cand, fl, LW);     // lowest d reaching the minimum
+            __syncwarp();                                                     // this pixel's stash is complete
+            if (gl == 0) {
+                pn_Sm = st[max(best - 1, 0)];
+                pn_Sq = st[min(best + 1, LW * DPL - 1)];
+                if (best > 0) st[best - 1] = 0xffffu;
+                st[best] = 0xffffu;
+                if (best + 1 < LW * DPL) st[best + 1] = 0xffffu;
+            }
+            pn_best = best; pn_minS = minS; pn_x = x;
+        }
+    };
+    auto drain_pending = [&]() {       // end of the row: the last pixel's second minimum gets its own reduction
+        if constexpr (!W3) {
+            if (pn_x >= 0) {
+                unsigned r1 = pending_local_min();
+#pragma unroll
+                for (int o = LW / 2; o > 0; o >>= 1) r1 = min(r1, __shfl_xor_sync(gmask, r1, o, LW));
+                finish_pending((int)r1);
+                pn_x = -1;
+            }
+        }
     };
     // checkpoint of the chunk that ends at xe -> L (in flight while other work runs); nothing to load at the row end
     auto fetch_ck = [&](const int xe) {
@@ -370,10 +470,10 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     auto prefetch_chunk = [&](const int xs) {    // bring C and Sv of chunk [xs, xs+K) towards L2
 #if ROWS_PF2
         if (active && xs + gl < a.W1 && gl < ROW_K) {
-            if (ROWS_PF2 & 1) prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL);
+            if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL);
             if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL);
             if (a.Dp > 64) {
-                if (ROWS_PF2 & 1) prefetch_l2_keep(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
+                if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
                 if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
             }
         }
@@ -384,65 +484,51 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
         prefetch_chunk(r0);
         start_from_ck(r0);
         for (int x = r0 - 1; x >= 0; x--) {
-            if (active) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_last);
-            stepb(x, 0, CA);
+            ldC(x, X2);
+            stepb(x, 0, X2);
         }
         __syncwarp();
-        if (r0 < a.W1) {   // set up chunk 1: its checkpoint and its first <- column
+        if (r0 < a.W1) {   // set up chunk 1: its checkpoint and its first two <- columns
             fetch_ck(r0 + ROW_K);
-            if (active) load_regs_pol<NR>(Crow + (size_t)(r0 + ROW_K - 1) * a.Dp, CB, pol_last);
+            ldC(r0 + ROW_K - 1, X0);
+            ldC(r0 + ROW_K - 2, X1);
         }
         for (int x = 0; x < r0; x++) {
-            if (active) {
-                load_regs_pol<NR>(Crow + (size_t)x * a.Dp, CA, pol_first);
-                load_regs_pol<NR>(Srow + (size_t)x * a.Dp, SA, pol_first);
-            }
-            stepf(x, 0, CA, SA);
+            ldS(x, X2);
+            stepf(x, 0, X2);
         }
         __syncwarp();
-#pragma unroll
-        for (int j = 0; j < NR; j++) CA[j] = CB[j];
     }
     for (int xs = r0; xs < a.W1; xs += ROW_K) {
-        // full chunk [xs, xe): CA = C(xe-1) and L = checkpoint(xe) were requested one phase ago
+        // full chunk [xs, xe): X0 = C(xe-1), X1 = C(xe-2) and L = checkpoint(xe) were requested a phase ago
         const int xe = xs + ROW_K;
         start_from_ck(xe);
         prefetch_chunk(xe);
-#pragma unroll 1   // keep the code small: the body inlines two full steps already
-        for (int i = 0; i < ROW_K; i += 2) {
+#pragma unroll 1   // keep the code small: the body inlines three full steps already
+        for (int i = 0; i < ROW_K; i += 3) {
             const int x = xe - 1 - i;
-            if (active) load_regs_pol<NR>(Crow + (size_t)(x - 1) * a.Dp, CB, pol_last);
-            stepb(x, xs, CA);
-            if (active) {
-                if (i + 2 < ROW_K) load_regs_pol<NR>(Crow + (size_t)(x - 2) * a.Dp, CA, pol_last);
-                else load_regs_pol<NR>(Srow + (size_t)xs * a.Dp, SA, pol_first);   // first -> column: Sv; its C is CB
-            }
-            stepb(x - 1, xs, CB);
+            ldC(x - 2, X2);
+            stepb(x, xs, X0);
+            if (i + 3 < ROW_K) ldC(x - 3, X0); else ldS(xs, X0);          // ... or Sv of the first -> column
+            stepb(x - 1, xs, X1);
+            if (i + 3 < ROW_K) ldC(x - 4, X1); else ldS(xs + 1, X1);
+            stepb(x - 2, xs, X2);
         }
         __syncwarp();
-#pragma unroll
-        for (int j = 0; j < NR; j++) CA[j] = CB[j];                      // C(xs), reused by the -> scan
         if (xe < a.W1) fetch_ck(xe + ROW_K);                             // L is dead until the next chunk
 #pragma unroll 1
-        for (int i = 0; i < ROW_K; i += 2) {
+        for (int i = 0; i < ROW_K; i += 3) {
             const int x = xs + i;
-            if (active) {
-                load_regs_pol<NR>(Crow + (size_t)(x + 1) * a.Dp, CB, pol_first);
-                load_regs_pol<NR>(Srow + (size_t)(x + 1) * a.Dp, SB, pol_first);
-            }
-            stepf(x, xs, CA, SA);
-            if (active) {
-                if (i + 2 < ROW_K) {
-                    load_regs_pol<NR>(Crow + (size_t)(x + 2) * a.Dp, CA, pol_first);
-                    load_regs_pol<NR>(Srow + (size_t)(x + 2) * a.Dp, SA, pol_first);
-                } else if (xe < a.W1) {
-                    load_regs_pol<NR>(Crow + (size_t)(xe + ROW_K - 1) * a.Dp, CA, pol_last);   // next chunk's first <- column
-                }
-            }
-            stepf(x + 1, xs, CB, SB);
+            ldS(x + 2, X2);
+            stepf(x, xs, X0);
+            if (i + 3 < ROW_K) ldS(x + 3, X0); else if (xe < a.W1) ldC(xe + ROW_K - 1, X0);   // ... or the next chunk's first <- columns
+            stepf(x + 1, xs, X1);
+            if (i + 3 < ROW_K) ldS(x + 4, X1); else if (xe < a.W1) ldC(xe + ROW_K - 2, X1);
+            stepf(x + 2, xs, X2);
         }
         __syncwarp();
     }
+    drain_pending();
     // ---- A.6 step 5: left-right check on the finished row, four pixels per lane in flight ------------------
     __syncwarp();
     if (valid) {
@@ -489,7 +575,13 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
 template <int LW, int NR>
 static size_t rows_smem() {
     constexpr int LINES = 128 / LW;
-    return (size_t)LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * (ROWS_STASH2 ? 2 : 1) * LW * 2 * NR * sizeof(unsigned short);
+    return (size_t)2 * LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * (ROWS_STASH2 ? 2 : 1) * LW * 2 * NR * sizeof(unsigned short);
+}
+
+template <int LW, int NR, bool PAD, bool W3>
+static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t st) {
+    cudaFuncSetAttribute(k_rows<LW, NR, PAD, W3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_rows<LW, NR, PAD, W3><<<grid, 128, smem, st>>>(a);
 }
 
 template <int LW, int NR>
@@ -497,14 +589,15 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
     constexpr int LINES = 128 / LW;
     const size_t smem = rows_smem<LW, NR>();
     const int grid = (a.nlines + LINES - 1) / LINES;
+    const bool w3 = (a.mode == B200S_MODE_SGBM_3WAY) && (8 * (a.D / 8) > 0);
     if (a.D == LW * 2 * NR) {   // no padded disparities anywhere: drop the pad clamps
-        cudaFuncSetAttribute(k_rows<LW, NR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_rows<LW, NR, false><<<grid, 128, smem, st>>>(a);
+        if (w3) launch_rows_k<LW, NR, false, true>(a, grid, smem, st);
+        else launch_rows_k<LW, NR, false, false>(a, grid, smem, st);
     } else {
         RowArgs b = a;
         b.nosat = 0;            // padded halves hold 0x7fff: their sums must keep saturating
-        cudaFuncSetAttribute(k_rows<LW, NR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_rows<LW, NR, true><<<grid, 128, smem, st>>>(b);
+        if (w3) launch_rows_k<LW, NR, true, true>(b, grid, smem, st);
+        else launch_rows_k<LW, NR, true, false>(b, grid, smem, st);
     }
 }
 
@@ -512,9 +605,9 @@ template <int LW, int NR>
 static int rows_capacity_t() {
     constexpr int LINES = 128 / LW;
     const size_t smem = rows_smem<LW, NR>();
-    cudaFuncSetAttribute(k_rows<LW, NR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_rows<LW, NR, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0, dev = 0, sms = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true, false>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     return nb * sms * LINES;

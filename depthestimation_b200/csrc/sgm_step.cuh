@@ -68,7 +68,7 @@ __device__ __forceinline__ void make_padmask(unsigned (&pm)[NR], int gl, int D) 
 // already-updated current column", 2 "d-1 neighbour of d0 is ignored". d0 = 8*floor(D/8).
 // PAD = false: every lane of the group holds only real disparities (D == LW * 2 * NR), the pad clamp is dropped.
 template <int LW, int NR, bool PAD = true>
-__device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const unsigned (&Cq)[NR],
+__device__ __forceinline__ unsigned sgm_step_core(unsigned (&L)[NR], const unsigned m, const unsigned (&Cq)[NR],
                                          const unsigned (&pm)[NR], const unsigned gmask, const int gl,
                                          const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
     unsigned up = __shfl_up_sync(gmask, L[NR - 1], 1, LW);
@@ -105,10 +105,19 @@ __device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const u
             }
         }
     }
-    unsigned mn = group_min2<LW>(local_min2<NR>(Ln), gmask);
-    m = min(mn & 0xffffu, mn >> 16);
 #pragma unroll
     for (int j = 0; j < NR; j++) L[j] = Ln[j];
+    return local_min2<NR>(Ln);   // packed (min over even d, min over odd d) of this lane; the caller reduces it
+}
+
+
+// full step: the minimum over d of the new column is reduced across the lane group here
+template <int LW, int NR, bool PAD = true>
+__device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const unsigned (&Cq)[NR],
+                                         const unsigned (&pm)[NR], const unsigned gmask, const int gl,
+                                         const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
+    const unsigned mn = group_min2<LW>(sgm_step_core<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirk, d0), gmask);
+    m = min(mn & 0xffffu, mn >> 16);
 }
 
 template <int NR>
