@@ -83,8 +83,17 @@ enum { RA_VG = 0, RA_NVG, RA_LOG, RA_NHIG, RA_VR, RA_NVR, RA_LOR, RA_NHIR, RA_CO
 #ifndef COST_MINB
 #define COST_MINB 4
 #endif
+#ifndef COST_BIAS
+#define COST_BIAS 0   // 1: negated samples are stored as (NB - v) so that the packed sums need no per-half carry
+#endif                //    handling and are plain 32-bit adds (ptxas places them on the FMA pipe); 0: VIADD.16x2. Measured: 0 is 5 % faster
+#define NB 0x1000u
+#if COST_BIAS
+#define NEG16(v) (NB - (v))
+#else
+#define NEG16(v) ((0u - (v)) & 0xffffu)
+#endif
 #ifndef COST_XT
-#define COST_XT 16          // cost columns per strip; measured on B200: 16 beats 8 and 32 (tools/exp_cost.sh)
+#define COST_XT 20          // cost columns per strip; measured on B200: 20 beats 16 (by 3 %), 24 and 32
 #endif
 
 // Compile-time geometry of one CTA. NTS = stride of the per-thread shared-memory arrays (power of two >= Dp / 2);
@@ -151,12 +160,23 @@ __device__ __forceinline__ void cost_row(const unsigned* __restrict__ sL, const 
         const unsigned vg = rv[RA_VG], nvg = rv[RA_NVG], log2_ = rv[RA_LOG], nhig = rv[RA_NHIG];
         const unsigned vr = rv[RA_VR], nvr = rv[RA_NVR], lor = rv[RA_LOR], nhir = rv[RA_NHIR];
         // c0 = max(0, u - hi2, lo2 - u); c1 = max(0, v - hi1, lo1 - v); cost = min(c0, c1)
+#if COST_BIAS
+        // every term carries the bias NB once: NB + (u - hi2), NB + (lo2 - u), ...; it is removed (with the clamp at 0)
+        // after the min. pk2(pixel) < 256 and NB = 4096, so no half ever carries into its neighbour.
+        unsigned c0 = __viaddmax_s16x2(nhig, l0.x, log2_ + l0.y);
+        unsigned c1 = __viaddmax_s16x2(vg, l0.w, nvg + l0.z);
+        const unsigned cg = __viaddmax_s16x2_relu(__vmins2(c0, c1), pk2(0x10000u - NB), 0u);
+        c0 = __viaddmax_s16x2(nhir, l1.x, lor + l1.y);
+        c1 = __viaddmax_s16x2(vr, l1.w, nvr + l1.z);
+        const unsigned cr = (__viaddmax_s16x2_relu(__vmins2(c0, c1), pk2(0x10000u - NB), 0u) >> 2) & 0x3fff3fffu;
+#else
         unsigned c0 = __viaddmax_s16x2_relu(nhig, l0.x, __vadd2(log2_, l0.y));
         unsigned c1 = __viaddmax_s16x2_relu(vg, l0.w, __vadd2(nvg, l0.z));
         const unsigned cg = __vmins2(c0, c1);
         c0 = __viaddmax_s16x2_relu(nhir, l1.x, __vadd2(lor, l1.y));
         c1 = __viaddmax_s16x2_relu(vr, l1.w, __vadd2(nvr, l1.z));
         const unsigned cr = (__vmins2(c0, c1) >> 2) & 0x3fff3fffu;
+#endif
         const unsigned pix = cg + cr;
         hs = hs + pix - pr[i % BS];
         pr[i % BS] = pix;
@@ -245,8 +265,8 @@ __global__ void __launch_bounds__(NTS, COST_MINB * 4 / ((NTS + 31) / 32)) k_cost
         const unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
         const unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
         uint4 w0, w1;
-        w0.x = pk2(g); w0.y = pk2(0u - g); w0.z = pk2(glo); w0.w = pk2(0u - ghi);
-        w1.x = pk2(rr); w1.y = pk2(0u - rr); w1.z = pk2(rlo); w1.w = pk2(0u - rhi);
+        w0.x = pk2(g); w0.y = pk2(NEG16(g)); w0.z = pk2(glo); w0.w = pk2(NEG16(ghi));
+        w1.x = pk2(rr); w1.y = pk2(NEG16(rr)); w1.z = pk2(rlo); w1.w = pk2(NEG16(rhi));
         *(uint4*)(bL + i * 8) = w0;
         *(uint4*)(bL + i * 8 + 4) = w1;
     };
@@ -258,8 +278,8 @@ __global__ void __launch_bounds__(NTS, COST_MINB * 4 / ((NTS + 31) / 32)) k_cost
             const unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
             const unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
             unsigned* v = q ? v1 : v0;
-            v[RA_VG] = g; v[RA_NVG] = (0u - g) & 0xffffu; v[RA_LOG] = glo; v[RA_NHIG] = (0u - ghi) & 0xffffu;
-            v[RA_VR] = rr; v[RA_NVR] = (0u - rr) & 0xffffu; v[RA_LOR] = rlo; v[RA_NHIR] = (0u - rhi) & 0xffffu;
+            v[RA_VG] = g; v[RA_NVG] = NEG16(g); v[RA_LOG] = glo; v[RA_NHIG] = NEG16(ghi);
+            v[RA_VR] = rr; v[RA_NVR] = NEG16(rr); v[RA_LOR] = rlo; v[RA_NHIR] = NEG16(rhi);
         }
 #pragma unroll
         for (int arr = 0; arr < RA_COUNT; arr++) bR[arr * RW + k] = v0[arr] | (v1[arr] << 16);
