@@ -14,54 +14,64 @@
 #include "common.cuh"
 
 // ------------------------------------------------------------------------------------------------
-// prefilter: one thread per pixel -> 8-byte record {g, g_lo, g_hi, r, r_lo, r_hi, 0, 0}
+// prefilter (A.1): Sobel-x clipped to [-ftzero, ftzero] + ftzero, raw sample, and their Birchfield-Tomasi half-sample
+// intervals -> 8-byte record {g, g_lo, g_hi, r, r_lo, r_hi, 0, 0}; border columns hold ftzero in both channels
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ int sobel_clip(const uint8_t* __restrict__ c, const uint8_t* __restrict__ n,
-                                          const uint8_t* __restrict__ s, int x, int W, int ftzero) {
-    if (x <= 0 || x >= W - 1) return ftzero;  // border columns: g = ftzero
-    int v = 2 * ((int)c[x + 1] - (int)c[x - 1]) + ((int)n[x + 1] - (int)n[x - 1]) + ((int)s[x + 1] - (int)s[x - 1]);
-    return min(max(v, -ftzero), ftzero) + ftzero;
-}
-__device__ __forceinline__ int raw_px(const uint8_t* __restrict__ c, int x, int W, int ftzero) {
-    return (x <= 0 || x >= W - 1) ? ftzero : (int)c[x];  // raw channel border is ftzero too
-}
-
-__global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ L, const uint8_t* __restrict__ R,
+// Four pixels per thread: the Sobel response and the raw sample are needed at x-1 .. x+4 (six columns, eight source
+// columns x-2 .. x+5 per row), each evaluated once instead of three times.
+__global__ void __launch_bounds__(128) k_prefilter(const uint8_t* __restrict__ L, const uint8_t* __restrict__ R,
                                                    int H, int W, int ftzero, uint2* __restrict__ recL,
                                                    uint2* __restrict__ recR) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y;
-    int z = blockIdx.z;  // 2*b + image
-    if (x >= W) return;
-    int b = z >> 1;
+    const int x0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int y = blockIdx.y;
+    const int z = blockIdx.z;  // 2*b + image
+    if (x0 >= W) return;
+    const int b = z >> 1;
     const uint8_t* img = ((z & 1) ? R : L) + (size_t)b * H * W;
     uint2* rec = ((z & 1) ? recR : recL) + (size_t)b * H * W;
     const uint8_t* c = img + (size_t)y * W;
     const uint8_t* n = img + (size_t)max(y - 1, 0) * W;
     const uint8_t* s = img + (size_t)min(y + 1, H - 1) * W;
-    int g0 = sobel_clip(c, n, s, x, W, ftzero);
-    int r0 = raw_px(c, x, W, ftzero);
-    int glo = g0, ghi = g0, rlo = r0, rhi = r0;
-    if (x > 0) {
-        int ga = (g0 + sobel_clip(c, n, s, x - 1, W, ftzero)) >> 1;
-        int ra = (r0 + raw_px(c, x - 1, W, ftzero)) >> 1;
-        glo = min(glo, ga); ghi = max(ghi, ga); rlo = min(rlo, ra); rhi = max(rhi, ra);
+    int cc[8], nn[8], ss[8];   // source columns x0-2 .. x0+5, clamped reads (clamped values are never used: borders give ftzero)
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const int xx = min(max(x0 - 2 + k, 0), W - 1);
+        cc[k] = c[xx]; nn[k] = n[xx]; ss[k] = s[xx];
     }
-    if (x < W - 1) {
-        int gb = (g0 + sobel_clip(c, n, s, x + 1, W, ftzero)) >> 1;
-        int rb = (r0 + raw_px(c, x + 1, W, ftzero)) >> 1;
-        glo = min(glo, gb); ghi = max(ghi, gb); rlo = min(rlo, rb); rhi = max(rhi, rb);
+    int g[6], r[6];            // columns x0-1 .. x0+4
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        const int x = x0 - 1 + k;
+        const bool border = (x <= 0 || x >= W - 1);
+        const int v = 2 * (cc[k + 2] - cc[k]) + (nn[k + 2] - nn[k]) + (ss[k + 2] - ss[k]);
+        g[k] = border ? ftzero : min(max(v, -ftzero), ftzero) + ftzero;
+        r[k] = border ? ftzero : cc[k + 1];
     }
-    uint2 o;
-    o.x = (unsigned)g0 | ((unsigned)glo << 8) | ((unsigned)ghi << 16) | ((unsigned)r0 << 24);
-    o.y = (unsigned)rlo | ((unsigned)rhi << 8);
-    rec[(size_t)y * W + x] = o;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = x0 + k;
+        if (x >= W) break;
+        const int g0 = g[k + 1], r0 = r[k + 1];
+        int glo = g0, ghi = g0, rlo = r0, rhi = r0;
+        if (x > 0) {
+            const int ga = (g0 + g[k]) >> 1, ra = (r0 + r[k]) >> 1;
+            glo = min(glo, ga); ghi = max(ghi, ga); rlo = min(rlo, ra); rhi = max(rhi, ra);
+        }
+        if (x < W - 1) {
+            const int gb = (g0 + g[k + 2]) >> 1, rb = (r0 + r[k + 2]) >> 1;
+            glo = min(glo, gb); ghi = max(ghi, gb); rlo = min(rlo, rb); rhi = max(rhi, rb);
+        }
+        uint2 o;
+        o.x = (unsigned)g0 | ((unsigned)glo << 8) | ((unsigned)ghi << 16) | ((unsigned)r0 << 24);
+        o.y = (unsigned)rlo | ((unsigned)rhi << 8);
+        rec[(size_t)y * W + x] = o;
+    }
 }
 
 void launch_prefilter(const Eff& e, const uint8_t* L, const uint8_t* R, int B, uint2* recL, uint2* recR,
                       cudaStream_t st) {
-    dim3 grid((e.W + 255) / 256, e.H, 2 * B);
-    k_prefilter<<<grid, 256, 0, st>>>(L, R, e.H, e.W, e.ftzero, recL, recR);
+    dim3 grid((e.W + 511) / 512, e.H, 2 * B);
+    k_prefilter<<<grid, 128, 0, st>>>(L, R, e.H, e.W, e.ftzero, recL, recR);
 }
 
 // ------------------------------------------------------------------------------------------------
