@@ -4,7 +4,7 @@
 // postprocess.filter_speckles (depthlib/postprocess.py:6-35).
 //
 // Tiled union-find: (A) each CTA labels a 64x16 tile entirely in shared memory (horizontal runs by
-// pointer jumping, vertical links by shared-memory atomicMin, redundant links skipped), and writes
+// warp ballot, vertical links by shared-memory atomicMin, redundant links skipped), and writes
 // per pixel the global index of its tile-local root plus, at roots, the local component size;
 // (B) only tile-border pixels link across tiles in global memory; (C) tile-local roots add their
 // size to the global root; (D) every pixel looks its root's size up. The result does not depend on
@@ -48,22 +48,22 @@ __global__ void __launch_bounds__(256) k_ccl_tile(const int16_t* __restrict__ im
         cnt[p] = 0;
     }
     __syncthreads();
-    // horizontal runs: parent = left neighbour if joined
-    for (int p = threadIdx.x; p < TH * TW; p += 256) {
-        int lx = p % TW, ly = p / TW;
-        par[p] = (lx > 0 && joined(val[ly][lx], val[ly][lx - 1], newVal, maxDiff)) ? p - 1 : p;
+    // horizontal runs: a warp covers 32 consecutive pixels of a row, so the start of a pixel's run inside that
+    // segment comes from one ballot ("joined to the left neighbour") and a count-leading-zeros; a run that reaches
+    // the segment start continues through that pixel's own link to the previous segment (chain of length 2)
+    static_assert(TW % 32 == 0 && (TH * TW) % 256 == 0, "tile layout");
+#pragma unroll
+    for (int k = 0; k < TH * TW / 256; k++) {
+        const int p = threadIdx.x + 256 * k;
+        const int lx = p % TW, ly = p / TW, lane = threadIdx.x & 31;
+        const bool jl = lx > 0 && joined(val[ly][lx], val[ly][lx - 1], newVal, maxDiff);
+        const unsigned bits = __ballot_sync(0xffffffffu, jl);
+        const unsigned zeros = ~bits & (0xffffffffu >> (31 - lane));      // run starts at or below this lane
+        // no start in the segment (lane 0 is joined to the previous segment): hang on lane 0, which links to p - 1
+        const int start = zeros ? 31 - __clz(zeros) : 0;
+        par[p] = (lane == 0) ? (jl ? p - 1 : p) : p - lane + start;
     }
     __syncthreads();
-#pragma unroll
-    for (int it = 0; it < 6; it++) {  // pointer jumping: 2^6 = TW
-        int np[TH * TW / 256];
-#pragma unroll
-        for (int k = 0; k < TH * TW / 256; k++) { int p = threadIdx.x + 256 * k; np[k] = par[par[p]]; }
-        __syncthreads();
-#pragma unroll
-        for (int k = 0; k < TH * TW / 256; k++) par[threadIdx.x + 256 * k] = np[k];
-        __syncthreads();
-    }
     // vertical links; skipped when the left neighbour pair already carries the same link
     for (int p = threadIdx.x; p < TH * TW; p += 256) {
         int lx = p % TW, ly = p / TW;
@@ -154,6 +154,7 @@ __global__ void __launch_bounds__(256) k_ccl_apply(int16_t* img, size_t n, int n
     if (i >= n) return;
     int l = lab[i];
     if (l < 0) return;
+    if (sizes[l] > maxSize) return;   // the tile-local part alone is big enough: the component stays (most pixels end here)
     int r = uf_find(lab, l);
     if (sizes[r] <= maxSize) img[i] = (int16_t)newVal;
 }
