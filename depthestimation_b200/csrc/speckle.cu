@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(256) k_ccl_tile(const int16_t* __restrict__ im
     // segment comes from one ballot ("joined to the left neighbour") and a count-leading-zeros; a run that reaches
     // the segment start continues through that pixel's own link to the previous segment (chain of length 2)
     static_assert(TW % 32 == 0 && (TH * TW) % 256 == 0, "tile layout");
+    int piece[TH * TW / 256];   // > 0: this pixel starts a run piece of that many valid pixels inside its 32-pixel segment
 #pragma unroll
     for (int k = 0; k < TH * TW / 256; k++) {
         const int p = threadIdx.x + 256 * k;
@@ -62,6 +63,9 @@ __global__ void __launch_bounds__(256) k_ccl_tile(const int16_t* __restrict__ im
         // no start in the segment (lane 0 is joined to the previous segment): hang on lane 0, which links to p - 1
         const int start = zeros ? 31 - __clz(zeros) : 0;
         par[p] = (lane == 0) ? (jl ? p - 1 : p) : p - lane + start;
+        const unsigned above = (lane == 31) ? 0u : (~bits & (0xffffffffu << (lane + 1)));   // run starts above this lane
+        const int len = (above ? __ffs(above) - 1 : 32) - lane;
+        piece[k] = ((lane == 0 || !jl) && val[ly][lx] != newVal) ? len : 0;
     }
     __syncthreads();
     // vertical links; skipped when the left neighbour pair already carries the same link
@@ -84,12 +88,10 @@ __global__ void __launch_bounds__(256) k_ccl_tile(const int16_t* __restrict__ im
         int lx = p % TW, ly = p / TW;
         root[k] = (val[ly][lx] != newVal) ? uf_find(par, p) : -1;
     }
-    // local component sizes, warp-aggregated
+    // local component sizes: one shared-memory atomic per run piece
 #pragma unroll
-    for (int k = 0; k < TH * TW / 256; k++) {
-        unsigned peers = __match_any_sync(0xffffffffu, root[k]);
-        if (root[k] >= 0 && (threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&cnt[root[k]], __popc(peers));
-    }
+    for (int k = 0; k < TH * TW / 256; k++)
+        if (piece[k] > 0) atomicAdd(&cnt[root[k]], piece[k]);
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < TH * TW / 256; k++) {
