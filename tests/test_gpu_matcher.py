@@ -124,3 +124,49 @@ def test_invalid_params(engine):
         engine.configure(block_size=4)
     with pytest.raises(ValueError):
         engine.configure(block_size=13)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_max_disparity_range(engine, mode):
+    """numDisparities = 256 (the engine's limit, BASELINE configs #3 / #5) against the oracle."""
+    L, R, _ = make_pair(72, 640, 256, seed=77)
+    _check(engine, L, R, stages=False, min_disp=0, num_disp=256, block_size=5, sgbm_mode=mode)
+    L, R, _ = make_pair(40, 420, 200, seed=78)          # D between the 128- and 256-wide lane layouts
+    _check(engine, L, R, stages=False, min_disp=0, num_disp=200, block_size=3, sgbm_mode=mode)
+
+
+def test_baseline_config_shapes_vs_oracle(engine):
+    """BASELINE.json configs at their own sizes where the CPU oracle finishes in seconds:
+    #1 example_stereo after its 0.5 downscale (994x1482, D=140, sgbm_3way) and #4 video frames (720x1280, D=128, sgbm_3way)."""
+    for (H, W, D, seed) in [(994, 1482, 140, 1001), (720, 1280, 128, 1004)]:
+        L, R, _ = make_pair(H, W, D, seed=seed)
+        _check(engine, L, R, stages=False, min_disp=0, num_disp=D, block_size=5, sgbm_mode="sgbm_3way")
+
+
+def _flows_agree(engine, H, W, D, mode, seed):
+    """Size-independent property for shapes the scalar oracle cannot do in seconds: the product flow (cluster kernel +
+    fused row kernel, S never materialised) and the debug flow (one generic kernel per direction + a selection kernel
+    on the full S, each diffed against the oracle stage by stage at small sizes) are two implementations of the same
+    spec and must give the same int16 image; plus the invariants of A.6/A.8 on the result."""
+    L, R, _ = make_pair(H, W, D, seed=seed)
+    engine.configure(min_disp=0, num_disp=D, block_size=5, sgbm_mode=mode)
+    engine.set_debug_flow(False)
+    a = engine.compute(L, R)
+    again = engine.compute(L, R)
+    engine.set_debug_flow(True)
+    b = engine.compute(L, R)
+    engine.set_debug_flow(False)
+    assert np.array_equal(a, again), "not deterministic"
+    assert np.array_equal(a, b), f"{(a != b).sum()} px differ between the fused and the generic flow"
+    assert np.all(a[:, :D] == -16), "columns without a full disparity range must be invalid"
+    valid = a[a != -16]
+    assert valid.size > 0.5 * H * (W - D)
+    assert valid.min() >= 0 and valid.max() <= (D - 1) * 16
+
+
+def test_full_size_1080p_hh_d256(engine):
+    _flows_agree(engine, 1080, 1920, 256, "hh", 1003)          # BASELINE config #3
+
+
+def test_full_size_4k_d256(engine):
+    _flows_agree(engine, 2160, 3840, 256, "sgbm", 1005)        # BASELINE config #5 (one pair of the 64)
