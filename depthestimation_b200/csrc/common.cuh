@@ -7,7 +7,7 @@
 // Data layout in HBM (per handle, batch-major):
 //   images        u8   [B][H][W]
 //   prefilter rec u8x8 [2][B][H][W]   {g, g_lo, g_hi, r, r_lo, r_hi, 0, 0}  (A.1 + A.2 intervals)
-//   C, S volumes  u16  [B][H][W1][Dp] d fastest, Dp = round_up(D, 8); C holds the block cost
+//   C, S volumes  u16  [B][H][W1][Dp] d fastest, Dp = round_up(D, 8), or round_up(D, 16) when D > 64; C holds the block cost
 //                                      WITHOUT the reference's +P2 (added back only for debug taps)
 //   disparity     s16  [B][H][W]
 // All volume values are in [0, 32767], so packed u16x2 arithmetic (VIMNMX.U16x2, VIMNMX3.U16x2,
@@ -37,7 +37,8 @@ static inline Eff make_eff(const B200sParams& p, int H, int W) {
     Eff e;
     e.minD = p.minDisparity;
     e.D = p.numDisparities;
-    e.Dp = (e.D + 7) & ~7;
+    // pitch of the d axis: whole 8-d lanes up to 64 disparities, whole 16-d lanes beyond (a lane never straddles the pitch)
+    e.Dp = (e.D > 64) ? ((e.D + 15) & ~15) : ((e.D + 7) & ~7);
     e.maxD = e.minD + e.D;
     e.bs = p.blockSize > 0 ? p.blockSize : 5;
     e.SW2 = e.SH2 = e.bs / 2;

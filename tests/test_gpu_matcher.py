@@ -131,8 +131,10 @@ def test_max_disparity_range(engine, mode):
     """numDisparities = 256 (the engine's limit, BASELINE configs #3 / #5) against the oracle."""
     L, R, _ = make_pair(72, 640, 256, seed=77)
     _check(engine, L, R, stages=False, min_disp=0, num_disp=256, block_size=5, sgbm_mode=mode)
-    L, R, _ = make_pair(40, 420, 200, seed=78)          # D between the 128- and 256-wide lane layouts
-    _check(engine, L, R, stages=False, min_disp=0, num_disp=200, block_size=3, sgbm_mode=mode)
+    # D between the lane layouts, incl. round_up(D, 8) % 16 == 8 (a 16-disparity lane must not straddle the pitch)
+    for D, seed in [(200, 78), (136, 79), (72, 80), (66, 81)]:
+        L, R, _ = make_pair(40, 420, D, seed=seed)
+        _check(engine, L, R, min_disp=0, num_disp=D, block_size=3, sgbm_mode=mode)
 
 
 def test_baseline_config_shapes_vs_oracle(engine):
