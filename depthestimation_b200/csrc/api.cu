@@ -5,7 +5,10 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <math.h>
+
 #include <new>
+#include <vector>
 
 #include "common.cuh"
 
@@ -490,6 +493,60 @@ int b200s_bgr2gray(B200sHandle* h, const uint8_t* img, int H, int W, size_t stri
     CUDA_TRY(h, cudaMemcpyAsync(gray, h->imgL.p, n, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));
     return check_launch(h, "bgr2gray");
+}
+
+// DecimateAlpha table of one axis, exactly as the reference's dependency builds it (double precision on the host)
+static void area_table(int ssize, int dsize, std::vector<int>& ofs, std::vector<int2>& taps) {
+    const double scale = (double)ssize / dsize;
+    ofs.clear(); taps.clear();
+    auto push = [&](int si, double w) { float f = (float)w; int2 t; t.x = si; memcpy(&t.y, &f, 4); taps.push_back(t); };
+    for (int d = 0; d < dsize; d++) {
+        const double f1 = d * scale, f2 = f1 + scale;
+        const double cell = scale < ssize - f1 ? scale : ssize - f1;
+        int s1 = (int)ceil(f1), s2 = (int)floor(f2);
+        if (s2 > ssize - 1) s2 = ssize - 1;
+        if (s1 > s2) s1 = s2;
+        ofs.push_back((int)taps.size());
+        if (s1 - f1 > 1e-3) push(s1 - 1, (s1 - f1) / cell);
+        for (int sx = s1; sx < s2; sx++) push(sx, 1.0 / cell);
+        if (f2 - s2 > 1e-3) { double t = f2 - s2; if (t > 1.0) t = 1.0; if (t > cell) t = cell; push(s2, t / cell); }
+    }
+    ofs.push_back((int)taps.size());
+}
+
+int b200s_resize_area_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int cn, size_t stride, uint8_t* dst, int dH, int dW) {
+    if (!h) return B200S_E_INVALID;
+    if (!src || !dst || sH <= 0 || sW <= 0 || dH <= 0 || dW <= 0 || (cn != 1 && cn != 3) || stride < (size_t)cn * sW) { h->set_error(B200S_E_INVALID, "resize_area: bad arguments"); return B200S_E_INVALID; }
+    if (dH > sH || dW > sW) { h->set_error(B200S_E_INVALID, "resize_area: only shrinking is supported (%dx%d -> %dx%d)", sW, sH, dW, dH); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const size_t ns = (size_t)sH * sW * cn, nd = (size_t)dH * dW * cn;
+    CUDA_TRY(h, h->hostio.ensure(ns));
+    CUDA_TRY(h, h->imgL.ensure(nd));
+    CUDA_TRY(h, cudaMemcpy2DAsync(h->hostio.p, (size_t)cn * sW, src, stride, (size_t)cn * sW, sH, cudaMemcpyHostToDevice, h->stream));
+    const int ix = sW / dW, iy = sH / dH;
+    if (ix * dW == sW && iy * dH == sH) {
+        launch_resize_area_int(h->hostio.as<uint8_t>(), sW, cn, ix, iy, h->imgL.as<uint8_t>(), dH, dW, h->stream);
+    } else {
+        std::vector<int> xo, yo; std::vector<int2> xt, yt;
+        area_table(sW, dW, xo, xt);
+        area_table(sH, dH, yo, yt);
+        const size_t bx = xo.size() * 4, by = yo.size() * 4, tx = xt.size() * 8, ty = yt.size() * 8;
+        auto al = [](size_t v) { return (v + 15) & ~(size_t)15; };
+        CUDA_TRY(h, h->imgR.ensure(al(bx) + al(by) + al(tx) + al(ty)));
+        char* base = h->imgR.as<char>();
+        int* dxo = (int*)base; int* dyo = (int*)(base + al(bx));
+        int2* dxt = (int2*)(base + al(bx) + al(by)); int2* dyt = (int2*)(base + al(bx) + al(by) + al(tx));
+        CUDA_TRY(h, cudaMemcpyAsync(dxo, xo.data(), bx, cudaMemcpyHostToDevice, h->stream));
+        CUDA_TRY(h, cudaMemcpyAsync(dyo, yo.data(), by, cudaMemcpyHostToDevice, h->stream));
+        CUDA_TRY(h, cudaMemcpyAsync(dxt, xt.data(), tx, cudaMemcpyHostToDevice, h->stream));
+        CUDA_TRY(h, cudaMemcpyAsync(dyt, yt.data(), ty, cudaMemcpyHostToDevice, h->stream));
+        CUDA_TRY(h, cudaStreamSynchronize(h->stream));     // the host vectors go out of scope below
+        launch_resize_area_tab(h->hostio.as<uint8_t>(), sW, cn, dxo, dxt, dyo, dyt, h->imgL.as<uint8_t>(), dH, dW, h->stream);
+    }
+    h->launches++;
+    CUDA_TRY(h, cudaMemcpyAsync(dst, h->imgL.p, nd, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "resize_area");
 }
 
 int b200s_remap_u8(B200sHandle* h, const uint8_t* L, const uint8_t* R, int srcH, int srcW, size_t stride, uint8_t* outL, uint8_t* outR) {

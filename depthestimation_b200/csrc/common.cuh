@@ -128,4 +128,7 @@ void launch_crop_s16(const int16_t* d16, int B, int H, int W, int x0, int16_t* o
 void launch_median3_f32_depth(const float* src, float* dst, int B, int H, int W, const B200sDepthParams& dp, float* Z, cudaStream_t st);
 void launch_median3_f32(const float* src, float* dst, int B, int H, int W, cudaStream_t st);
 void launch_depth(const float* disp, size_t n, const B200sDepthParams& dp, float* Z, cudaStream_t st);
+void launch_resize_area_int(const uint8_t* src, int sW, int cn, int ix, int iy, uint8_t* dst, int dH, int dW, cudaStream_t st);
+void launch_resize_area_tab(const uint8_t* src, int sW, int cn, const int* xo, const int2* xt, const int* yo, const int2* yt,
+                            uint8_t* dst, int dH, int dW, cudaStream_t st);
 void launch_debug_volume(const uint16_t* V, int H, int W1, int Dp, int D, int add, int16_t* out, cudaStream_t st);

@@ -250,3 +250,52 @@ void launch_debug_volume(const uint16_t* V, int H, int W1, int Dp, int D, int ad
     size_t npx = (size_t)H * W1;
     k_debug_volume<<<(unsigned)((npx * D + 255) / 256), 256, 0, st>>>(V, npx, Dp, D, add, out);
 }
+
+// ---- input preparation: cv2.resize(..., INTER_AREA), shrinking (depthlib/input.py:39-43, threaded_stereo.py:41-46) --
+// Integer factors ("area fast"): 2 x 2 -> (sum + 2) >> 2, else rint(sum * (float)(1 / area)). Otherwise the weighted
+// tables built on the host (double precision, as the reference's dependency does): row value = sum_x S * alpha in
+// float32 in table order, pixel = sum_y beta * row value, rint, clamp. No FMA anywhere (--fmad=false + explicit _rn).
+__global__ void __launch_bounds__(256) k_resize_area_int(const uint8_t* __restrict__ src, int sW, int cn, int ix, int iy,
+                                                         float scale, uint8_t* __restrict__ dst, int dH, int dW) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)dH * dW * cn) return;
+    const int c = (int)(i % cn), x = (int)((i / cn) % dW), y = (int)(i / ((size_t)cn * dW));
+    int sum = 0;
+    for (int j = 0; j < iy; j++) {
+        const uint8_t* r = src + ((size_t)(y * iy + j) * sW + (size_t)x * ix) * cn + c;
+        for (int k = 0; k < ix; k++) sum += r[(size_t)k * cn];
+    }
+    int v = (ix == 2 && iy == 2) ? (sum + 2) >> 2 : __float2int_rn(__fmul_rn((float)sum, scale));
+    dst[i] = (uint8_t)min(max(v, 0), 255);
+}
+__global__ void __launch_bounds__(256) k_resize_area_tab(const uint8_t* __restrict__ src, int sW, int cn,
+                                                         const int* __restrict__ xo, const int2* __restrict__ xt,
+                                                         const int* __restrict__ yo, const int2* __restrict__ yt,
+                                                         uint8_t* __restrict__ dst, int dH, int dW) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)dH * dW * cn) return;
+    const int c = (int)(i % cn), x = (int)((i / cn) % dW), y = (int)(i / ((size_t)cn * dW));
+    const int x0 = xo[x], x1 = xo[x + 1], y0 = yo[y], y1 = yo[y + 1];
+    float sum = 0.f;
+    for (int j = y0; j < y1; j++) {
+        const int2 ty = yt[j];                               // {source row, weight bits}
+        const uint8_t* r = src + (size_t)ty.x * sW * cn + c;
+        float buf = 0.f;
+        for (int k = x0; k < x1; k++) {
+            const int2 tx = xt[k];
+            buf = __fadd_rn(buf, __fmul_rn((float)r[(size_t)tx.x * cn], __int_as_float(tx.y)));
+        }
+        const float t = __fmul_rn(__int_as_float(ty.y), buf);
+        sum = (j == y0) ? t : __fadd_rn(sum, t);
+    }
+    dst[i] = (uint8_t)min(max(__float2int_rn(sum), 0), 255);
+}
+void launch_resize_area_int(const uint8_t* src, int sW, int cn, int ix, int iy, uint8_t* dst, int dH, int dW, cudaStream_t st) {
+    const size_t n = (size_t)dH * dW * cn;
+    k_resize_area_int<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, sW, cn, ix, iy, (float)(1.0 / (ix * iy)), dst, dH, dW);
+}
+void launch_resize_area_tab(const uint8_t* src, int sW, int cn, const int* xo, const int2* xt, const int* yo, const int2* yt,
+                            uint8_t* dst, int dH, int dW, cudaStream_t st) {
+    const size_t n = (size_t)dH * dW * cn;
+    k_resize_area_tab<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, sW, cn, xo, xt, yo, yt, dst, dH, dW);
+}

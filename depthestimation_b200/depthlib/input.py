@@ -13,10 +13,12 @@ def _cv2():
 
 
 def _area_downscale(img: np.ndarray, factor: float) -> np.ndarray:
+    """cv2.resize(img, (int(W * f), int(H * f)), INTER_AREA) of input.py:39-43 / threaded_stereo.py:41-46, on the GPU
+    (b200s_resize_area_u8, bit-exact). The reference only ever shrinks here (0 < factor <= 1)."""
     if factor == 1.0:
         return img
-    cv2 = _cv2()
-    return cv2.resize(img, (int(img.shape[1] * factor), int(img.shape[0] * factor)), interpolation=cv2.INTER_AREA)
+    from ..engine import thread_engine
+    return thread_engine().resize_area(img, (int(img.shape[1] * factor), int(img.shape[0] * factor)))
 
 
 def load_stereo_pair(left_image_path, right_image_path, downscale_factor=1.0):

@@ -8,13 +8,14 @@ arithmetic on the GPU. Device-resident batch calls take integer device pointers 
 from __future__ import annotations
 
 import ctypes as C
+import threading
 
 import numpy as np
 
 from . import _lib
 from ._lib import B200sDepthParams, B200sParams, B200sPostParams, MODES
 
-__all__ = ["StereoEngine", "EngineError", "make_params", "make_post_params", "make_depth_params"]
+__all__ = ["StereoEngine", "EngineError", "make_params", "make_post_params", "make_depth_params", "thread_engine"]
 
 
 class EngineError(RuntimeError):
@@ -66,6 +67,22 @@ def _pair(left, right):
     if left.strides != right.strides:
         left, right = np.ascontiguousarray(left), np.ascontiguousarray(right)
     return left, right
+
+
+_tls = threading.local()
+
+
+def thread_engine(device: int = 0) -> "StereoEngine":
+    """One lazily created engine per (thread, device) for the stateless image ops (gray, INTER_AREA downscale) that
+    the reference issues as free cv2 calls (input.py:39-43, threaded_stereo.py:41-46): a handle owns a stream and
+    scratch, so it is not shared between threads."""
+    cache = getattr(_tls, "engines", None)
+    if cache is None:
+        cache = _tls.engines = {}
+    e = cache.get(device)
+    if e is None:
+        e = cache[device] = StereoEngine(device)
+    return e
 
 
 class StereoEngine:
@@ -159,6 +176,19 @@ class StereoEngine:
         out = np.empty((H, W), np.uint8)
         self._check(self._lib.b200s_bgr2gray(self._h, img.ctypes.data, H, W, img.strides[0], out.ctypes.data),
                     "b200s_bgr2gray")
+        return out
+
+    def resize_area(self, img, dsize):
+        """== cv2.resize(img, (dW, dH), interpolation=cv2.INTER_AREA) for uint8 HxW or HxWx3, shrinking only."""
+        img = np.asarray(img)
+        if img.dtype != np.uint8 or img.ndim not in (2, 3) or (img.ndim == 3 and img.shape[2] not in (1, 3)):
+            raise ValueError("resize_area expects a uint8 HxW or HxWx3 image")
+        img = np.ascontiguousarray(img)
+        cn = 1 if img.ndim == 2 else img.shape[2]
+        dW, dH = int(dsize[0]), int(dsize[1])
+        out = np.empty((dH, dW) if img.ndim == 2 else (dH, dW, cn), np.uint8)
+        self._check(self._lib.b200s_resize_area_u8(self._h, img.ctypes.data, img.shape[0], img.shape[1], cn,
+                                                   img.strides[0], out.ctypes.data, dH, dW), "b200s_resize_area_u8")
         return out
 
     def remap(self, left, right):

@@ -114,6 +114,12 @@ int b200s_set_maps(B200sHandle* h, const float* map1_L, const float* map2_L,
 /* cv2.cvtColor(img, COLOR_BGR2GRAY) at depthlib/rectify.py:116, stereo_core.py:157-159. */
 int b200s_bgr2gray(B200sHandle* h, const uint8_t* img, int H, int W, size_t stride, uint8_t* gray);
 
+/* cv2.resize(img, (dW, dH), interpolation=cv2.INTER_AREA) at depthlib/input.py:39-43 and
+ * depthlib/threaded_stereo.py:41-46 (the downscale_factor input prep): uint8, cn = 1 or 3 interleaved channels,
+ * shrinking only (dH <= sH, dW <= sW; anything else is B200S_E_INVALID). dst is dense dH x dW x cn. */
+int b200s_resize_area_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int cn, size_t stride,
+                         uint8_t* dst, int dH, int dW);
+
 /* 2x cv2.remap(gray, map1, map2, INTER_LINEAR) at depthlib/rectify.py:185-186. Source images
  * are srcH x srcW; outputs have the size of the maps (dense). */
 int b200s_remap_u8(B200sHandle* h, const uint8_t* L, const uint8_t* R, int srcH, int srcW,

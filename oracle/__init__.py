@@ -149,6 +149,23 @@ def bgr2gray(img: np.ndarray) -> np.ndarray:
     return out
 
 
+def resize_area(img: np.ndarray, dsize) -> np.ndarray:
+    """cv2.resize(img, (dW, dH), interpolation=cv2.INTER_AREA) for uint8 [H,W] or [H,W,C], shrinking only
+    (depthlib/input.py:39-43)."""
+    img = np.ascontiguousarray(img, np.uint8)
+    dW, dH = int(dsize[0]), int(dsize[1])
+    cn = 1 if img.ndim == 2 else img.shape[2]
+    out = np.empty((dH, dW) if img.ndim == 2 else (dH, dW, cn), np.uint8)
+    fn = lib().orc_resize_area_u8
+    fn.argtypes = [ctypes.POINTER(ctypes.c_uint8), ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                   ctypes.POINTER(ctypes.c_uint8), ctypes.c_int, ctypes.c_int]
+    fn.restype = ctypes.c_int
+    rc = fn(_p(img, ctypes.c_uint8), img.shape[0], img.shape[1], cn, _p(out, ctypes.c_uint8), dH, dW)
+    if rc:
+        raise ValueError("resize_area: only shrinking is restated (dsize must not exceed the source size)")
+    return out
+
+
 def median3_f32(a: np.ndarray) -> np.ndarray:
     a = np.ascontiguousarray(a, dtype=np.float32)
     out = np.empty_like(a)

@@ -135,3 +135,81 @@ void orc_disp_to_depth(const float *disp, size_t n, float fB, float doffs, float
         Z[i] = z;
     }
 }
+
+/* cv2.resize(src, (dW, dH), interpolation=INTER_AREA), uint8, cn interleaved channels, shrinking only
+ * (depthlib/input.py:39-43, threaded_stereo.py:41-46). Restated from the published OpenCV algorithm (imgproc resize:
+ * "area fast" for integer factors, DecimateAlpha tables otherwise) and pinned against the live binary by
+ * tests/test_oracle_vs_cv2.py:
+ *   both factors integer, 2 x 2:   (a + b + c + d + 2) >> 2
+ *   both factors integer, other:   rint( sum * (float)(1.0 / area) )               (float32 product, ties to even)
+ *   otherwise: per axis a table of (source index, float weight): with scale = ssize / dsize (double),
+ *     f1 = d * scale, f2 = f1 + scale, cell = min(scale, ssize - f1), s1 = ceil(f1), s2 = min(floor(f2), ssize - 1),
+ *     s1 = min(s1, s2); [s1 - 1: (s1 - f1) / cell if s1 - f1 > 1e-3], [s1 .. s2 - 1: 1 / cell],
+ *     [s2: min(min(f2 - s2, 1), cell) / cell if f2 - s2 > 1e-3]; row value = sum_x S * alpha accumulated in float32 in
+ *     table order, pixel = sum_y beta * row value (first term assigned, the rest added), then rint and clamp. */
+typedef struct { int si; float w; } OrcAreaTap;
+
+static int orc_area_tab(int ssize, int dsize, OrcAreaTap *tab, int *ofs)
+{
+    double scale = (double)ssize / dsize;
+    int k = 0;
+    for (int d = 0; d < dsize; d++) {
+        double f1 = d * scale, f2 = f1 + scale;
+        double cell = scale < ssize - f1 ? scale : ssize - f1;
+        int s1 = (int)ceil(f1), s2 = (int)floor(f2);
+        if (s2 > ssize - 1) s2 = ssize - 1;
+        if (s1 > s2) s1 = s2;
+        ofs[d] = k;
+        if (s1 - f1 > 1e-3) { tab[k].si = s1 - 1; tab[k].w = (float)((s1 - f1) / cell); k++; }
+        for (int s = s1; s < s2; s++) { tab[k].si = s; tab[k].w = (float)(1.0 / cell); k++; }
+        if (f2 - s2 > 1e-3) {
+            double t = f2 - s2; if (t > 1.0) t = 1.0; if (t > cell) t = cell;
+            tab[k].si = s2; tab[k].w = (float)(t / cell); k++;
+        }
+    }
+    ofs[dsize] = k;
+    return k;
+}
+
+int orc_resize_area_u8(const uint8_t *src, int sH, int sW, int cn, uint8_t *dst, int dH, int dW)
+{
+    if (dH > sH || dW > sW || dH <= 0 || dW <= 0 || cn <= 0) return -1;
+    const int ix = sW / dW, iy = sH / dH;
+    if (ix * dW == sW && iy * dH == sH) {             /* integer factors: "area fast" */
+        const int area = ix * iy;
+        const float scale = (float)(1.0 / area);
+        for (int y = 0; y < dH; y++)
+            for (int x = 0; x < dW; x++)
+                for (int c = 0; c < cn; c++) {
+                    int sum = 0;
+                    for (int j = 0; j < iy; j++)
+                        for (int i = 0; i < ix; i++) sum += src[((size_t)(y * iy + j) * sW + x * ix + i) * cn + c];
+                    int v;
+                    if (ix == 2 && iy == 2) v = (sum + 2) >> 2;
+                    else { float f = (float)sum * scale; v = (int)lrintf(f); }
+                    dst[((size_t)y * dW + x) * cn + c] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+                }
+        return 0;
+    }
+    OrcAreaTap *xt = (OrcAreaTap *)malloc(sizeof(OrcAreaTap) * (size_t)(sW + 2 * dW + 2));
+    OrcAreaTap *yt = (OrcAreaTap *)malloc(sizeof(OrcAreaTap) * (size_t)(sH + 2 * dH + 2));
+    int *xo = (int *)malloc(sizeof(int) * (size_t)(dW + 1)), *yo = (int *)malloc(sizeof(int) * (size_t)(dH + 1));
+    orc_area_tab(sW, dW, xt, xo);
+    orc_area_tab(sH, dH, yt, yo);
+    for (int y = 0; y < dH; y++)
+        for (int x = 0; x < dW; x++)
+            for (int c = 0; c < cn; c++) {
+                float sum = 0.f;
+                for (int j = yo[y]; j < yo[y + 1]; j++) {
+                    float buf = 0.f;
+                    for (int i = xo[x]; i < xo[x + 1]; i++)
+                        buf = buf + (float)src[((size_t)yt[j].si * sW + xt[i].si) * cn + c] * xt[i].w;
+                    float t = yt[j].w * buf;
+                    sum = (j == yo[y]) ? t : sum + t;
+                }
+                long v = lrintf(sum);
+                dst[((size_t)y * dW + x) * cn + c] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+            }
+    free(xt); free(yt); free(xo); free(yo);
+    return 0;
+}

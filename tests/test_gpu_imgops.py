@@ -56,6 +56,33 @@ def test_bgr2gray(engine):
     assert np.array_equal(engine.bgr2gray(img), oracle.bgr2gray(img))
 
 
+@pytest.mark.parametrize("H,W,f,cn", [(60, 90, 0.7, 3), (61, 97, 0.5, 3), (50, 83, 0.33, 1), (64, 100, 0.9, 3),
+                                       (200, 302, 0.5, 3), (201, 303, 1 / 3, 3), (200, 304, 0.25, 1),
+                                       (497, 741, 0.5, 3), (97, 131, 0.77, 1), (64, 64, 1.0, 3), (33, 40, 0.1, 3),
+                                       (1988, 2964, 0.5, 3), (1080, 1920, 2 / 3, 3)])
+def test_resize_area(engine, H, W, f, cn):
+    """INTER_AREA downscale of input.py:39-43 (2x2, integer-factor and weighted-table paths) vs the oracle, which
+    tests/test_oracle_vs_cv2.py pins to the live cv2 binary; the last two are config #1's 2964x1988 x0.5 and 1080p."""
+    rng = np.random.default_rng(H * W + cn)
+    img = rng.integers(0, 256, (H, W, cn) if cn > 1 else (H, W), dtype=np.uint8)
+    dsize = (int(W * f), int(H * f))
+    assert np.array_equal(engine.resize_area(img, dsize), oracle.resize_area(img, dsize))
+
+
+def test_resize_area_rejects_upscale(engine):
+    with pytest.raises(ValueError):
+        engine.resize_area(np.zeros((10, 10), np.uint8), (20, 20))
+
+
+def test_input_downscale_uses_gpu(engine):
+    """depthlib.input._area_downscale == the reference's cv2.resize(..., INTER_AREA) call."""
+    from depthestimation_b200.depthlib.input import _area_downscale
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, (120, 161, 3), dtype=np.uint8)
+    assert np.array_equal(_area_downscale(img, 0.5), oracle.resize_area(img, (80, 60)))
+    assert _area_downscale(img, 1.0) is img
+
+
 @pytest.mark.parametrize("name", golden_cases())
 def test_post_and_depth_golden(engine, name, golden):
     from depthestimation_b200.engine import make_post_params, make_depth_params

@@ -79,3 +79,17 @@ def test_remap_gray_median_speckle_post_depth():
         a = oracle.disp_to_depth(post, 0.8 * W, 0.54, 1.25, eps=0, max_depth=md)
         b = cr.disparity_to_depth(post, 0.8 * W, 0.54, 1.25, eps=0, max_depth=md)
         assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("H,W,f,cn", [(60, 90, 0.7, 3), (61, 97, 0.5, 3), (50, 83, 0.33, 1), (64, 100, 0.9, 3),
+                                       (200, 302, 0.5, 3), (201, 303, 1 / 3, 3), (200, 304, 0.25, 1),
+                                       (497, 741, 0.5, 3), (97, 131, 0.77, 1), (64, 64, 1.0, 3), (33, 40, 0.1, 3)])
+def test_resize_area_matches_cv2(H, W, f, cn):
+    """INTER_AREA downscale as depthlib/input.py:39-43 calls it (size = int(dim * factor)): 2x2 fast path,
+    integer-factor fast path, and the weighted-table path, uint8 gray and 3-channel."""
+    import cv2
+    rng = np.random.default_rng(H * W + cn)
+    img = rng.integers(0, 256, (H, W, cn) if cn > 1 else (H, W), dtype=np.uint8)
+    dsize = (int(W * f), int(H * f))
+    ref = cv2.resize(img, dsize, interpolation=cv2.INTER_AREA)
+    assert np.array_equal(oracle.resize_area(img, dsize), ref)
