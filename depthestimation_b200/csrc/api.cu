@@ -212,7 +212,16 @@ int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch) {
     // more than one of them (the second wave de-synchronises the phases of the CTAs: ~25 % faster per frame than a
     // single wave); beyond three waves the gain is < 3 %
     int cap = 3 * rows_capacity_lines(e) / H;
-    if (granule <= 0) { *batch = cap > 0 ? cap : 16; return B200S_OK; }
+    // never more than ~70 % of the free HBM: C and S are 2 B/cell each, the O(N) buffers about 64 B/px
+    size_t freeb = 0, totalb = 0;
+    if (cudaMemGetInfo(&freeb, &totalb) == cudaSuccess) {
+        const double per_frame = 4.0 * H * (double)e.W1 * e.Dp + 64.0 * H * W;
+        const double fit = 0.7 * (double)freeb / per_frame;
+        if (fit < cap) cap = fit < 1.0 ? 1 : (int)fit;
+    }
+    if (cap < 1) cap = 1;
+    if (granule > cap) granule = 0;
+    if (granule <= 0) { *batch = cap; return B200S_OK; }
     int b = granule;
     while (b + granule <= cap) b += granule;   // largest multiple of the cluster granule within three row-kernel waves
     *batch = b;

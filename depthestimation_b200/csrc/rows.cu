@@ -73,6 +73,15 @@ __device__ __forceinline__ void load_regs_pol(const uint16_t* p, unsigned (&r)[N
 #endif
 }
 
+// Stash layout: 16-byte unit (q, lane) at (q * LW + lane) * 8 halves, so that a lane group's vector access covers 128
+// contiguous bytes (lane-major units 32 bytes apart put lanes g and g+4 on the same banks: a 2-way conflict on every
+// stash store and load). Disparity d lives in lane d / DPL, unit (d % DPL) / 8, half d % 8.
+template <int LW, int NR>
+__device__ __forceinline__ int stash_idx(const int d) {
+    if (NR <= 4) return d;
+    return ((((d >> 3) & (NR / 4 - 1)) * LW + d / (2 * NR)) << 3) + (d & 7);
+}
+
 // ---- A.6 steps 1-4 for one pixel whose S(., d) sits in v[] across the lane group ------------------
 template <int LW, int NR, bool PAD>
 __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigned (&pm)[NR], const RowArgs& a,
@@ -95,7 +104,7 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
 #endif
 #pragma unroll
     for (int q = 0; q < NR / 4; q++)
-        *(uint4*)(stash + (gl * DPL + 8 * q)) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+        *(uint4*)(stash + (q * LW + gl) * 8) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
     int minS, best;
     if (!simd3) {
         // binary min tree over the lane's registers; the winner's position is found by walking it down
@@ -178,16 +187,18 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
     __syncwarp();                                                   // the stash is complete
     int Sm = 0, Sq = 0;
     if (gl == 0) {
-        Sm = stash[max(best - 1, 0)];
-        Sq = stash[min(best + 1, LW * DPL - 1)];
-        if (best > 0) stash[best - 1] = 0xffffu;
-        stash[best] = 0xffffu;
-        if (best + 1 < LW * DPL) stash[best + 1] = 0xffffu;
+        const int im = stash_idx<LW, NR>(max(best - 1, 0)), ib = stash_idx<LW, NR>(best);
+        const int iq = stash_idx<LW, NR>(min(best + 1, LW * DPL - 1));
+        Sm = stash[im];
+        Sq = stash[iq];
+        if (best > 0) stash[im] = 0xffffu;
+        stash[ib] = 0xffffu;
+        if (best + 1 < LW * DPL) stash[iq] = 0xffffu;
     }
     __syncwarp();
 #pragma unroll
     for (int q = 0; q < NR / 4; q++) {
-        const uint4 t = *(const uint4*)(stash + (gl * DPL + 8 * q));
+        const uint4 t = *(const uint4*)(stash + (q * LW + gl) * 8);
         e[4 * q] = t.x; e[4 * q + 1] = t.y; e[4 * q + 2] = t.z; e[4 * q + 3] = t.w;
     }
     bool reject;
@@ -245,7 +256,7 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
 template <int LW, int NR, bool PAD, bool W3>
 __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
-    constexpr int LINES = 128 / LW;                 // lines per CTA
+    const int LINES = (int)blockDim.x / LW;         // lines per CTA (128 threads for throughput, one warp per CTA when few lines are in flight)
     extern __shared__ __align__(16) uint4 rsm[];    // [LINES][ROW_K][NR/4][LW] uint4: L(<-) of the current chunk
     const int gl = threadIdx.x % LW;
     const int lic = threadIdx.x / LW;               // line in CTA
@@ -354,7 +365,7 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
         unsigned e[NR];
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
-            const uint4 t = *(const uint4*)(sp + (gl * DPL + 8 * q));
+            const uint4 t = *(const uint4*)(sp + (q * LW + gl) * 8);
             e[4 * q] = t.x; e[4 * q + 1] = t.y; e[4 * q + 2] = t.z; e[4 * q + 3] = t.w;
         }
         const unsigned me = local_min2<NR>(e);
@@ -397,7 +408,7 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             unsigned short* st = stash + (x & 1) * (LW * DPL);
 #pragma unroll
             for (int q = 0; q < NR / 4; q++)
-                *(uint4*)(st + (gl * DPL + 8 * q)) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+                *(uint4*)(st + (q * LW + gl) * 8) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
             unsigned t1[NR / 2 > 0 ? NR / 2 : 1], t2[NR / 4 > 0 ? NR / 4 : 1];
 #pragma unroll
             for (int j = 0; j < NR / 2; j++) t1[j] = umin2(w[2 * j], w[2 * j + 1]);
@@ -433,11 +444,13 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             const int best = fl * DPL + __shfl_sync(gmask, cand, fl, LW);     // lowest d reaching the minimum
             __syncwarp();                                                     // this pixel's stash is complete
             if (gl == 0) {
-                pn_Sm = st[max(best - 1, 0)];
-                pn_Sq = st[min(best + 1, LW * DPL - 1)];
-                if (best > 0) st[best - 1] = 0xffffu;
-                st[best] = 0xffffu;
-                if (best + 1 < LW * DPL) st[best + 1] = 0xffffu;
+                const int im = stash_idx<LW, NR>(max(best - 1, 0)), ib = stash_idx<LW, NR>(best);
+                const int iq = stash_idx<LW, NR>(min(best + 1, LW * DPL - 1));
+                pn_Sm = st[im];
+                pn_Sq = st[iq];
+                if (best > 0) st[im] = 0xffffu;
+                st[ib] = 0xffffu;
+                if (best + 1 < LW * DPL) st[iq] = 0xffffu;
             }
             pn_best = best; pn_minS = minS; pn_x = x;
         }
@@ -580,8 +593,16 @@ static size_t rows_smem() {
 
 template <int LW, int NR, bool PAD, bool W3>
 static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t st) {
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     cudaFuncSetAttribute(k_rows<LW, NR, PAD, W3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_rows<LW, NR, PAD, W3><<<grid, 128, smem, st>>>(a);
+    // a single frame (or a few small ones) leaves most SMs without a CTA at 128 threads: spread the lines one warp per CTA
+    if (grid < 2 * sms) {
+        constexpr int L1 = 32 / LW;
+        k_rows<LW, NR, PAD, W3><<<(a.nlines + L1 - 1) / L1, 32, smem / 4, st>>>(a);
+    } else {
+        k_rows<LW, NR, PAD, W3><<<grid, 128, smem, st>>>(a);
+    }
 }
 
 template <int LW, int NR>
