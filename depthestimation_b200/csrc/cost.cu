@@ -88,7 +88,8 @@ struct CostArgs {
 };
 
 // right-image arrays in shared memory, stored reversed in x so that increasing d walks forward
-enum { RA_VG = 0, RA_NVG, RA_LOG, RA_NHIG, RA_VR, RA_NVR, RA_LOR, RA_NHIR, RA_COUNT };
+// (the negated samples -v are not stored: lo1 - v is formed as (lo1 + 1) + ~v, one LOP3 instead of an LDS + PRMT)
+enum { RA_VG = 0, RA_LOG, RA_NHIG, RA_VR, RA_LOR, RA_NHIR, RA_COUNT };
 
 #ifndef COST_MINB
 #define COST_MINB 4
@@ -99,8 +100,10 @@ enum { RA_VG = 0, RA_NVG, RA_LOG, RA_NHIG, RA_VR, RA_NVR, RA_LOR, RA_NHIR, RA_CO
 #define NB 0x1000u
 #if COST_BIAS
 #define NEG16(v) (NB - (v))
+#define LO1 0u
 #else
 #define NEG16(v) ((0u - (v)) & 0xffffu)
+#define LO1 1u   // the left interval's lower end is stored + 1 (pairs with ~v of the right sample)
 #endif
 #ifndef COST_XT
 #define COST_XT 20          // cost columns per strip; measured on B200: 20 beats 16 (by 3 %), 24 and 32
@@ -167,8 +170,13 @@ __device__ __forceinline__ void cost_row(const unsigned* __restrict__ sL, const 
         }
         const uint4 l0 = *(const uint4*)(sL + i * 8);                 // {u, -u, lo1, -hi1} gradient channel
         const uint4 l1 = *(const uint4*)(sL + i * 8 + 4);             // raw channel
-        const unsigned vg = rv[RA_VG], nvg = rv[RA_NVG], log2_ = rv[RA_LOG], nhig = rv[RA_NHIG];
-        const unsigned vr = rv[RA_VR], nvr = rv[RA_NVR], lor = rv[RA_LOR], nhir = rv[RA_NHIR];
+        const unsigned vg = rv[RA_VG], log2_ = rv[RA_LOG], nhig = rv[RA_NHIG];
+        const unsigned vr = rv[RA_VR], lor = rv[RA_LOR], nhir = rv[RA_NHIR];
+#if COST_BIAS
+        const unsigned nvg = pk2(NB) - vg, nvr = pk2(NB) - vr;
+#else
+        const unsigned nvg = ~vg, nvr = ~vr;                          // -v - 1 per half; the left record holds lo1 + 1
+#endif
         // c0 = max(0, u - hi2, lo2 - u); c1 = max(0, v - hi1, lo1 - v); cost = min(c0, c1)
 #if COST_BIAS
         // every term carries the bias NB once: NB + (u - hi2), NB + (lo2 - u), ...; it is removed (with the clamp at 0)
@@ -275,8 +283,8 @@ __global__ void __launch_bounds__(NTS, COST_MINB * 4 / ((NTS + 31) / 32)) k_cost
         const unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
         const unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
         uint4 w0, w1;
-        w0.x = pk2(g); w0.y = pk2(NEG16(g)); w0.z = pk2(glo); w0.w = pk2(NEG16(ghi));
-        w1.x = pk2(rr); w1.y = pk2(NEG16(rr)); w1.z = pk2(rlo); w1.w = pk2(NEG16(rhi));
+        w0.x = pk2(g); w0.y = pk2(NEG16(g)); w0.z = pk2(glo + LO1); w0.w = pk2(NEG16(ghi));
+        w1.x = pk2(rr); w1.y = pk2(NEG16(rr)); w1.z = pk2(rlo + LO1); w1.w = pk2(NEG16(rhi));
         *(uint4*)(bL + i * 8) = w0;
         *(uint4*)(bL + i * 8 + 4) = w1;
     };
@@ -288,8 +296,8 @@ __global__ void __launch_bounds__(NTS, COST_MINB * 4 / ((NTS + 31) / 32)) k_cost
             const unsigned g = r.x & 255u, glo = (r.x >> 8) & 255u, ghi = (r.x >> 16) & 255u;
             const unsigned rr = r.x >> 24, rlo = r.y & 255u, rhi = (r.y >> 8) & 255u;
             unsigned* v = q ? v1 : v0;
-            v[RA_VG] = g; v[RA_NVG] = NEG16(g); v[RA_LOG] = glo; v[RA_NHIG] = NEG16(ghi);
-            v[RA_VR] = rr; v[RA_NVR] = NEG16(rr); v[RA_LOR] = rlo; v[RA_NHIR] = NEG16(rhi);
+            v[RA_VG] = g; v[RA_LOG] = glo; v[RA_NHIG] = NEG16(ghi);
+            v[RA_VR] = rr; v[RA_LOR] = rlo; v[RA_NHIR] = NEG16(rhi);
         }
 #pragma unroll
         for (int arr = 0; arr < RA_COUNT; arr++) bR[arr * RW + k] = v0[arr] | (v1[arr] << 16);

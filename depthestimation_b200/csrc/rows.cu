@@ -252,12 +252,18 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
 #define ROWS_MINB 4   // 4 CTAs (16 warps) per SM: 57 KB of shared memory each, <= 128 registers
 #endif
 
-// W3 = true: sgbm_3way (its 8-wide SIMD winner rule keeps the monolithic wta_pixel); false: pipelined winner search
-template <int LW, int NR, bool PAD, bool W3>
+// W3 = true: sgbm_3way (its 8-wide SIMD winner rule keeps the monolithic per-column wta_pixel); false: the winner of
+// every pixel of a chunk is selected AFTER the chunk's -> scan, one lane per pixel (select_chunk below).
+// NS (only read when !W3): the sum of all paths cannot reach 32768, plain adds instead of saturating ones.
+template <int LW, int NR, bool PAD, bool W3, bool NS>
 __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
+    constexpr int RPW = 32 / LW;                    // lines per warp
+    constexpr int NCH = LW * NR / 4;                // 16-byte units per pixel record (all disparities of one pixel)
+    constexpr int NPW = ROW_K * RPW;                // pixels per warp and chunk
+    constexpr int SWZ = NCH >= 8 ? 7 : NCH - 1;     // unit swizzle: record p stores logical unit c at c ^ (p & SWZ)
     const int LINES = (int)blockDim.x / LW;         // lines per CTA (128 threads for throughput, one warp per CTA when few lines are in flight)
-    extern __shared__ __align__(16) uint4 rsm[];    // [LINES][ROW_K][NR/4][LW] uint4: L(<-) of the current chunk
+    extern __shared__ __align__(16) uint4 rsm[];    // [LINES][ROW_K][NR/4][LW] uint4: L(<-), then S, of the current chunk
     const int gl = threadIdx.x % LW;
     const int lic = threadIdx.x / LW;               // line in CTA
     const int line_raw = blockIdx.x * LINES + lic;
@@ -267,8 +273,16 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     // divergence check per shuffle); ballots are shifted by gbase
     const unsigned gmask = 0xffffffffu;
     const int gbase = (threadIdx.x & 31) / LW * LW;
-    const bool active = gl * DPL < a.Dp;
-    uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;                                  // L(<-) of the current chunk
+    const int Dp = PAD ? a.Dp : LW * DPL;           // no padded disparities: the pitch is a compile-time constant
+    const bool active = gl * DPL < Dp;
+    const bool nosat = W3 ? (a.nosat != 0) : NS;
+    uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;                                  // L(<-) of the current chunk (W3)
+    // !W3: one RECORD per pixel = all its disparities (NCH units of 8), records of a warp ordered column-major
+    // (p = column-in-chunk * RPW + line-in-warp). Lane gl's q-th unit (disparities gl*DPL + 8q ..) is logical unit
+    // gl + LW*q, stored at unit ^ (p & SWZ): conflict-free both for the lane groups that write a record during the
+    // scans (8 lanes, 8 different units) and for the lanes that each read a whole record during selection.
+    uint4* Lw = rsm + (size_t)(lic / RPW) * NPW * NCH;
+    const int rw = lic % RPW;
     uint4* Cb = rsm + (size_t)(LINES + lic) * ROW_K * (NR / 4) * LW;                        // C of the current chunk
     unsigned short* stash = (unsigned short*)(rsm + (size_t)2 * LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * (ROWS_STASH2 ? 2 : 1) * LW * DPL;
 
@@ -279,9 +293,9 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     const bool tail3 = (a.mode == B200S_MODE_SGBM_3WAY) && (a.D % 8 != 0) && d0 > 0;
     const int quirkL = tail3 ? 2 : 0;               // the (x+1, y) path ignores the d-1 neighbour at d0 (A.7)
 
-    const uint16_t* Crow = a.C + (size_t)line * a.W1 * a.Dp + gl * DPL;
-    const uint16_t* Srow = a.Sv + (size_t)line * a.W1 * a.Dp + gl * DPL;
-    uint16_t* ck = a.ck + (size_t)line * a.nck * a.Dp + gl * DPL;
+    const uint16_t* Crow = a.C + (size_t)line * a.W1 * Dp + gl * DPL;
+    const uint16_t* Srow = a.Sv + (size_t)line * a.W1 * Dp + gl * DPL;
+    uint16_t* ck = a.ck + (size_t)line * a.nck * Dp + gl * DPL;
     unsigned* keys = a.keys + (size_t)line * a.W;
     int16_t* out = a.raw + (size_t)line * a.W;
 
@@ -302,33 +316,41 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
 #pragma unroll
     for (int j = 0; j < NR; j++) { X0[j] = 0u; X1[j] = 0u; X2[j] = 0u; }
     const uint64_t pol_first = l2_policy_first();
-    auto ldC = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Crow + (size_t)x * a.Dp, dst, pol_first); };
-    auto ldS = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Srow + (size_t)x * a.Dp, dst, pol_first); };
+    auto ldC = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Crow + (size_t)x * Dp, dst, pol_first); };
+    auto ldS = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Srow + (size_t)x * Dp, dst, pol_first); };
     // ---- pass 1: <- over the row down to column r0, checkpoint L at every chunk start -------------------
     sgm_reset<NR>(L, m);
     {
-        auto step1 = [&](const int x, const unsigned (&Cc)[NR]) {
-            sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
-            if ((x - r0) % ROW_K == 0 && active && valid) store_regs<NR>(ck + (size_t)((x - r0) / ROW_K + 1) * a.Dp, L);
-        };
+        // W1 - r0 is a multiple of ROW_K: the pass runs whole groups of ROW_K columns, each ending on a checkpoint
+        // column, so neither the ring position nor the checkpoint test depends on x
+        auto step1 = [&](const unsigned (&Cc)[NR]) { sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0); };
         int x = a.W1 - 1;
-        if (x >= r0) ldC(x, X0);
-        if (x - 1 >= r0) ldC(x - 1, X1);
-        for (; x - 2 >= r0; x -= 3) {
-            ldC(x - 2, X2);
-            if (active && x - ROW_PD - 2 >= r0) {
-                prefetch_l2(Crow + (size_t)(x - ROW_PD) * a.Dp);
-                prefetch_l2(Crow + (size_t)(x - ROW_PD - 1) * a.Dp);
-                prefetch_l2(Crow + (size_t)(x - ROW_PD - 2) * a.Dp);
-            }
-            step1(x, X0);
-            if (x - 3 >= r0) ldC(x - 3, X0);
-            step1(x - 1, X1);
-            if (x - 4 >= r0) ldC(x - 4, X1);
-            step1(x - 2, X2);
+        const uint16_t* pC = Crow + (size_t)x * Dp;                                   // C of column x
+        uint16_t* pck = ck + (size_t)((x - (ROW_K - 1) - r0) / ROW_K + 1) * Dp;       // checkpoint of the group that starts at x
+        if (x >= r0 && active) {
+            load_regs_pol<NR>(pC, X0, pol_first);
+            load_regs_pol<NR>(pC - Dp, X1, pol_first);
         }
-        if (x >= r0) step1(x, X0);
-        if (x - 1 >= r0) step1(x - 1, X1);
+        for (; x >= r0; x -= ROW_K, pC -= (size_t)ROW_K * Dp, pck -= Dp) {
+            const bool more = x - ROW_K >= r0;                                        // another group follows
+#pragma unroll
+            for (int i = 0; i < ROW_K; i += 3) {
+                if (active) {
+                    load_regs_pol<NR>(pC - (size_t)(i + 2) * Dp, X2, pol_first);
+                    if (x - i - ROW_PD - 2 >= r0) {
+                        prefetch_l2(pC - (size_t)(i + ROW_PD) * Dp);
+                        prefetch_l2(pC - (size_t)(i + ROW_PD + 1) * Dp);
+                        prefetch_l2(pC - (size_t)(i + ROW_PD + 2) * Dp);
+                    }
+                }
+                step1(X0);
+                if (active && (i + 3 < ROW_K || more)) load_regs_pol<NR>(pC - (size_t)(i + 3) * Dp, X0, pol_first);
+                step1(X1);
+                if (active && (i + 3 < ROW_K || more)) load_regs_pol<NR>(pC - (size_t)(i + 4) * Dp, X1, pol_first);
+                step1(X2);
+            }
+            if (active && valid) store_regs<NR>(pck, L);
+        }
     }
     __syncwarp();
     // ---- pass 2: chunk by chunk, left to right ------------------------------------------------------
@@ -337,39 +359,14 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     sgm_reset<NR>(Lr, mr);
     auto stepb = [&](const int x, const int xs, const unsigned (&Cc)[NR]) {     // one <- step; L and C kept for the -> scan
         sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
+        const int pix = (x - xs) * RPW + rw;
+        uint4* rec = Lw + pix * NCH + (gl ^ (pix & SWZ));
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
-            Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+            if constexpr (W3) Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+            else rec[q * LW] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
             Cb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(Cc[4 * q], Cc[4 * q + 1], Cc[4 * q + 2], Cc[4 * q + 3]);
         }
-    };
-    // pixel whose uniqueness test and output are still pending (x < 0: none); Sm / Sq are meaningful on lane 0
-    int pn_best = 0, pn_minS = 0, pn_Sm = 0, pn_Sq = 0, pn_x = -1;
-    auto finish_pending = [&](const int min2) {
-        const int nexcl = 1 + (pn_best > 0) + (pn_best < a.D - 1);
-        const bool reject = (a.D > nexcl) && (min2 * (100 - a.ue) < pn_minS * 100);
-        if (!reject && gl == 0 && valid) {
-            const int x2 = pn_x + a.minX1 - pn_best - a.minD;
-            if (pn_minS < 32767) atomicMin(&keys[x2], ((unsigned)pn_minS << 16) | (0xffffu - (unsigned)pn_best));
-            int d16 = pn_best * 16;
-            if (pn_best > 0 && pn_best < a.D - 1) {
-                const int den2 = max(pn_Sm + pn_Sq - 2 * pn_minS, 1);
-                d16 += (int)__fdiv_rn((float)((pn_Sm - pn_Sq) * 16 + den2), (float)(2 * den2));   // exact, see wta_pixel
-            }
-            out[pn_x + a.minX1] = (int16_t)(d16 + a.minD * 16);
-        }
-    };
-    auto pending_local_min = [&]() -> unsigned {   // lane-local minimum of the pending pixel's S with the winner knocked out
-        __syncwarp();                               // lane 0's knock-out stores are visible
-        const unsigned short* sp = stash + (pn_x & 1) * (LW * DPL);
-        unsigned e[NR];
-#pragma unroll
-        for (int q = 0; q < NR / 4; q++) {
-            const uint4 t = *(const uint4*)(sp + (q * LW + gl) * 8);
-            e[4 * q] = t.x; e[4 * q + 1] = t.y; e[4 * q + 2] = t.z; e[4 * q + 3] = t.w;
-        }
-        const unsigned me = local_min2<NR>(e);
-        return min(me & 0xffffu, me >> 16);
     };
     auto stepf = [&](const int x, const int xs, unsigned (&Sc)[NR]) {   // one -> step + winner; Sc holds Sv on entry
         unsigned Cc[NR];
@@ -378,15 +375,13 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             const uint4 t = Cb[((x - xs) * (NR / 4) + q) * LW + gl];
             Cc[4 * q] = t.x; Cc[4 * q + 1] = t.y; Cc[4 * q + 2] = t.z; Cc[4 * q + 3] = t.w;
         }
-        if constexpr (W3) {
-            sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
-        }
-        unsigned mlL = 0u;
-        if constexpr (!W3) mlL = sgm_step_core<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+        sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+        const int pix = (x - xs) * RPW + rw;
+        uint4* rec = Lw + pix * NCH + (gl ^ (pix & SWZ));
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
-            const uint4 t = Lb[((x - xs) * (NR / 4) + q) * LW + gl];
-            if (a.nosat) {   // the sum of all paths provably stays below 32768: plain adds on the packed halves
+            const uint4 t = W3 ? Lb[((x - xs) * (NR / 4) + q) * LW + gl] : rec[q * LW];
+            if (nosat) {   // the sum of all paths provably stays below 32768: plain adds on the packed halves
                 Sc[4 * q] += Lr[4 * q] + t.x; Sc[4 * q + 1] += Lr[4 * q + 1] + t.y;
                 Sc[4 * q + 2] += Lr[4 * q + 2] + t.z; Sc[4 * q + 3] += Lr[4 * q + 3] + t.w;
             } else {
@@ -399,78 +394,103 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
         if constexpr (W3) {
             wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
         } else {
-            // Winner search, software-pipelined by one pixel so that ONE lane-group reduction per step serves three
-            // minima: min_d L(->) (needed by the next column), min_d S of this pixel, and the second minimum of the
-            // previous pixel (its winner's neighbourhood was knocked out in the stash one step ago).
-            unsigned w[NR];
+            // S(p, .) replaces L(<-) in the pixel's record (padded disparities forced to 0x7fff); the winner is
+            // selected once the chunk's -> scan is done (select_chunk)
 #pragma unroll
-            for (int j = 0; j < NR; j++) w[j] = PAD ? umax2(Sc[j], pm[j]) : Sc[j];
-            unsigned short* st = stash + (x & 1) * (LW * DPL);
-#pragma unroll
-            for (int q = 0; q < NR / 4; q++)
-                *(uint4*)(st + (q * LW + gl) * 8) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
-            unsigned t1[NR / 2 > 0 ? NR / 2 : 1], t2[NR / 4 > 0 ? NR / 4 : 1];
-#pragma unroll
-            for (int j = 0; j < NR / 2; j++) t1[j] = umin2(w[2 * j], w[2 * j + 1]);
-#pragma unroll
-            for (int j = 0; j < NR / 4; j++) t2[j] = umin2(t1[2 * j], t1[2 * j + 1]);
-            const unsigned mlS = (NR == 8) ? umin2(t2[0], t2[1]) : t2[0];
-            const unsigned lm = min(mlS & 0xffffu, mlS >> 16);
-            unsigned r0 = min(mlL & 0xffffu, mlL >> 16) | (lm << 16);
-            unsigned r1 = (pn_x >= 0) ? pending_local_min() : 0xffffu;
-#pragma unroll
-            for (int o = LW / 2; o > 0; o >>= 1) {
-                r0 = umin2(r0, __shfl_xor_sync(gmask, r0, o, LW));
-                r1 = min(r1, __shfl_xor_sync(gmask, r1, o, LW));
+            for (int q = 0; q < NR / 4; q++) {
+                uint4 w;
+                w.x = PAD ? umax2(Sc[4 * q], pm[4 * q]) : Sc[4 * q];
+                w.y = PAD ? umax2(Sc[4 * q + 1], pm[4 * q + 1]) : Sc[4 * q + 1];
+                w.z = PAD ? umax2(Sc[4 * q + 2], pm[4 * q + 2]) : Sc[4 * q + 2];
+                w.w = PAD ? umax2(Sc[4 * q + 3], pm[4 * q + 3]) : Sc[4 * q + 3];
+                rec[q * LW] = w;
             }
-            mr = r0 & 0xffffu;
-            const int minS = (int)(r0 >> 16);
-            if (pn_x >= 0) finish_pending((int)r1);
-            // position of the winner: walk the min tree down, lowest index wins at every level
-            auto has = [&](unsigned v) { return (int)min(v & 0xffffu, v >> 16) == minS; };
-            int j4 = 0;
-            if (NR == 8 && !has(t2[0])) j4 = 1;
-            const unsigned a0 = (NR == 8 && j4) ? t1[2] : t1[0];
-            const int j2 = 2 * j4 + (has(a0) ? 0 : 1);
-            unsigned b0 = w[0], b1 = w[1];
-#pragma unroll
-            for (int j = 1; j < NR / 2; j++) { b0 = (j2 == j) ? w[2 * j] : b0; b1 = (j2 == j) ? w[2 * j + 1] : b1; }
-            const int j1 = 2 * j2 + (has(b0) ? 0 : 1);
-            const unsigned c0 = has(b0) ? b0 : b1;
-            const int cand = 2 * j1 + (((int)(c0 & 0xffffu) == minS) ? 0 : 1);
-            const unsigned gbits = (LW == 32) ? 0xffffffffu : ((1u << LW) - 1u);
-            const unsigned bits = (__ballot_sync(gmask, (int)lm == minS) >> gbase) & gbits;
-            const int fl = __ffs(bits) - 1;                                   // lowest lane reaching the minimum
-            const int best = fl * DPL + __shfl_sync(gmask, cand, fl, LW);     // lowest d reaching the minimum
-            __syncwarp();                                                     // this pixel's stash is complete
-            if (gl == 0) {
-                const int im = stash_idx<LW, NR>(max(best - 1, 0)), ib = stash_idx<LW, NR>(best);
-                const int iq = stash_idx<LW, NR>(min(best + 1, LW * DPL - 1));
-                pn_Sm = st[im];
-                pn_Sq = st[iq];
-                if (best > 0) st[im] = 0xffffu;
-                st[ib] = 0xffffu;
-                if (best + 1 < LW * DPL) st[iq] = 0xffffu;
-            }
-            pn_best = best; pn_minS = minS; pn_x = x;
         }
     };
-    auto drain_pending = [&]() {       // end of the row: the last pixel's second minimum gets its own reduction
+    // ---- A.6 steps 1-4 for the pixels of chunk [xs, xs + ncols), one lane per pixel (!W3) ---------------------------
+    // The scans leave S(p, .) of every pixel of the chunk in shared memory. Selection per pixel is scalar work
+    // (lowest d reaching the minimum, its two neighbours, the smallest S outside [best-1, best+1], the uniqueness
+    // test, the right-view key, the sub-pixel parabola): done by the lane group it cost ~250 warp instructions per
+    // COLUMN with one lane in eight busy; done here it costs about as much per CHUNK, NPW pixels at a time.
+    auto select_chunk = [&](const int xs, const int ncols) {
         if constexpr (!W3) {
-            if (pn_x >= 0) {
-                unsigned r1 = pending_local_min();
+            __syncwarp();                                       // every record of the chunk is complete
+            const int wline0 = blockIdx.x * LINES + (lic - rw);   // first line of this warp
+#pragma unroll 1
+            for (int pix = threadIdx.x & 31; pix < NPW; pix += 32) {
+                const int k = pix / RPW, r = pix % RPW;
+                const int pline = wline0 + r;
+                if (k >= ncols || pline >= a.nlines) continue;
+                const uint4* pb = Lw + pix * NCH;
+                const int sw = pix & SWZ;
+                auto unit_of = [&](const int j) {                 // record unit that holds disparities 8j .. 8j+7
+                    const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;
+                    return c ^ sw;
+                };
+                // minimum and the first block of 8 disparities that reaches it: min over (value << 8 | block)
+                unsigned kmin = 0xffffffffu;
 #pragma unroll
-                for (int o = LW / 2; o > 0; o >>= 1) r1 = min(r1, __shfl_xor_sync(gmask, r1, o, LW));
-                finish_pending((int)r1);
-                pn_x = -1;
+                for (int j = 0; j < NCH; j++) {
+                    const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;          // compile-time
+                    const uint4 v = pb[(c & ~SWZ) + ((c & SWZ) ^ sw)];
+                    const unsigned m2 = umin2(umin3_2(v.x, v.y, v.z), v.w);
+                    kmin = min(kmin, (min(m2 & 0xffffu, m2 >> 16) << 8) | (unsigned)j);
+                }
+                const int minS = (int)(kmin >> 8), jb = (int)(kmin & 0xffu);
+                int best;
+                {
+                    const uint4 v = pb[unit_of(jb)];
+                    const unsigned pk = pk2((unsigned)minS);
+                    const unsigned e0 = v.x ^ pk, e1 = v.y ^ pk, e2 = v.z ^ pk, e3 = v.w ^ pk;
+                    int hb = 7;                                   // some half equals minS; the lowest one wins
+                    if ((e3 & 0xffffu) == 0u) hb = 6;
+                    if ((e2 >> 16) == 0u) hb = 5;
+                    if ((e2 & 0xffffu) == 0u) hb = 4;
+                    if ((e1 >> 16) == 0u) hb = 3;
+                    if ((e1 & 0xffffu) == 0u) hb = 2;
+                    if ((e0 >> 16) == 0u) hb = 1;
+                    if ((e0 & 0xffffu) == 0u) hb = 0;
+                    best = 8 * jb + hb;
+                }
+                // the winner's neighbours, then knock the three out for the uniqueness test
+                unsigned short* ph = (unsigned short*)pb;
+                const int dm = max(best - 1, 0), dq = min(best + 1, LW * DPL - 1);
+                unsigned short* pm_ = ph + 8 * unit_of(dm >> 3) + (dm & 7);
+                unsigned short* pq_ = ph + 8 * unit_of(dq >> 3) + (dq & 7);
+                const int Sm = *pm_, Sq = *pq_;
+                if (best > 0) *pm_ = 0xffffu;
+                ph[8 * unit_of(best >> 3) + (best & 7)] = 0xffffu;
+                if (best + 1 < LW * DPL) *pq_ = 0xffffu;
+                unsigned acc = 0xffffffffu;
+#pragma unroll
+                for (int c = 0; c < NCH; c++) {                   // any order: physical unit (c & ~SWZ) + ((c & SWZ) ^ sw)
+                    const uint4 v = pb[(c & ~SWZ) + ((c & SWZ) ^ sw)];
+                    acc = umin3_2(acc, v.x, v.y);
+                    acc = umin3_2(acc, v.z, v.w);
+                }
+                const int min2 = (int)min(acc & 0xffffu, acc >> 16);
+                const int nexcl = 1 + (best > 0) + (best < a.D - 1);
+                const bool reject = (a.D > nexcl) && (min2 * (100 - a.ue) < minS * 100);
+                if (reject) continue;
+                const int x = xs + k;
+                const size_t prow = (size_t)pline * a.W;
+                const int x2 = x + a.minX1 - best - a.minD;
+                if (minS < 32767) atomicMin(a.keys + prow + x2, ((unsigned)minS << 16) | (0xffffu - (unsigned)best));   // RED.MIN
+                int d16 = best * 16;
+                if (best > 0 && best < a.D - 1) {
+                    const int den2 = max(Sm + Sq - 2 * minS, 1);
+                    d16 += (int)__fdiv_rn((float)((Sm - Sq) * 16 + den2), (float)(2 * den2));   // exact, see wta_pixel
+                }
+                a.raw[prow + x + a.minX1] = (int16_t)(d16 + a.minD * 16);
             }
+            __syncwarp();                                       // the records are free for the next chunk
         }
     };
     // checkpoint of the chunk that ends at xe -> L (in flight while other work runs); nothing to load at the row end
     auto fetch_ck = [&](const int xe) {
 #pragma unroll
         for (int j = 0; j < NR; j++) L[j] = 0x7fff7fffu;
-        if (active && xe < a.W1) load_regs<NR>(ck + (size_t)((xe - r0) / ROW_K + 1) * a.Dp, L);
+        if (active && xe < a.W1) load_regs<NR>(ck + (size_t)((xe - r0) / ROW_K + 1) * Dp, L);
     };
     auto start_from_ck = [&](const int xe) {
         if (xe < a.W1) {
@@ -483,11 +503,11 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
     auto prefetch_chunk = [&](const int xs) {    // bring C and Sv of chunk [xs, xs+K) towards L2
 #if ROWS_PF2
         if (active && xs + gl < a.W1 && gl < ROW_K) {
-            if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL);
-            if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL);
-            if (a.Dp > 64) {
-                if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
-                if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * a.Dp - gl * DPL + 64);
+            if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * Dp - gl * DPL);
+            if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * Dp - gl * DPL);
+            if (Dp > 64) {
+                if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * Dp - gl * DPL + 64);
+                if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * Dp - gl * DPL + 64);
             }
         }
 #endif
@@ -510,6 +530,7 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             ldS(x, X2);
             stepf(x, 0, X2);
         }
+        select_chunk(0, r0);
         __syncwarp();
     }
     for (int xs = r0; xs < a.W1; xs += ROW_K) {
@@ -539,9 +560,9 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
             if (i + 3 < ROW_K) ldS(x + 4, X1); else if (xe < a.W1) ldC(xe + ROW_K - 2, X1);
             stepf(x + 2, xs, X2);
         }
+        select_chunk(xs, ROW_K);
         __syncwarp();
     }
-    drain_pending();
     // ---- A.6 step 5: left-right check on the finished row, four pixels per lane in flight ------------------
     __syncwarp();
     if (valid) {
@@ -591,17 +612,17 @@ static size_t rows_smem() {
     return (size_t)2 * LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * (ROWS_STASH2 ? 2 : 1) * LW * 2 * NR * sizeof(unsigned short);
 }
 
-template <int LW, int NR, bool PAD, bool W3>
+template <int LW, int NR, bool PAD, bool W3, bool NS>
 static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t st) {
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-    cudaFuncSetAttribute(k_rows<LW, NR, PAD, W3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_rows<LW, NR, PAD, W3, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     // a single frame (or a few small ones) leaves most SMs without a CTA at 128 threads: spread the lines one warp per CTA
     if (grid < 2 * sms) {
         constexpr int L1 = 32 / LW;
-        k_rows<LW, NR, PAD, W3><<<(a.nlines + L1 - 1) / L1, 32, smem / 4, st>>>(a);
+        k_rows<LW, NR, PAD, W3, NS><<<(a.nlines + L1 - 1) / L1, 32, smem / 4, st>>>(a);
     } else {
-        k_rows<LW, NR, PAD, W3><<<grid, 128, smem, st>>>(a);
+        k_rows<LW, NR, PAD, W3, NS><<<grid, 128, smem, st>>>(a);
     }
 }
 
@@ -612,13 +633,14 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
     const int grid = (a.nlines + LINES - 1) / LINES;
     const bool w3 = (a.mode == B200S_MODE_SGBM_3WAY) && (8 * (a.D / 8) > 0);
     if (a.D == LW * 2 * NR) {   // no padded disparities anywhere: drop the pad clamps
-        if (w3) launch_rows_k<LW, NR, false, true>(a, grid, smem, st);
-        else launch_rows_k<LW, NR, false, false>(a, grid, smem, st);
+        if (w3) launch_rows_k<LW, NR, false, true, false>(a, grid, smem, st);
+        else if (a.nosat) launch_rows_k<LW, NR, false, false, true>(a, grid, smem, st);
+        else launch_rows_k<LW, NR, false, false, false>(a, grid, smem, st);
     } else {
         RowArgs b = a;
         b.nosat = 0;            // padded halves hold 0x7fff: their sums must keep saturating
-        if (w3) launch_rows_k<LW, NR, true, true>(b, grid, smem, st);
-        else launch_rows_k<LW, NR, true, false>(b, grid, smem, st);
+        if (w3) launch_rows_k<LW, NR, true, true, false>(b, grid, smem, st);
+        else launch_rows_k<LW, NR, true, false, false>(b, grid, smem, st);
     }
 }
 
@@ -626,9 +648,9 @@ template <int LW, int NR>
 static int rows_capacity_t() {
     constexpr int LINES = 128 / LW;
     const size_t smem = rows_smem<LW, NR>();
-    cudaFuncSetAttribute(k_rows<LW, NR, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_rows<LW, NR, true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0, dev = 0, sms = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true, false>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true, false, false>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     return nb * sms * LINES;
