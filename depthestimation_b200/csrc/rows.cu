@@ -248,6 +248,9 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
     out[xc + a.minX1] = (int16_t)(d16 + a.minD * 16);
 }
 
+#ifndef ROWS_THREADS
+#define ROWS_THREADS 128
+#endif
 #ifndef ROWS_MINB
 #define ROWS_MINB 4   // 4 CTAs (16 warps) per SM: 57 KB of shared memory each, <= 128 registers
 #endif
@@ -256,7 +259,7 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
 // every pixel of a chunk is selected AFTER the chunk's -> scan, one lane per pixel (select_chunk below).
 // NS (only read when !W3): the sum of all paths cannot reach 32768, plain adds instead of saturating ones.
 template <int LW, int NR, bool PAD, bool W3, bool NS>
-__global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
+__global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
     constexpr int RPW = 32 / LW;                    // lines per warp
     constexpr int NCH = LW * NR / 4;                // 16-byte units per pixel record (all disparities of one pixel)
@@ -607,9 +610,10 @@ __global__ void __launch_bounds__(128, ROWS_MINB) k_rows(const RowArgs a) {
 }
 
 template <int LW, int NR>
-static size_t rows_smem() {
-    constexpr int LINES = 128 / LW;
-    return (size_t)2 * LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) + (size_t)LINES * (ROWS_STASH2 ? 2 : 1) * LW * 2 * NR * sizeof(unsigned short);
+static size_t rows_smem(const bool w3) {   // L / S records + C of the chunk; sgbm_3way adds its per-line stash
+    constexpr int LINES = ROWS_THREADS / LW;
+    return (size_t)2 * LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) +
+           (w3 ? (size_t)LINES * (ROWS_STASH2 ? 2 : 1) * LW * 2 * NR * sizeof(unsigned short) : 0);
 }
 
 template <int LW, int NR, bool PAD, bool W3, bool NS>
@@ -620,18 +624,18 @@ static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t 
     // a single frame (or a few small ones) leaves most SMs without a CTA at 128 threads: spread the lines one warp per CTA
     if (grid < 2 * sms) {
         constexpr int L1 = 32 / LW;
-        k_rows<LW, NR, PAD, W3, NS><<<(a.nlines + L1 - 1) / L1, 32, smem / 4, st>>>(a);
+        k_rows<LW, NR, PAD, W3, NS><<<(a.nlines + L1 - 1) / L1, 32, smem / (ROWS_THREADS / 32), st>>>(a);
     } else {
-        k_rows<LW, NR, PAD, W3, NS><<<grid, 128, smem, st>>>(a);
+        k_rows<LW, NR, PAD, W3, NS><<<grid, ROWS_THREADS, smem, st>>>(a);
     }
 }
 
 template <int LW, int NR>
 static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
-    constexpr int LINES = 128 / LW;
-    const size_t smem = rows_smem<LW, NR>();
-    const int grid = (a.nlines + LINES - 1) / LINES;
+    constexpr int LINES = ROWS_THREADS / LW;
     const bool w3 = (a.mode == B200S_MODE_SGBM_3WAY) && (8 * (a.D / 8) > 0);
+    const size_t smem = rows_smem<LW, NR>(w3);
+    const int grid = (a.nlines + LINES - 1) / LINES;
     if (a.D == LW * 2 * NR) {   // no padded disparities anywhere: drop the pad clamps
         if (w3) launch_rows_k<LW, NR, false, true, false>(a, grid, smem, st);
         else if (a.nosat) launch_rows_k<LW, NR, false, false, true>(a, grid, smem, st);
@@ -646,11 +650,11 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
 
 template <int LW, int NR>
 static int rows_capacity_t() {
-    constexpr int LINES = 128 / LW;
-    const size_t smem = rows_smem<LW, NR>();
+    constexpr int LINES = ROWS_THREADS / LW;
+    const size_t smem = rows_smem<LW, NR>(false);
     cudaFuncSetAttribute(k_rows<LW, NR, true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0, dev = 0, sms = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true, false, false>, 128, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true, false, false>, ROWS_THREADS, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     return nb * sms * LINES;
