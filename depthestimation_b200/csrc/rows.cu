@@ -37,10 +37,6 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 #ifndef ROWS_PF2
 #define ROWS_PF2 3   // pass-2 L2 prefetch of the next chunk: bit 0 = C, bit 1 = Sv
 #endif
-#ifndef ROWS_STASH2
-#define ROWS_STASH2 1   // two alternating sub-pixel stashes per line (no write-after-read sync)
-#endif
-
 // L2 residency hints. The row kernel touches a chunk of C twice within a few microseconds (reverse re-scan, then
 // forward scan) while ~6000 lines stream 40+ MB of other data through L2 in between: the chunk is fetched
 // evict_last, everything that is used for the last time is read evict_first.
@@ -73,181 +69,6 @@ __device__ __forceinline__ void load_regs_pol(const uint16_t* p, unsigned (&r)[N
 #endif
 }
 
-// Stash layout: 16-byte unit (q, lane) at (q * LW + lane) * 8 halves, so that a lane group's vector access covers 128
-// contiguous bytes (lane-major units 32 bytes apart put lanes g and g+4 on the same banks: a 2-way conflict on every
-// stash store and load). Disparity d lives in lane d / DPL, unit (d % DPL) / 8, half d % 8.
-template <int LW, int NR>
-__device__ __forceinline__ int stash_idx(const int d) {
-    if (NR <= 4) return d;
-    return ((((d >> 3) & (NR / 4 - 1)) * LW + d / (2 * NR)) << 3) + (d & 7);
-}
-
-// ---- A.6 steps 1-4 for one pixel whose S(., d) sits in v[] across the lane group ------------------
-template <int LW, int NR, bool PAD>
-__device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigned (&pm)[NR], const RowArgs& a,
-                                          const unsigned gmask, const int gl, const int gbase, const int xc,
-                                          unsigned* keys, int16_t* out, const bool valid, unsigned short* stash) {
-    constexpr int DPL = 2 * NR;
-    unsigned w[NR];
-#pragma unroll
-    for (int j = 0; j < NR; j++) w[j] = PAD ? umax2(v[j], pm[j]) : v[j];
-    const int d0 = 8 * (a.D / 8);
-    const bool simd3 = (a.mode == B200S_MODE_SGBM_3WAY) && d0 > 0;
-    const unsigned gbits = (LW == 32) ? 0xffffffffu : ((1u << LW) - 1u);
-    // S(., d) of this pixel goes through a per-line shared-memory stash: lane 0 reads the two neighbours of the
-    // winner by address, and the winner's neighbourhood is knocked out there for the uniqueness test (dynamic
-    // indexing costs one store in shared memory, but ~8 ALU operations per register when done on registers)
-#if ROWS_STASH2
-    stash += (xc & 1) * (LW * DPL);   // two stashes alternate: lane 0 may still be reading the previous pixel's
-#else
-    __syncwarp();                     // lane 0 is done with the previous pixel's stash
-#endif
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++)
-        *(uint4*)(stash + (q * LW + gl) * 8) = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
-    int minS, best;
-    if (!simd3) {
-        // binary min tree over the lane's registers; the winner's position is found by walking it down
-        unsigned t1[NR / 2 > 0 ? NR / 2 : 1], t2[NR / 4 > 0 ? NR / 4 : 1];
-#pragma unroll
-        for (int j = 0; j < NR / 2; j++) t1[j] = umin2(w[2 * j], w[2 * j + 1]);
-#pragma unroll
-        for (int j = 0; j < NR / 4; j++) t2[j] = umin2(t1[2 * j], t1[2 * j + 1]);
-        const unsigned ml = (NR == 8) ? umin2(t2[0], t2[1]) : t2[0];
-        const int lm = (int)min(ml & 0xffffu, ml >> 16);
-        const unsigned mg = group_min2<LW>(ml, gmask);
-        minS = (int)min(mg & 0xffffu, mg >> 16);
-        auto has = [&](unsigned x) { return (int)min(x & 0xffffu, x >> 16) == minS; };
-        int cand = 0;
-        {   // lowest index wins at every level
-            int j4 = 0;
-            if (NR == 8 && !has(t2[0])) j4 = 1;
-            const unsigned a0 = (NR == 8 && j4) ? t1[2] : t1[0];
-            const int j2 = 2 * j4 + (has(a0) ? 0 : 1);
-            unsigned b0 = w[0], b1 = w[1];
-#pragma unroll
-            for (int j = 1; j < NR / 2; j++) { b0 = (j2 == j) ? w[2 * j] : b0; b1 = (j2 == j) ? w[2 * j + 1] : b1; }
-            const int j1 = 2 * j2 + (has(b0) ? 0 : 1);
-            const unsigned c0 = has(b0) ? b0 : b1;
-            cand = 2 * j1 + (((int)(c0 & 0xffffu) == minS) ? 0 : 1);
-        }
-        const unsigned bits = (__ballot_sync(gmask, lm == minS) >> gbase) & gbits;
-        const int fl = __ffs(bits) - 1;                       // lowest lane reaching the minimum
-        best = fl * DPL + __shfl_sync(gmask, cand, fl, LW);   // lowest d reaching the minimum
-    } else {
-        // sgbm_3way: minimum over d < d0 taken 8 SIMD lanes wide (lane = d % 8); inside a SIMD lane the
-        // LAST d reaching the lane minimum is kept, across SIMD lanes the lowest such d; the scalar
-        // tail d >= d0 only wins when strictly smaller.
-        unsigned lm4[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            unsigned t = 0x7fff7fffu;
-#pragma unroll
-            for (int h = 0; h < NR / 4; h++) {
-                const int dreg = gl * DPL + 8 * h;            // first d of this 8-block
-                t = umin2(t, (dreg + 8 <= d0) ? v[4 * h + j] : 0x7fff7fffu);
-            }
-            lm4[j] = group_min2<LW>(t, gmask);
-        }
-        minS = 32767;
-#pragma unroll
-        for (int j = 0; j < 4; j++) minS = min(minS, (int)min(lm4[j] & 0xffffu, lm4[j] >> 16));
-        best = 0x7fffffff;
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-            const int lmin = (k & 1) ? (int)(lm4[k >> 1] >> 16) : (int)(lm4[k >> 1] & 0xffffu);
-            int dk = -1;
-#pragma unroll
-            for (int h = NR / 4 - 1; h >= 0; h--) {           // upper 8-block first: larger d
-                const int dreg = gl * DPL + 8 * h;
-                const unsigned r = v[4 * h + (k >> 1)];
-                const int val = (k & 1) ? (int)(r >> 16) : (int)(r & 0xffffu);
-                const unsigned bits = (__ballot_sync(gmask, (dreg + 8 <= d0) && val == lmin) >> gbase) & gbits;
-                if (bits) dk = max(dk, (31 - __clz(bits)) * DPL + 8 * h + k);
-            }
-            if (lmin == minS && dk >= 0) best = min(best, dk);
-        }
-        if (a.D > d0) {  // scalar tail, evaluated by the lane that holds it, then broadcast
-            const int ql = d0 / DPL, e0 = d0 % DPL;
-            int ms = minS, bs_ = best;
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                if (e0 + k < DPL && d0 + k < a.D) {
-                    const int val = elem_of<NR>(v, e0 + k);
-                    if (val < ms) { ms = val; bs_ = d0 + k; }
-                }
-            }
-            minS = __shfl_sync(gmask, ms, ql, LW);
-            best = __shfl_sync(gmask, bs_, ql, LW);
-        }
-    }
-
-    // ---- uniqueness: smallest S outside [best-1, best+1] ------------------------------------------
-    unsigned e[NR];
-    __syncwarp();                                                   // the stash is complete
-    int Sm = 0, Sq = 0;
-    if (gl == 0) {
-        const int im = stash_idx<LW, NR>(max(best - 1, 0)), ib = stash_idx<LW, NR>(best);
-        const int iq = stash_idx<LW, NR>(min(best + 1, LW * DPL - 1));
-        Sm = stash[im];
-        Sq = stash[iq];
-        if (best > 0) stash[im] = 0xffffu;
-        stash[ib] = 0xffffu;
-        if (best + 1 < LW * DPL) stash[iq] = 0xffffu;
-    }
-    __syncwarp();
-#pragma unroll
-    for (int q = 0; q < NR / 4; q++) {
-        const uint4 t = *(const uint4*)(stash + (q * LW + gl) * 8);
-        e[4 * q] = t.x; e[4 * q + 1] = t.y; e[4 * q + 2] = t.z; e[4 * q + 3] = t.w;
-    }
-    bool reject;
-    const int nexcl = 1 + (best > 0) + (best < a.D - 1);
-    if (a.mode != B200S_MODE_SGBM_3WAY) {
-        const unsigned mg = group_min2<LW>(local_min2<NR>(e), gmask);
-        const int min2 = (int)min(mg & 0xffffu, mg >> 16);
-        reject = (a.D > nexcl) && (min2 * (100 - a.ue) < minS * 100);
-    } else {
-        reject = false;
-        if (a.ue > 0) {
-            // SIMD part d < d0: S[d] < (int16)(thr + 1); scalar tail d >= d0: S[d]*(100-ue) < minS*100
-            unsigned la = 0xffffffffu, lb = 0xffffffffu;
-#pragma unroll
-            for (int j = 0; j < NR; j++) {
-                const int d = gl * DPL + 2 * j;  // d0 is even, so a register is entirely on one side
-                if (d < d0) la = umin2(la, e[j]); else lb = umin2(lb, e[j]);
-            }
-            unsigned key = min(la & 0xffffu, la >> 16) | (min(lb & 0xffffu, lb >> 16) << 16);
-            key = group_min2<LW>(key, gmask);
-            const int m2a = (int)(key & 0xffffu), m2b = (int)(key >> 16);
-            const int thr = (100 * minS) / (100 - a.ue);
-            const int t16 = (int)(short)(thr + 1);
-            if (m2a != 0xffff && m2a < t16) reject = true;
-            if (m2b != 0xffff && m2b < 0x7fff + 1 && (m2b * (100 - a.ue) < minS * 100)) {
-                // padded disparities (forced to 0x7fff) are not candidates: make sure a real tail element exists
-                const int lo = max(d0, 0), hi = a.D - 1;
-                int ntail = hi - lo + 1;
-                for (int d = best - 1; d <= best + 1; d++) ntail -= (d >= lo && d <= hi);
-                if (ntail > 0) reject = true;
-            }
-        }
-    }
-    if (reject || gl != 0 || !valid) return;
-    const int x2 = xc + a.minX1 - best - a.minD;
-    if (minS < 32767) {
-        const unsigned nk = ((unsigned)minS << 16) | (0xffffu - (unsigned)best);
-        atomicMin(&keys[x2], nk);           // result unused -> RED.MIN: no round trip on the scan's critical path
-    }
-    int d16 = best * 16;
-    if (best > 0 && best < a.D - 1) {
-        const int den2 = max(Sm + Sq - 2 * minS, 1);
-        // C truncating division. |Sm - Sq| <= den2, so |quotient| <= 8.5 and a non-integer quotient is at least
-        // 2^-17 away from an integer: the correctly rounded float quotient truncates to the exact result.
-        d16 += (int)__fdiv_rn((float)((Sm - Sq) * 16 + den2), (float)(2 * den2));
-    }
-    out[xc + a.minX1] = (int16_t)(d16 + a.minD * 16);
-}
-
 #ifndef ROWS_THREADS
 #define ROWS_THREADS 128
 #endif
@@ -255,9 +76,9 @@ __device__ __forceinline__ void wta_pixel(const unsigned (&v)[NR], const unsigne
 #define ROWS_MINB 4   // 4 CTAs (16 warps) per SM: 57 KB of shared memory each, <= 128 registers
 #endif
 
-// W3 = true: sgbm_3way (its 8-wide SIMD winner rule keeps the monolithic per-column wta_pixel); false: the winner of
-// every pixel of a chunk is selected AFTER the chunk's -> scan, one lane per pixel (select_chunk below).
-// NS (only read when !W3): the sum of all paths cannot reach 32768, plain adds instead of saturating ones.
+// The winner of every pixel of a chunk is selected AFTER the chunk's -> scan, one lane per pixel (select_chunk below).
+// W3 = true: sgbm_3way's selection rule (the binary's 8-wide SIMD minimum + scalar tail, A.7); false: A.6.
+// NS: the sum of all paths cannot reach 32768, plain adds instead of saturating ones.
 template <int LW, int NR, bool PAD, bool W3, bool NS>
 __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
@@ -273,21 +94,18 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
     const bool valid = line_raw < a.nlines;
     const int line = valid ? line_raw : a.nlines - 1;   // keep the warp converged: surplus groups shadow the last line
     // every lane of the warp runs the same loops, so shuffles use the full mask with width LW (no
-    // divergence check per shuffle); ballots are shifted by gbase
+    // divergence check per shuffle)
     const unsigned gmask = 0xffffffffu;
-    const int gbase = (threadIdx.x & 31) / LW * LW;
     const int Dp = PAD ? a.Dp : LW * DPL;           // no padded disparities: the pitch is a compile-time constant
     const bool active = gl * DPL < Dp;
-    const bool nosat = W3 ? (a.nosat != 0) : NS;
-    uint4* Lb = rsm + (size_t)lic * ROW_K * (NR / 4) * LW;                                  // L(<-) of the current chunk (W3)
-    // !W3: one RECORD per pixel = all its disparities (NCH units of 8), records of a warp ordered column-major
+    constexpr bool nosat = NS;
+    // one RECORD per pixel = all its disparities (NCH units of 8), records of a warp ordered column-major
     // (p = column-in-chunk * RPW + line-in-warp). Lane gl's q-th unit (disparities gl*DPL + 8q ..) is logical unit
     // gl + LW*q, stored at unit ^ (p & SWZ): conflict-free both for the lane groups that write a record during the
     // scans (8 lanes, 8 different units) and for the lanes that each read a whole record during selection.
     uint4* Lw = rsm + (size_t)(lic / RPW) * NPW * NCH;
     const int rw = lic % RPW;
     uint4* Cb = rsm + (size_t)(LINES + lic) * ROW_K * (NR / 4) * LW;                        // C of the current chunk
-    unsigned short* stash = (unsigned short*)(rsm + (size_t)2 * LINES * ROW_K * (NR / 4) * LW) + (size_t)lic * (ROWS_STASH2 ? 2 : 1) * LW * DPL;
 
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
@@ -366,8 +184,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         uint4* rec = Lw + pix * NCH + (gl ^ (pix & SWZ));
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
-            if constexpr (W3) Lb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
-            else rec[q * LW] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+            rec[q * LW] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
             Cb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(Cc[4 * q], Cc[4 * q + 1], Cc[4 * q + 2], Cc[4 * q + 3]);
         }
     };
@@ -383,7 +200,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         uint4* rec = Lw + pix * NCH + (gl ^ (pix & SWZ));
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
-            const uint4 t = W3 ? Lb[((x - xs) * (NR / 4) + q) * LW + gl] : rec[q * LW];
+            const uint4 t = rec[q * LW];
             if (nosat) {   // the sum of all paths provably stays below 32768: plain adds on the packed halves
                 Sc[4 * q] += Lr[4 * q] + t.x; Sc[4 * q + 1] += Lr[4 * q + 1] + t.y;
                 Sc[4 * q + 2] += Lr[4 * q + 2] + t.z; Sc[4 * q + 3] += Lr[4 * q + 3] + t.w;
@@ -394,100 +211,174 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
                 Sc[4 * q + 3] = uaddmin2(uaddmin2(Sc[4 * q + 3], Lr[4 * q + 3], 0x7fff7fffu), t.w, 0x7fff7fffu);
             }
         }
-        if constexpr (W3) {
-            wta_pixel<LW, NR, PAD>(Sc, pm, a, gmask, gl, gbase, x, keys, out, valid, stash);
-        } else {
-            // S(p, .) replaces L(<-) in the pixel's record (padded disparities forced to 0x7fff); the winner is
-            // selected once the chunk's -> scan is done (select_chunk)
+        // S(p, .) replaces L(<-) in the pixel's record (padded disparities forced to 0x7fff); the winner is
+        // selected once the chunk's -> scan is done (select_chunk)
 #pragma unroll
-            for (int q = 0; q < NR / 4; q++) {
-                uint4 w;
-                w.x = PAD ? umax2(Sc[4 * q], pm[4 * q]) : Sc[4 * q];
-                w.y = PAD ? umax2(Sc[4 * q + 1], pm[4 * q + 1]) : Sc[4 * q + 1];
-                w.z = PAD ? umax2(Sc[4 * q + 2], pm[4 * q + 2]) : Sc[4 * q + 2];
-                w.w = PAD ? umax2(Sc[4 * q + 3], pm[4 * q + 3]) : Sc[4 * q + 3];
-                rec[q * LW] = w;
-            }
+        for (int q = 0; q < NR / 4; q++) {
+            uint4 w;
+            w.x = PAD ? umax2(Sc[4 * q], pm[4 * q]) : Sc[4 * q];
+            w.y = PAD ? umax2(Sc[4 * q + 1], pm[4 * q + 1]) : Sc[4 * q + 1];
+            w.z = PAD ? umax2(Sc[4 * q + 2], pm[4 * q + 2]) : Sc[4 * q + 2];
+            w.w = PAD ? umax2(Sc[4 * q + 3], pm[4 * q + 3]) : Sc[4 * q + 3];
+            rec[q * LW] = w;
         }
     };
-    // ---- A.6 steps 1-4 for the pixels of chunk [xs, xs + ncols), one lane per pixel (!W3) ---------------------------
+    // ---- A.6 steps 1-4 for the pixels of chunk [xs, xs + ncols), one lane per pixel ---------------------------------
     // The scans leave S(p, .) of every pixel of the chunk in shared memory. Selection per pixel is scalar work
-    // (lowest d reaching the minimum, its two neighbours, the smallest S outside [best-1, best+1], the uniqueness
-    // test, the right-view key, the sub-pixel parabola): done by the lane group it cost ~250 warp instructions per
-    // COLUMN with one lane in eight busy; done here it costs about as much per CHUNK, NPW pixels at a time.
+    // (the winning d, its two neighbours, the smallest S outside [best-1, best+1], the uniqueness test, the
+    // right-view key, the sub-pixel parabola): done by the lane group it cost ~250 warp instructions per COLUMN
+    // with one lane in eight busy; done here it costs about as much per CHUNK, NPW pixels at a time.
     auto select_chunk = [&](const int xs, const int ncols) {
-        if constexpr (!W3) {
-            __syncwarp();                                       // every record of the chunk is complete
-            const int wline0 = blockIdx.x * LINES + (lic - rw);   // first line of this warp
+        __syncwarp();                                       // every record of the chunk is complete
+        const int wline0 = blockIdx.x * LINES + (lic - rw);   // first line of this warp
 #pragma unroll 1
-            for (int pix = threadIdx.x & 31; pix < NPW; pix += 32) {
-                const int k = pix / RPW, r = pix % RPW;
-                const int pline = wline0 + r;
-                if (k >= ncols || pline >= a.nlines) continue;
-                const uint4* pb = Lw + pix * NCH;
-                const int sw = pix & SWZ;
-                auto unit_of = [&](const int j) {                 // record unit that holds disparities 8j .. 8j+7
-                    const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;
-                    return c ^ sw;
-                };
-                // minimum and the first block of 8 disparities that reaches it: min over (value << 8 | block)
+        for (int pix = threadIdx.x & 31; pix < NPW; pix += 32) {
+            const int k = pix / RPW, r = pix % RPW;
+            const int pline = wline0 + r;
+            if (k >= ncols || pline >= a.nlines) continue;
+            uint4* pb = Lw + pix * NCH;
+            const int sw = pix & SWZ;
+            auto unit_of = [&](const int j) {                 // record unit that holds disparities 8j .. 8j+7
+                const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;
+                return c ^ sw;
+            };
+            auto unit_ct = [&](const int j) -> uint4 {        // the same for a compile-time j: immediate offsets
+                const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;
+                return pb[(c & ~SWZ) + ((c & SWZ) ^ sw)];
+            };
+            int minS, best;
+            if constexpr (!W3) {
+                // A.6: minimum and the first block of 8 disparities that reaches it: min over (value << 8 | block)
                 unsigned kmin = 0xffffffffu;
 #pragma unroll
                 for (int j = 0; j < NCH; j++) {
-                    const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;          // compile-time
-                    const uint4 v = pb[(c & ~SWZ) + ((c & SWZ) ^ sw)];
+                    const uint4 v = unit_ct(j);
                     const unsigned m2 = umin2(umin3_2(v.x, v.y, v.z), v.w);
                     kmin = min(kmin, (min(m2 & 0xffffu, m2 >> 16) << 8) | (unsigned)j);
                 }
-                const int minS = (int)(kmin >> 8), jb = (int)(kmin & 0xffu);
-                int best;
-                {
-                    const uint4 v = pb[unit_of(jb)];
-                    const unsigned pk = pk2((unsigned)minS);
-                    const unsigned e0 = v.x ^ pk, e1 = v.y ^ pk, e2 = v.z ^ pk, e3 = v.w ^ pk;
-                    int hb = 7;                                   // some half equals minS; the lowest one wins
-                    if ((e3 & 0xffffu) == 0u) hb = 6;
-                    if ((e2 >> 16) == 0u) hb = 5;
-                    if ((e2 & 0xffffu) == 0u) hb = 4;
-                    if ((e1 >> 16) == 0u) hb = 3;
-                    if ((e1 & 0xffffu) == 0u) hb = 2;
-                    if ((e0 >> 16) == 0u) hb = 1;
-                    if ((e0 & 0xffffu) == 0u) hb = 0;
-                    best = 8 * jb + hb;
+                minS = (int)(kmin >> 8);
+                const int jb = (int)(kmin & 0xffu);
+                const uint4 v = pb[unit_of(jb)];
+                const unsigned pk = pk2((unsigned)minS);
+                const unsigned e0 = v.x ^ pk, e1 = v.y ^ pk, e2 = v.z ^ pk, e3 = v.w ^ pk;
+                int hb = 7;                                   // some half equals minS; the lowest one wins
+                if ((e3 & 0xffffu) == 0u) hb = 6;
+                if ((e2 >> 16) == 0u) hb = 5;
+                if ((e2 & 0xffffu) == 0u) hb = 4;
+                if ((e1 >> 16) == 0u) hb = 3;
+                if ((e1 & 0xffffu) == 0u) hb = 2;
+                if ((e0 >> 16) == 0u) hb = 1;
+                if ((e0 & 0xffffu) == 0u) hb = 0;
+                best = 8 * jb + hb;
+            } else {
+                // A.7 (sgbm_3way): the minimum over the NB whole blocks is taken 8 SIMD lanes wide (SIMD lane = d % 8 =
+                // the half's position in a unit); inside a SIMD lane the LAST d reaching the lane minimum is kept,
+                // across SIMD lanes the lowest such d; the scalar tail d >= 8 NB only wins when strictly smaller.
+                const int NB = a.D >> 3;
+                unsigned l0 = 0x7fff7fffu, l1 = l0, l2 = l0, l3 = l0;
+#pragma unroll
+                for (int j = 0; j < NCH; j++) {
+                    if (j < NB) {
+                        const uint4 v = unit_ct(j);
+                        l0 = umin2(l0, v.x); l1 = umin2(l1, v.y); l2 = umin2(l2, v.z); l3 = umin2(l3, v.w);
+                    }
                 }
-                // the winner's neighbours, then knock the three out for the uniqueness test
-                unsigned short* ph = (unsigned short*)pb;
-                const int dm = max(best - 1, 0), dq = min(best + 1, LW * DPL - 1);
-                unsigned short* pm_ = ph + 8 * unit_of(dm >> 3) + (dm & 7);
-                unsigned short* pq_ = ph + 8 * unit_of(dq >> 3) + (dq & 7);
-                const int Sm = *pm_, Sq = *pq_;
-                if (best > 0) *pm_ = 0xffffu;
-                ph[8 * unit_of(best >> 3) + (best & 7)] = 0xffffu;
-                if (best + 1 < LW * DPL) *pq_ = 0xffffu;
+                const unsigned mm = umin2(umin2(l0, l1), umin2(l2, l3));
+                minS = (int)min(mm & 0xffffu, mm >> 16);
+                // per SIMD lane: 1 + the last block whose value equals minS (0: none). v - minS has no borrow (minS is the
+                // minimum of these blocks), min(., 1) is 0 where equal, and (j+1) - (j+1) * that is j+1 or 0 per half.
+                const unsigned pkm = pk2((unsigned)minS);
+                unsigned j0 = 0u, j1 = 0u, j2 = 0u, j3 = 0u;
+#pragma unroll
+                for (int j = 0; j < NCH; j++) {
+                    if (j < NB) {
+                        const uint4 v = unit_ct(j);
+                        const unsigned pj = pk2((unsigned)(j + 1));
+                        j0 = umax2(j0, pj - umin2(v.x - pkm, 0x00010001u) * (unsigned)(j + 1));
+                        j1 = umax2(j1, pj - umin2(v.y - pkm, 0x00010001u) * (unsigned)(j + 1));
+                        j2 = umax2(j2, pj - umin2(v.z - pkm, 0x00010001u) * (unsigned)(j + 1));
+                        j3 = umax2(j3, pj - umin2(v.w - pkm, 0x00010001u) * (unsigned)(j + 1));
+                    }
+                }
+                best = 0x7fffffff;
+                const unsigned jl[4] = {j0, j1, j2, j3};
+#pragma unroll
+                for (int q = 3; q >= 0; q--) {                // descending, so the lowest d is the last assignment that sticks via min
+                    const int hi = (int)(jl[q] >> 16), lo = (int)(jl[q] & 0xffffu);
+                    if (hi) best = min(best, 8 * (hi - 1) + 2 * q + 1);
+                    if (lo) best = min(best, 8 * (lo - 1) + 2 * q);
+                }
+                if (a.D > 8 * NB) {                           // scalar tail: at most 7 disparities, all in unit NB
+                    const uint4 v = pb[unit_of(NB)];
+                    const unsigned t[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int kk = 0; kk < 8; kk++) {
+                        const int val = (kk & 1) ? (int)(t[kk >> 1] >> 16) : (int)(t[kk >> 1] & 0xffffu);
+                        if (8 * NB + kk < a.D && val < minS) { minS = val; best = 8 * NB + kk; }
+                    }
+                }
+            }
+            // the winner's neighbours, then knock the three out for the uniqueness test
+            unsigned short* ph = (unsigned short*)pb;
+            const int dm = max(best - 1, 0), dq = min(best + 1, LW * DPL - 1);
+            unsigned short* pm_ = ph + 8 * unit_of(dm >> 3) + (dm & 7);
+            unsigned short* pq_ = ph + 8 * unit_of(dq >> 3) + (dq & 7);
+            const int Sm = *pm_, Sq = *pq_;
+            if (best > 0) *pm_ = 0xffffu;
+            ph[8 * unit_of(best >> 3) + (best & 7)] = 0xffffu;
+            if (best + 1 < LW * DPL) *pq_ = 0xffffu;
+            bool reject;
+            if constexpr (!W3) {
                 unsigned acc = 0xffffffffu;
 #pragma unroll
-                for (int c = 0; c < NCH; c++) {                   // any order: physical unit (c & ~SWZ) + ((c & SWZ) ^ sw)
-                    const uint4 v = pb[(c & ~SWZ) + ((c & SWZ) ^ sw)];
+                for (int j = 0; j < NCH; j++) {
+                    const uint4 v = unit_ct(j);
                     acc = umin3_2(acc, v.x, v.y);
                     acc = umin3_2(acc, v.z, v.w);
                 }
                 const int min2 = (int)min(acc & 0xffffu, acc >> 16);
                 const int nexcl = 1 + (best > 0) + (best < a.D - 1);
-                const bool reject = (a.D > nexcl) && (min2 * (100 - a.ue) < minS * 100);
-                if (reject) continue;
-                const int x = xs + k;
-                const size_t prow = (size_t)pline * a.W;
-                const int x2 = x + a.minX1 - best - a.minD;
-                if (minS < 32767) atomicMin(a.keys + prow + x2, ((unsigned)minS << 16) | (0xffffu - (unsigned)best));   // RED.MIN
-                int d16 = best * 16;
-                if (best > 0 && best < a.D - 1) {
-                    const int den2 = max(Sm + Sq - 2 * minS, 1);
-                    d16 += (int)__fdiv_rn((float)((Sm - Sq) * 16 + den2), (float)(2 * den2));   // exact, see wta_pixel
+                reject = (a.D > nexcl) && (min2 * (100 - a.ue) < minS * 100);
+            } else {
+                reject = false;
+                if (a.ue > 0) {
+                    // SIMD part d < 8 NB: S[d] < (int16)(thr + 1); scalar tail: S[d] * (100 - ue) < minS * 100
+                    const int NB = a.D >> 3;
+                    unsigned la = 0xffffffffu, lb = 0xffffffffu;
+#pragma unroll
+                    for (int j = 0; j < NCH; j++) {
+                        const uint4 v = unit_ct(j);
+                        const unsigned m2 = umin2(umin3_2(v.x, v.y, v.z), v.w);
+                        if (j < NB) la = umin2(la, m2); else lb = umin2(lb, m2);
+                    }
+                    const int m2a = (int)min(la & 0xffffu, la >> 16), m2b = (int)min(lb & 0xffffu, lb >> 16);
+                    const int thr = (100 * minS) / (100 - a.ue);
+                    const int t16 = (int)(short)(thr + 1);
+                    if (m2a != 0xffff && m2a < t16) reject = true;
+                    if (m2b != 0xffff && m2b < 0x7fff + 1 && (m2b * (100 - a.ue) < minS * 100)) {
+                        // padded disparities (forced to 0x7fff) are not candidates: make sure a real tail element exists
+                        const int lo = 8 * NB, hi = a.D - 1;
+                        int ntail = hi - lo + 1;
+                        for (int d = best - 1; d <= best + 1; d++) ntail -= (d >= lo && d <= hi);
+                        if (ntail > 0) reject = true;
+                    }
                 }
-                a.raw[prow + x + a.minX1] = (int16_t)(d16 + a.minD * 16);
             }
-            __syncwarp();                                       // the records are free for the next chunk
+            if (reject) continue;
+            const int x = xs + k;
+            const size_t prow = (size_t)pline * a.W;
+            const int x2 = x + a.minX1 - best - a.minD;
+            if (minS < 32767) atomicMin(a.keys + prow + x2, ((unsigned)minS << 16) | (0xffffu - (unsigned)best));   // RED.MIN
+            int d16 = best * 16;
+            if (best > 0 && best < a.D - 1) {
+                const int den2 = max(Sm + Sq - 2 * minS, 1);
+                // C truncating division. |Sm - Sq| <= den2, so |quotient| <= 8.5 and a non-integer quotient is at least
+                // 2^-17 away from an integer: the correctly rounded float quotient truncates to the exact result.
+                d16 += (int)__fdiv_rn((float)((Sm - Sq) * 16 + den2), (float)(2 * den2));
+            }
+            a.raw[prow + x + a.minX1] = (int16_t)(d16 + a.minD * 16);
         }
+        __syncwarp();                                       // the records are free for the next chunk
     };
     // checkpoint of the chunk that ends at xe -> L (in flight while other work runs); nothing to load at the row end
     auto fetch_ck = [&](const int xe) {
@@ -610,10 +501,9 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
 }
 
 template <int LW, int NR>
-static size_t rows_smem(const bool w3) {   // L / S records + C of the chunk; sgbm_3way adds its per-line stash
+static size_t rows_smem() {   // L / S records + C of the chunk
     constexpr int LINES = ROWS_THREADS / LW;
-    return (size_t)2 * LINES * ROW_K * (NR / 4) * LW * sizeof(uint4) +
-           (w3 ? (size_t)LINES * (ROWS_STASH2 ? 2 : 1) * LW * 2 * NR * sizeof(unsigned short) : 0);
+    return (size_t)2 * LINES * ROW_K * (NR / 4) * LW * sizeof(uint4);
 }
 
 template <int LW, int NR, bool PAD, bool W3, bool NS>
@@ -634,10 +524,10 @@ template <int LW, int NR>
 static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
     constexpr int LINES = ROWS_THREADS / LW;
     const bool w3 = (a.mode == B200S_MODE_SGBM_3WAY) && (8 * (a.D / 8) > 0);
-    const size_t smem = rows_smem<LW, NR>(w3);
+    const size_t smem = rows_smem<LW, NR>();
     const int grid = (a.nlines + LINES - 1) / LINES;
     if (a.D == LW * 2 * NR) {   // no padded disparities anywhere: drop the pad clamps
-        if (w3) launch_rows_k<LW, NR, false, true, false>(a, grid, smem, st);
+        if (w3) { if (a.nosat) launch_rows_k<LW, NR, false, true, true>(a, grid, smem, st); else launch_rows_k<LW, NR, false, true, false>(a, grid, smem, st); }
         else if (a.nosat) launch_rows_k<LW, NR, false, false, true>(a, grid, smem, st);
         else launch_rows_k<LW, NR, false, false, false>(a, grid, smem, st);
     } else {
@@ -651,7 +541,7 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
 template <int LW, int NR>
 static int rows_capacity_t() {
     constexpr int LINES = ROWS_THREADS / LW;
-    const size_t smem = rows_smem<LW, NR>(false);
+    const size_t smem = rows_smem<LW, NR>();
     cudaFuncSetAttribute(k_rows<LW, NR, true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0, dev = 0, sms = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rows<LW, NR, true, false, false>, ROWS_THREADS, smem) != cudaSuccess) { cudaGetLastError(); return 0; }

@@ -31,7 +31,7 @@ struct VertArgs {
     uint16_t* S;
     int H, W1, D, Dp, P1, P2;
     int NC;          // columns per CTA (last CTA of the cluster may own fewer)
-    int KIT, nrec;   // column slots per thread group, shared-memory records (KIT * G + 1)
+    int KIT, nrec;   // column slots per thread group, shared-memory records (NC + 1: own columns + the right halo)
     int CS;          // cluster size = strips per frame
     int dy;          // +1: top-down (predecessor row y-1), -1: bottom-up (predecessor row y+1)
     int accumulate;  // 0: S = sum, 1: S = sat(S + sum)
@@ -85,12 +85,17 @@ template <int LW, int NR, int VT>
 struct VertLayout {
     static constexpr int COLQ = (NR / 4) * LW;       // uint4 per field
     static constexpr int FLD = COLQ * 16;            // bytes per field
-    static constexpr int OFF_A = 0, OFF_B = 2 * FLD, OFF_U = 4 * FLD, OFF_M = 5 * FLD;
-    static constexpr int REC = 5 * FLD + 32;         // bytes per record
+    // (with VERT_UREG the vertical path's L lives in registers: no U field, records are a fifth smaller)
+    static constexpr int NFLD = VERT_UREG ? 4 : 5;
+    static constexpr int OFF_A = 0, OFF_B = 2 * FLD, OFF_U = 4 * FLD, OFF_M = NFLD * FLD;
+    static constexpr int REC = NFLD * FLD + 32;      // bytes per record
     static constexpr int G = VT / LW;                // column groups per CTA
 };
 
-template <int LW, int NR, bool PAD, int VT>
+// CL = true: the strip state is sized NC + 1 records instead of KIT * G + 1 and the surplus groups of the last column
+// slot are redirected to the strip's last column (a run-time record offset instead of an immediate: measurably slower,
+// so it is only used for shapes whose state would not fit otherwise, e.g. 1920 wide with 256 disparities)
+template <int LW, int NR, bool PAD, int VT, bool CL>
 __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs a) {
     using VL = VertLayout<LW, NR, VT>;
     constexpr int DPL = 2 * NR, G = VL::G, FLD = VL::FLD, REC = VL::REC;
@@ -110,6 +115,7 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
     unsigned char* const tb = vsm + g * REC + gl * 16;   // this thread's chunk 0 of field 0 of record g
     unsigned char* const tm = vsm + g * REC + OFF_M;     // minima of record g
 
+    const int lastrec = NCr - 1 - g;                     // record offset (relative to g) of the strip's last column
     const bool has_right = r + 1 < a.CS, has_left = r > 0;
     constexpr unsigned HALO_BYTES = (unsigned)FLD + 4u;                 // one column of L plus its minimum
     const unsigned barA = smem_u32(bars), barB = smem_u32(bars + 2);    // + 8 * slot
@@ -169,8 +175,9 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
             if (k < KIT) {
                 const int i = k * G + g;
                 const bool valid = i < NCr;
-                unsigned char* const rb = tb + k * G * REC;
-                unsigned char* const rm = tm + k * G * REC;
+                const int ro = CL ? min(k * G, lastrec) * REC : k * G * REC;   // CL: surplus groups shadow record NCr-1
+                unsigned char* const rb = tb + ro;
+                unsigned char* const rm = tm + ro;
                 const unsigned (&Cq)[NR] = Cb[k];
                 unsigned LA[NR], LB[NR], LU[NR];
                 // halo of row t-1 from the neighbours: only the warps that own a strip-edge column wait
@@ -283,7 +290,7 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
 }
 
 // ---- launcher ------------------------------------------------------------------------------------
-struct VertPlan { int CS, NC, KIT, clusters, threads; size_t smem; double score; };
+struct VertPlan { int CS, NC, KIT, clusters, threads, clamp; size_t smem; double score; };
 
 static cudaLaunchConfig_t vert_cfg(int threads, int CS, int B, size_t smem, cudaStream_t st, cudaLaunchAttribute* attr) {
     cudaLaunchConfig_t cfg = {};
@@ -305,10 +312,13 @@ static bool plan_vert(const Eff& e, VertPlan& best) {
     constexpr int G = VL::G;
     static bool configured = false;
     if (!configured) {
-        if (cudaFuncSetAttribute(k_vert<LW, NR, true, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return false; }
-        if (cudaFuncSetAttribute(k_vert<LW, NR, true, VT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return false; }
-        if (cudaFuncSetAttribute(k_vert<LW, NR, false, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return false; }
-        if (cudaFuncSetAttribute(k_vert<LW, NR, false, VT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return false; }
+        auto cfgk = [](auto kern) {
+            if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return false; }
+            if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return false; }
+            return true;
+        };
+        if (!cfgk(k_vert<LW, NR, true, VT, false>) || !cfgk(k_vert<LW, NR, false, VT, false>) ||
+            !cfgk(k_vert<LW, NR, true, VT, true>) || !cfgk(k_vert<LW, NR, false, VT, true>)) return false;
         configured = true;
     }
     static int cs_env = -1;
@@ -319,15 +329,21 @@ static bool plan_vert(const Eff& e, VertPlan& best) {
         int NC = (e.W1 + CS - 1) / CS;
         if ((CS - 1) * NC >= e.W1) continue;                       // last strip would be empty
         int KIT = (NC + G - 1) / G;
-        size_t smem = (size_t)(KIT * G + 1) * VL::REC + 4 * sizeof(unsigned long long);
-        if (smem > 225 * 1024 || KIT > VERT_KMAX) continue;
+        if (KIT > VERT_KMAX) continue;
+        size_t smem = (size_t)(KIT * G + 1) * VL::REC + 4 * sizeof(unsigned long long);   // a record per group and slot + the right halo
+        int clamp = 0;
+        if (smem > 225 * 1024) {                                   // own columns + the right halo only (k_vert<.., CL = true>)
+            smem = (size_t)(NC + 1) * VL::REC + 4 * sizeof(unsigned long long);
+            clamp = 1;
+        }
+        if (smem > 225 * 1024) continue;
         cudaLaunchAttribute attr[1];
         cudaLaunchConfig_t cfg = vert_cfg(VT, CS, 1, smem, 0, attr);
         int ncl = 0;
-        if (cudaOccupancyMaxActiveClusters(&ncl, k_vert<LW, NR, true, VT>, &cfg) != cudaSuccess) { cudaGetLastError(); continue; }
+        if (cudaOccupancyMaxActiveClusters(&ncl, k_vert<LW, NR, true, VT, false>, &cfg) != cudaSuccess) { cudaGetLastError(); continue; }
         if (ncl <= 0) continue;
-        double score = (double)ncl / KIT + 1e-3 * (double)e.W1 / ((double)CS * KIT * G);
-        if (score > best.score) { best.score = score; best.CS = CS; best.NC = NC; best.KIT = KIT; best.smem = smem; best.clusters = ncl; best.threads = VT; }
+        double score = (double)ncl / KIT * (clamp ? 0.8 : 1.0) + 1e-3 * (double)e.W1 / ((double)CS * KIT * G);
+        if (score > best.score) { best.score = score; best.CS = CS; best.NC = NC; best.KIT = KIT; best.smem = smem; best.clusters = ncl; best.threads = VT; best.clamp = clamp; }
     }
     return best.score > 0.0;
 }
@@ -336,7 +352,8 @@ template <int LW, int NR, int VT>
 static cudaError_t launch_vert_vt(const VertPlan& pl, const VertArgs& a, int B, bool pad, cudaStream_t st) {
     cudaLaunchAttribute attr[1];
     cudaLaunchConfig_t cfg = vert_cfg(VT, pl.CS, B, pl.smem, st, attr);
-    return pad ? cudaLaunchKernelEx(&cfg, k_vert<LW, NR, true, VT>, a) : cudaLaunchKernelEx(&cfg, k_vert<LW, NR, false, VT>, a);
+    if (pl.clamp) return pad ? cudaLaunchKernelEx(&cfg, k_vert<LW, NR, true, VT, true>, a) : cudaLaunchKernelEx(&cfg, k_vert<LW, NR, false, VT, true>, a);
+    return pad ? cudaLaunchKernelEx(&cfg, k_vert<LW, NR, true, VT, false>, a) : cudaLaunchKernelEx(&cfg, k_vert<LW, NR, false, VT, false>, a);
 }
 
 template <int LW, int NR>
@@ -354,8 +371,8 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
         if (cok) cached = (okn && (!okw || narrow.score > wide.score)) ? narrow : wide;
         cW1 = e.W1; cDp = e.Dp;
         if (getenv("B200S_VERBOSE") && cok)
-            fprintf(stderr, "[b200s] k_vert<%d,%d>: W1=%d Dp=%d -> %d threads, cluster %d x %d cols (%d per thread group), %zu B smem, %d clusters co-resident\n",
-                    LW, NR, e.W1, e.Dp, cached.threads, cached.CS, cached.NC, cached.KIT, cached.smem, cached.clusters);
+            fprintf(stderr, "[b200s] k_vert<%d,%d>: W1=%d Dp=%d -> %d threads, cluster %d x %d cols (%d per thread group), %zu B smem%s, %d clusters co-resident\n",
+                    LW, NR, e.W1, e.Dp, cached.threads, cached.CS, cached.NC, cached.KIT, cached.smem, cached.clamp ? " (clamped records)" : "", cached.clusters);
     }
     if (!cok) return 1;                                            // does not fit: caller falls back to k_path
     if (clusters_out) *clusters_out = cached.clusters;
@@ -363,7 +380,7 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     VertArgs a;
     a.C = C; a.S = S; a.H = e.H; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e;
     a.NC = cached.NC; a.CS = cached.CS; a.dy = dy; a.accumulate = accumulate; a.nosat = (sum_cannot_saturate(e) && e.D == LW * 2 * NR) ? 1 : 0;   // padded halves (0x7fff) must keep saturating
-    a.KIT = cached.KIT; a.nrec = cached.KIT * (cached.threads / LW) + 1;
+    a.KIT = cached.KIT; a.nrec = cached.clamp ? cached.NC + 1 : cached.KIT * (cached.threads / LW) + 1;
     const bool pad = e.D != LW * 2 * NR;
     cudaError_t le = (cached.threads == VERT_THREADS_WIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_WIDE>(cached, a, B, pad, st)
                                                            : launch_vert_vt<LW, NR, VERT_THREADS_NARROW>(cached, a, B, pad, st);
