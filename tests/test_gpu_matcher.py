@@ -172,3 +172,41 @@ def test_full_size_1080p_hh_d256(engine):
 
 def test_full_size_4k_d256(engine):
     _flows_agree(engine, 2160, 3840, 256, "sgbm", 1005)        # BASELINE config #5 (one pair of the 64)
+
+
+_CLAMP_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, {root!r})
+import oracle
+from depthestimation_b200.engine import StereoEngine
+from depthestimation_b200.synth import make_pair
+e = StereoEngine(0)
+bad = 0
+for mode in ("sgbm", "hh"):
+    for (H, W, D, seed) in [(36, 360, 256, 91), (33, 353, 250, 92)]:
+        L, R, _ = make_pair(H, W, D, seed=seed)
+        kw = dict(min_disp=0, num_disp=D, block_size=3, sgbm_mode=mode)
+        e.configure(**kw)
+        got = e.compute(L, R)
+        ref = oracle.sgbm_compute(L, R, oracle.make_params(**kw))
+        bad += int((got != ref).sum())
+e.close()
+print("MISMATCH", bad)
+"""
+
+
+def test_vertical_kernel_clamped_records():
+    """k_vert<.., CL = true> (strip state sized NC + 1 records, surplus groups redirected to the last column) against
+    the oracle. The planner only picks it for shapes like 1920x1080 at D = 256; forcing one strip per frame
+    (B200S_VERT_CS=1, read once per process, hence the subprocess) selects it at a size the oracle does in seconds:
+    W1 = 104 columns, 4 slots of 32 groups = 129 records of 2080 B do not fit, 105 do."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = str(Path(__file__).resolve().parents[1])
+    env = dict(os.environ, B200S_VERT_CS="1", B200S_VERBOSE="1")
+    r = subprocess.run([sys.executable, "-c", _CLAMP_SCRIPT.format(root=root)], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "clamped records" in r.stderr, "the clamped instantiation was not selected:\n" + r.stderr[-1000:]
+    assert "MISMATCH 0" in r.stdout, r.stdout[-500:]
