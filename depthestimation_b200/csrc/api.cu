@@ -210,8 +210,8 @@ int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch) {
         if (launch_vert_family(e, 0, nullptr, nullptr, +1, 0, h->stream, &granule) != 0) granule = 0;
     // measured on B200: the row kernel wants whole waves (a partly filled last wave costs up to 10 % per frame) and
     // more than one of them (the second wave de-synchronises the phases of the CTAs: ~25 % faster per frame than a
-    // single wave); beyond three waves the gain is < 3 %
-    int cap = 3 * rows_capacity_lines(e) / H;
+    // single wave); three waves -> six still gains 1.5 % (kernel tails amortised), six -> nine nothing
+    int cap = 6 * rows_capacity_lines(e) / H;
     // never more than ~70 % of the free HBM: C and S are 2 B/cell each, the O(N) buffers about 64 B/px
     size_t freeb = 0, totalb = 0;
     if (cudaMemGetInfo(&freeb, &totalb) == cudaSuccess) {
