@@ -19,58 +19,76 @@
 // ------------------------------------------------------------------------------------------------
 // Four pixels per thread: the Sobel response and the raw sample are needed at x-1 .. x+4 (six columns, eight source
 // columns x-2 .. x+5 per row), each evaluated once instead of three times.
+#define PF_ROWS 8   // rows per CTA (one row per CTA made a batch ~170 000 tiny CTAs: CTA launch rate bound)
 __global__ void __launch_bounds__(128) k_prefilter(const uint8_t* __restrict__ L, const uint8_t* __restrict__ R,
                                                    int H, int W, int ftzero, uint2* __restrict__ recL,
                                                    uint2* __restrict__ recR) {
     const int x0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
-    const int y = blockIdx.y;
     const int z = blockIdx.z;  // 2*b + image
     if (x0 >= W) return;
     const int b = z >> 1;
     const uint8_t* img = ((z & 1) ? R : L) + (size_t)b * H * W;
     uint2* rec = ((z & 1) ? recR : recL) + (size_t)b * H * W;
-    const uint8_t* c = img + (size_t)y * W;
-    const uint8_t* n = img + (size_t)max(y - 1, 0) * W;
-    const uint8_t* s = img + (size_t)min(y + 1, H - 1) * W;
-    int cc[8], nn[8], ss[8];   // source columns x0-2 .. x0+5, clamped reads (clamped values are never used: borders give ftzero)
+    int xx[8];                 // source columns x0-2 .. x0+5, clamped reads (clamped values are never used: borders give ftzero)
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        const int xx = min(max(x0 - 2 + k, 0), W - 1);
-        cc[k] = c[xx]; nn[k] = n[xx]; ss[k] = s[xx];
+    for (int k = 0; k < 8; k++) xx[k] = min(max(x0 - 2 + k, 0), W - 1);
+    const bool vec = (W & 1) == 0;   // rows (and frames) of 8-byte records then start on 16-byte boundaries
+    const int yb = blockIdx.y * PF_ROWS, ye = min(yb + PF_ROWS, H);
+    // the three source rows roll through registers: one new row of eight bytes per output row
+    int nn[8], cc[8], ss[8];
+    {
+        const uint8_t* n = img + (size_t)max(yb - 1, 0) * W;
+        const uint8_t* c = img + (size_t)yb * W;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { nn[k] = n[xx[k]]; cc[k] = c[xx[k]]; }
     }
-    int g[6], r[6];            // columns x0-1 .. x0+4
+    for (int y = yb; y < ye; y++) {
+        const uint8_t* sp = img + (size_t)min(y + 1, H - 1) * W;
 #pragma unroll
-    for (int k = 0; k < 6; k++) {
-        const int x = x0 - 1 + k;
-        const bool border = (x <= 0 || x >= W - 1);
-        const int v = 2 * (cc[k + 2] - cc[k]) + (nn[k + 2] - nn[k]) + (ss[k + 2] - ss[k]);
-        g[k] = border ? ftzero : min(max(v, -ftzero), ftzero) + ftzero;
-        r[k] = border ? ftzero : cc[k + 1];
-    }
+        for (int k = 0; k < 8; k++) ss[k] = sp[xx[k]];
+        int g[6], r[6];            // columns x0-1 .. x0+4
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int x = x0 + k;
-        if (x >= W) break;
-        const int g0 = g[k + 1], r0 = r[k + 1];
-        int glo = g0, ghi = g0, rlo = r0, rhi = r0;
-        if (x > 0) {
-            const int ga = (g0 + g[k]) >> 1, ra = (r0 + r[k]) >> 1;
-            glo = min(glo, ga); ghi = max(ghi, ga); rlo = min(rlo, ra); rhi = max(rhi, ra);
+        for (int k = 0; k < 6; k++) {
+            const int x = x0 - 1 + k;
+            const bool border = (x <= 0 || x >= W - 1);
+            const int v = 2 * (cc[k + 2] - cc[k]) + (nn[k + 2] - nn[k]) + (ss[k + 2] - ss[k]);
+            g[k] = border ? ftzero : min(max(v, -ftzero), ftzero) + ftzero;
+            r[k] = border ? ftzero : cc[k + 1];
         }
-        if (x < W - 1) {
-            const int gb = (g0 + g[k + 2]) >> 1, rb = (r0 + r[k + 2]) >> 1;
-            glo = min(glo, gb); ghi = max(ghi, gb); rlo = min(rlo, rb); rhi = max(rhi, rb);
+        uint2 o[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = x0 + k;
+            const int g0 = g[k + 1], r0 = r[k + 1];
+            int glo = g0, ghi = g0, rlo = r0, rhi = r0;
+            if (x > 0) {
+                const int ga = (g0 + g[k]) >> 1, ra = (r0 + r[k]) >> 1;
+                glo = min(glo, ga); ghi = max(ghi, ga); rlo = min(rlo, ra); rhi = max(rhi, ra);
+            }
+            if (x < W - 1) {
+                const int gb = (g0 + g[k + 2]) >> 1, rb = (r0 + r[k + 2]) >> 1;
+                glo = min(glo, gb); ghi = max(ghi, gb); rlo = min(rlo, rb); rhi = max(rhi, rb);
+            }
+            o[k].x = (unsigned)g0 | ((unsigned)glo << 8) | ((unsigned)ghi << 16) | ((unsigned)r0 << 24);
+            o[k].y = (unsigned)rlo | ((unsigned)rhi << 8);
         }
-        uint2 o;
-        o.x = (unsigned)g0 | ((unsigned)glo << 8) | ((unsigned)ghi << 16) | ((unsigned)r0 << 24);
-        o.y = (unsigned)rlo | ((unsigned)rhi << 8);
-        rec[(size_t)y * W + x] = o;
+        uint2* dst = rec + (size_t)y * W + x0;
+        if (vec && x0 + 3 < W) {   // 32 contiguous bytes per thread as two 16-byte stores (whole sectors)
+            ((uint4*)dst)[0] = make_uint4(o[0].x, o[0].y, o[1].x, o[1].y);
+            ((uint4*)dst)[1] = make_uint4(o[2].x, o[2].y, o[3].x, o[3].y);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (x0 + k < W) dst[k] = o[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) { nn[k] = cc[k]; cc[k] = ss[k]; }
     }
 }
 
 void launch_prefilter(const Eff& e, const uint8_t* L, const uint8_t* R, int B, uint2* recL, uint2* recR,
                       cudaStream_t st) {
-    dim3 grid((e.W + 511) / 512, e.H, 2 * B);
+    dim3 grid((e.W + 511) / 512, (e.H + PF_ROWS - 1) / PF_ROWS, 2 * B);
     k_prefilter<<<grid, 128, 0, st>>>(L, R, e.H, e.W, e.ftzero, recL, recR);
 }
 

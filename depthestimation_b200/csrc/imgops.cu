@@ -10,35 +10,41 @@
 #include "common.cuh"
 
 // ---- B.1 remap: fixed-point bilinear, 5 fractional bits, constant-0 border ---------------------
+// Every O(N) kernel below gives a thread several pixels (or a CTA several rows): with one pixel per thread a batch is
+// ~140 000 tiny CTAs per launch and the launch rate of CTAs (~0.7 per clock), not memory, sets the time (~95 us).
+#define REMAP_PPT 4
 __global__ void __launch_bounds__(256) k_remap(const uint8_t* __restrict__ src, int sH, int sW,
                                                const float* __restrict__ m1, const float* __restrict__ m2, int H, int W,
                                                uint8_t* __restrict__ dst) {
     const size_t n = (size_t)H * W;
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
     const uint8_t* s = src + (size_t)blockIdx.y * sH * sW;
-    int sx = __float2int_rn(__fmul_rn(m1[i], 32.0f));
-    int sy = __float2int_rn(__fmul_rn(m2[i], 32.0f));
-    int ix = sx >> 5, iy = sy >> 5, fx = sx & 31, fy = sy & 31;
-    int p00 = 0, p01 = 0, p10 = 0, p11 = 0;
-    const bool x0 = (ix >= 0 && ix < sW), x1 = (ix + 1 >= 0 && ix + 1 < sW);
-    if (iy >= 0 && iy < sH) {
-        const uint8_t* r = s + (size_t)iy * sW;
-        if (x0) p00 = r[ix];
-        if (x1) p01 = r[ix + 1];
+#pragma unroll
+    for (int k = 0; k < REMAP_PPT; k++) {
+        const size_t i = ((size_t)blockIdx.x * REMAP_PPT + k) * 256 + threadIdx.x;
+        if (i >= n) return;
+        int sx = __float2int_rn(__fmul_rn(m1[i], 32.0f));
+        int sy = __float2int_rn(__fmul_rn(m2[i], 32.0f));
+        int ix = sx >> 5, iy = sy >> 5, fx = sx & 31, fy = sy & 31;
+        int p00 = 0, p01 = 0, p10 = 0, p11 = 0;
+        const bool x0 = (ix >= 0 && ix < sW), x1 = (ix + 1 >= 0 && ix + 1 < sW);
+        if (iy >= 0 && iy < sH) {
+            const uint8_t* r = s + (size_t)iy * sW;
+            if (x0) p00 = r[ix];
+            if (x1) p01 = r[ix + 1];
+        }
+        if (iy + 1 >= 0 && iy + 1 < sH) {
+            const uint8_t* r = s + (size_t)(iy + 1) * sW;
+            if (x0) p10 = r[ix];
+            if (x1) p11 = r[ix + 1];
+        }
+        int acc = (32 - fy) * ((32 - fx) * p00 + fx * p01) + fy * ((32 - fx) * p10 + fx * p11);
+        dst[(size_t)blockIdx.y * n + i] = (uint8_t)((acc * 32 + 16384) >> 15);
     }
-    if (iy + 1 >= 0 && iy + 1 < sH) {
-        const uint8_t* r = s + (size_t)(iy + 1) * sW;
-        if (x0) p10 = r[ix];
-        if (x1) p11 = r[ix + 1];
-    }
-    int acc = (32 - fy) * ((32 - fx) * p00 + fx * p01) + fy * ((32 - fx) * p10 + fx * p11);
-    dst[(size_t)blockIdx.y * n + i] = (uint8_t)((acc * 32 + 16384) >> 15);
 }
 
 void launch_remap(const uint8_t* src, int B, int sH, int sW, const float* m1, const float* m2, int H, int W,
                   uint8_t* dst, cudaStream_t st) {
-    dim3 grid((unsigned)(((size_t)H * W + 255) / 256), B);
+    dim3 grid((unsigned)(((size_t)H * W + 256 * REMAP_PPT - 1) / (256 * REMAP_PPT)), B);
     k_remap<<<grid, 256, 0, st>>>(src, sH, sW, m1, m2, H, W, dst);
 }
 
@@ -70,25 +76,37 @@ __device__ __forceinline__ T median9(T v0, T v1, T v2, T v3, T v4, T v5, T v6, T
     cswap(v4, v2);
     return v4;
 }
+// A CTA walks ROWS_PER_CTA rows of its 256 columns; the three taps of a source row are loaded once and roll through
+// registers (3 loads per output instead of 9).
+#define ROWS_PER_CTA 8
+template <typename T, typename F>
+__device__ __forceinline__ void median3_rows(const T* __restrict__ s, int H, int W, int x, int yb, F&& emit) {
+    const int xm = max(x - 1, 0), xp = min(x + 1, W - 1);
+    const T* r = s + (size_t)max(yb - 1, 0) * W;
+    T a0 = r[xm], a1 = r[x], a2 = r[xp];
+    r = s + (size_t)yb * W;
+    T b0 = r[xm], b1 = r[x], b2 = r[xp];
+    const int ye = min(yb + ROWS_PER_CTA, H);
+    for (int y = yb; y < ye; y++) {
+        r = s + (size_t)min(y + 1, H - 1) * W;
+        const T c0 = r[xm], c1 = r[x], c2 = r[xp];
+        emit(y, median9<T>(a0, a1, a2, b0, b1, b2, c0, c1, c2));
+        a0 = b0; a1 = b1; a2 = b2; b0 = c0; b1 = c1; b2 = c2;
+    }
+}
 template <typename T>
 __global__ void __launch_bounds__(256) k_median3(const T* __restrict__ src, T* __restrict__ dst, int H, int W) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= W) return;
-    const T* s = src + (size_t)blockIdx.z * H * W;
-    int xm = max(x - 1, 0), xp = min(x + 1, W - 1);
-    const T* r0 = s + (size_t)max(y - 1, 0) * W;
-    const T* r1 = s + (size_t)y * W;
-    const T* r2 = s + (size_t)min(y + 1, H - 1) * W;
-    dst[(size_t)blockIdx.z * H * W + (size_t)y * W + x] =
-        median9<T>(r0[xm], r0[x], r0[xp], r1[xm], r1[x], r1[xp], r2[xm], r2[x], r2[xp]);
+    const size_t frame = (size_t)blockIdx.z * H * W;
+    median3_rows<T>(src + frame, H, W, x, blockIdx.y * ROWS_PER_CTA, [&](int y, T m) { dst[frame + (size_t)y * W + x] = m; });
 }
 void launch_median3_s16(const int16_t* src, int16_t* dst, int B, int H, int W, cudaStream_t st) {
-    dim3 grid((W + 255) / 256, H, B);
+    dim3 grid((W + 255) / 256, (H + ROWS_PER_CTA - 1) / ROWS_PER_CTA, B);
     k_median3<int16_t><<<grid, 256, 0, st>>>(src, dst, H, W);
 }
 void launch_median3_f32(const float* src, float* dst, int B, int H, int W, cudaStream_t st) {
-    dim3 grid((W + 255) / 256, H, B);
+    dim3 grid((W + 255) / 256, (H + ROWS_PER_CTA - 1) / ROWS_PER_CTA, B);
     k_median3<float><<<grid, 256, 0, st>>>(src, dst, H, W);
 }
 
@@ -105,14 +123,17 @@ void launch_disp16_to_f32_crop(const int16_t* d16, int B, int H, int W, int x0, 
     k_d16_to_f32_crop<<<grid, 256, 0, st>>>(d16, H, W, x0, out);
 }
 __global__ void __launch_bounds__(256) k_crop_s16(const int16_t* __restrict__ d16, int H, int W, int x0, int16_t* __restrict__ out) {
-    int Wc = W - x0;
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int Wc = W - x0;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= Wc) return;
-    size_t row = (size_t)blockIdx.z * H + blockIdx.y;
-    out[row * Wc + x] = d16[row * W + x0 + x];
+    const int yb = blockIdx.y * ROWS_PER_CTA, ye = min(yb + ROWS_PER_CTA, H);
+    for (int y = yb; y < ye; y++) {
+        const size_t row = (size_t)blockIdx.z * H + y;
+        out[row * Wc + x] = d16[row * W + x0 + x];
+    }
 }
 void launch_crop_s16(const int16_t* d16, int B, int H, int W, int x0, int16_t* out, cudaStream_t st) {
-    dim3 grid((W - x0 + 255) / 256, H, B);
+    dim3 grid((W - x0 + 255) / 256, (H + ROWS_PER_CTA - 1) / ROWS_PER_CTA, B);
     k_crop_s16<<<grid, 256, 0, st>>>(d16, H, W, x0, out);
 }
 // (d * 16).astype(int16): C truncation toward zero, then wrap to 16 bits (numpy behaviour for in-range values)
@@ -212,25 +233,21 @@ __global__ void __launch_bounds__(256) k_depth(const float* __restrict__ disp, s
 __global__ void __launch_bounds__(256) k_median3_f32_depth(const float* __restrict__ src, float* __restrict__ dst, int H, int W,
                                                            float fB, float doffs, float eps, float maxDepth, int hasMax,
                                                            float* __restrict__ Z) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= W) return;
-    const float* s = src + (size_t)blockIdx.z * H * W;
-    int xm = max(x - 1, 0), xp = min(x + 1, W - 1);
-    const float* r0 = s + (size_t)max(y - 1, 0) * W;
-    const float* r1 = s + (size_t)y * W;
-    const float* r2 = s + (size_t)min(y + 1, H - 1) * W;
-    const float m = median9<float>(r0[xm], r0[x], r0[xp], r1[xm], r1[x], r1[xp], r2[xm], r2[x], r2[xp]);
-    const size_t i = (size_t)blockIdx.z * H * W + (size_t)y * W + x;
-    dst[i] = m;
-    float adj = __fadd_rn(m, doffs);
-    float z = __int_as_float(0x7f800000);
-    if (adj > eps) z = __fdiv_rn(fB, adj);
-    if (hasMax && z > maxDepth) z = maxDepth;
-    Z[i] = z;
+    const size_t frame = (size_t)blockIdx.z * H * W;
+    median3_rows<float>(src + frame, H, W, x, blockIdx.y * ROWS_PER_CTA, [&](int y, float m) {
+        const size_t i = frame + (size_t)y * W + x;
+        dst[i] = m;
+        float adj = __fadd_rn(m, doffs);
+        float z = __int_as_float(0x7f800000);
+        if (adj > eps) z = __fdiv_rn(fB, adj);
+        if (hasMax && z > maxDepth) z = maxDepth;
+        Z[i] = z;
+    });
 }
 void launch_median3_f32_depth(const float* src, float* dst, int B, int H, int W, const B200sDepthParams& dp, float* Z, cudaStream_t st) {
-    dim3 grid((W + 255) / 256, H, B);
+    dim3 grid((W + 255) / 256, (H + ROWS_PER_CTA - 1) / ROWS_PER_CTA, B);
     k_median3_f32_depth<<<grid, 256, 0, st>>>(src, dst, H, W, dp.fB, dp.doffs, dp.eps, dp.maxDepth, dp.hasMaxDepth, Z);
 }
 void launch_depth(const float* disp, size_t n, const B200sDepthParams& dp, float* Z, cudaStream_t st) {

@@ -137,34 +137,42 @@ __global__ void __launch_bounds__(256) k_ccl_border(const int16_t* __restrict__ 
     }
 }
 
-// tile-local roots hand their size to the global root
+// tile-local roots hand their size to the global root (CCL_IPT block-strided items per thread: a batch would otherwise
+// be ~140 000 one-item CTAs, and CTA launch rate, not memory, would set the time)
+#define CCL_IPT 8
 __global__ void __launch_bounds__(256) k_ccl_count(size_t n, int* lab, int* sizes) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int c = sizes[i];
-    if (c == 0) return;               // not a tile-local root
-    int r = uf_find(lab, (int)i);
-    if (r != (int)i) {
-        atomicAdd(&sizes[r], c);
-        lab[i] = r;                   // roots do not change in this kernel
+#pragma unroll
+    for (int k = 0; k < CCL_IPT; k++) {
+        const size_t i = ((size_t)blockIdx.x * CCL_IPT + k) * 256 + threadIdx.x;
+        if (i >= n) return;
+        int c = sizes[i];
+        if (c == 0) continue;             // not a tile-local root
+        int r = uf_find(lab, (int)i);
+        if (r != (int)i) {
+            atomicAdd(&sizes[r], c);
+            lab[i] = r;                   // roots do not change in this kernel
+        }
     }
 }
 
 __global__ void __launch_bounds__(256) k_ccl_apply(int16_t* img, size_t n, int newVal, int maxSize, const int* lab,
                                                    const int* __restrict__ sizes) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int l = lab[i];
-    if (l < 0) return;
-    if (sizes[l] > maxSize) return;   // the tile-local part alone is big enough: the component stays (most pixels end here)
-    int r = uf_find(lab, l);
-    if (sizes[r] <= maxSize) img[i] = (int16_t)newVal;
+#pragma unroll
+    for (int k = 0; k < CCL_IPT; k++) {
+        const size_t i = ((size_t)blockIdx.x * CCL_IPT + k) * 256 + threadIdx.x;
+        if (i >= n) return;
+        int l = lab[i];
+        if (l < 0) continue;
+        if (sizes[l] > maxSize) continue; // the tile-local part alone is big enough: the component stays (most pixels end here)
+        int r = uf_find(lab, l);
+        if (sizes[r] <= maxSize) img[i] = (int16_t)newVal;
+    }
 }
 
 void launch_speckle(int16_t* img, int B, int H, int W, int newVal, int maxSize, int maxDiff, int* labels, int* sizes,
                     cudaStream_t st, long long* launches) {
     size_t n = (size_t)B * H * W;
-    unsigned blocks = (unsigned)((n + 255) / 256);
+    unsigned blocks = (unsigned)((n + 256 * CCL_IPT - 1) / (256 * CCL_IPT));
     dim3 tg((W + TW - 1) / TW, (H + TH - 1) / TH, B);
     k_ccl_tile<<<tg, 256, 0, st>>>(img, H, W, newVal, maxDiff, labels, sizes);
     int items = ((H - 1) / TH) * W + ((W - 1) / TW) * H;
