@@ -29,10 +29,13 @@ struct RowArgs {
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 #ifndef ROW_PD
-#define ROW_PD 6  // L2 prefetch distance in columns
+#define ROW_PD 12  // pass-1 L2 prefetch distance in columns (measured: 3 -> 72.8, 6 -> 67.9, 12 -> 66.2, 18 -> 66.6, 24 -> 67.1 us per frame)
 #endif
 #ifndef ROW_PBLK
 #define ROW_PBLK 0
+#endif
+#ifndef ROWS_PFC
+#define ROWS_PFC 1   // pass-2 L2 prefetch runs that many chunks ahead
 #endif
 #ifndef ROWS_PF2
 #define ROWS_PF2 3   // pass-2 L2 prefetch of the next chunk: bit 0 = C, bit 1 = Sv
@@ -408,7 +411,8 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
     };
     {   // chunk 0 = [0, r0): short and ragged, simple loops (once per row)
         fetch_ck(r0);
-        prefetch_chunk(r0);
+#pragma unroll
+        for (int c = 0; c < ROWS_PFC; c++) prefetch_chunk(r0 + c * ROW_K);
         start_from_ck(r0);
         for (int x = r0 - 1; x >= 0; x--) {
             ldC(x, X2);
@@ -431,7 +435,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         // full chunk [xs, xe): X0 = C(xe-1), X1 = C(xe-2) and L = checkpoint(xe) were requested a phase ago
         const int xe = xs + ROW_K;
         start_from_ck(xe);
-        prefetch_chunk(xe);
+        prefetch_chunk(xe + (ROWS_PFC - 1) * ROW_K);
 #pragma unroll 1   // keep the code small: the body inlines three full steps already
         for (int i = 0; i < ROW_K; i += 3) {
             const int x = xe - 1 - i;
