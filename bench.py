@@ -205,8 +205,8 @@ def algorithmic_bytes(eng, batch):
     g = eng.geometry(W)
     V = H * g["W1"] * D
     per_kernel = {"cost": ("k_cost<5,64,1> (prefiltered rows -> C)", 2.0 * V * batch),
-                  "paths": ("k_vert<8,8,0,512> (3 vertical-family directions, one cluster per frame)", 4.0 * V * batch),
-                  "wta": ("k_rows<8,8,0> (2 horizontal directions + WTA + LR check)", 4.0 * V * batch)}
+                  "paths": ("k_vert<8,8,0,512,0> (3 vertical-family directions, one cluster per frame)", 4.0 * V * batch),
+                  "wta": ("k_rows<8,8,0,0,1> (2 horizontal directions + per-chunk winner selection + LR check)", 4.0 * V * batch)}
     return V, per_kernel, 10.0 * V * batch
 
 
