@@ -7,11 +7,13 @@
 //
 // A row's two scans run in opposite directions, so L(<-) of a column is needed long after it was
 // produced. Instead of spilling a 2V scratch volume the kernel checkpoints:
-//   pass 1: scan <- over the whole row, keep only L(<-) at every K-th column (checkpoint, 2*Dp bytes);
-//   pass 2: for each K-column chunk, left to right: re-run <- inside the chunk from its checkpoint
-//           into shared memory, then scan -> over the chunk, add Sv + L(->) + L(<-) and select.
-// HBM traffic: C twice (the third read of a chunk hits L1/L2) + Sv once = 6 B/cell instead of the
-// 14 B/cell of two read-modify-write passes plus a selection pass.
+//   pass 1: scan <- over the whole row, keep only L(<-) after every K columns (checkpoint, 2*Dp bytes);
+//   pass 2: for each K-column chunk, left to right: re-run <- inside the chunk from its checkpoint into the
+//           chunk's per-pixel records in shared memory (C of the chunk is kept there too), scan -> over the chunk,
+//           S = Sv + L(->) + L(<-) replaces L(<-) in the records, then select_chunk picks every pixel's winner,
+//           one lane per pixel (A.6, or A.7's SIMD rule for sgbm_3way).
+// HBM traffic: C twice + Sv once + the checkpoints = 6.7 B/cell instead of the 14 B/cell of two read-modify-write
+// passes plus a selection pass.
 #include "sgm_step.cuh"
 
 #ifndef ROW_K
@@ -31,33 +33,20 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 #ifndef ROW_PD
 #define ROW_PD 12  // pass-1 L2 prefetch distance in columns (measured: 3 -> 72.8, 6 -> 67.9, 12 -> 66.2, 18 -> 66.6, 24 -> 67.1 us per frame)
 #endif
-#ifndef ROW_PBLK
-#define ROW_PBLK 0
-#endif
 #ifndef ROWS_PFC
 #define ROWS_PFC 1   // pass-2 L2 prefetch runs that many chunks ahead
 #endif
 #ifndef ROWS_PF2
 #define ROWS_PF2 3   // pass-2 L2 prefetch of the next chunk: bit 0 = C, bit 1 = Sv
 #endif
-// L2 residency hints. The row kernel touches a chunk of C twice within a few microseconds (reverse re-scan, then
-// forward scan) while ~6000 lines stream 40+ MB of other data through L2 in between: the chunk is fetched
-// evict_last, everything that is used for the last time is read evict_first.
+// L2 residency hints: thousands of lines stream their C and Sv through L2 once per pass; everything that is used for
+// the last time is read evict_first so that the prefetched columns ahead of the scans survive (measured: 72.6 -> 67.9 us
+// per frame).
 #ifndef ROWS_HINTS
 #define ROWS_HINTS 1
 #endif
 __device__ __forceinline__ uint64_t l2_policy_first() {
     uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
-}
-__device__ __forceinline__ uint64_t l2_policy_last() {
-    uint64_t p; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p;
-}
-__device__ __forceinline__ void prefetch_l2_keep(const void* p) {
-#if ROWS_HINTS
-    asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(p));
-#else
-    prefetch_l2(p);
-#endif
 }
 template <int NR>
 __device__ __forceinline__ void load_regs_pol(const uint16_t* p, unsigned (&r)[NR], const uint64_t pol) {
