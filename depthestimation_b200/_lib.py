@@ -52,6 +52,7 @@ SYMBOLS = {
     "b200s_remap_u8": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_size_t, _VP, _VP]),
     "b200s_sgbm_compute": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_size_t, _VP]),
     "b200s_postprocess": (C.c_int, [_H, _VP, C.c_int, C.c_int, _PP]),
+    "b200s_fill_nearest": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int]),
     "b200s_disp_to_depth": (C.c_int, [_H, _VP, C.c_size_t, _DP, _VP]),
     "b200s_pipeline": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_size_t, C.c_int, _PP, _DP,
                                  _VP, _VP, _VP, _VP]),

@@ -608,6 +608,32 @@ int b200s_postprocess(B200sHandle* h, float* disp, int H, int W, const B200sPost
     return check_launch(h, "postprocess");
 }
 
+int b200s_fill_nearest(B200sHandle* h, float* disp, const uint8_t* mask, int H, int W, int kernel_size) {
+    if (!h) return B200S_E_INVALID;
+    if (!disp || H <= 0 || W <= 0 || kernel_size < 1 || kernel_size > 31) { h->set_error(B200S_E_INVALID, "fill_nearest: bad arguments (1 <= kernel_size <= 31)"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const size_t n = (size_t)H * W;
+    CUDA_TRY(h, h->f0.ensure(n * sizeof(float)));
+    CUDA_TRY(h, h->f1.ensure(n * sizeof(float)));
+    CUDA_TRY(h, h->imgL.ensure(n));
+    CUDA_TRY(h, cudaMemcpyAsync(h->f0.p, disp, n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    std::vector<uint8_t> m;
+    const uint8_t* hm = mask;
+    if (!hm) {                                   // the reference's default mask: disparity <= 0
+        m.resize(n);
+        for (size_t i = 0; i < n; i++) m[i] = disp[i] <= 0.0f;
+        hm = m.data();
+    }
+    CUDA_TRY(h, cudaMemcpyAsync(h->imgL.p, hm, n, cudaMemcpyHostToDevice, h->stream));
+    const int nl = launch_fill_nearest(h->f0.as<float>(), h->f1.as<float>(), h->imgL.as<uint8_t>(), H, W, kernel_size, h->stream);
+    if (nl < 0) { h->set_error(B200S_E_INVALID, "fill_nearest: unsupported kernel size"); return B200S_E_INVALID; }
+    h->launches += nl;
+    const float* res = (kernel_size & 1) ? h->f1.as<float>() : h->f0.as<float>();
+    CUDA_TRY(h, cudaMemcpyAsync(disp, res, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));   // also keeps `m` alive until the upload has been consumed
+    return check_launch(h, "fill_nearest");
+}
+
 int b200s_disp_to_depth(B200sHandle* h, const float* disp, size_t n, const B200sDepthParams* dp, float* depth) {
     if (!h) return B200S_E_INVALID;
     if (!disp || !depth || !dp || n == 0) { h->set_error(B200S_E_INVALID, "disp_to_depth: bad arguments"); return B200S_E_INVALID; }

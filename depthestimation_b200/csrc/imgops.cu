@@ -6,6 +6,7 @@
 //   outliers      detect_outliers + masking                          depthlib/postprocess.py:37-70,151-158
 //   median3 f32   cv2.medianBlur(float32, 3)                         depthlib/postprocess.py:169, stereo_core.py:173
 //   depth         StereoCore.disparity_to_depth                      depthlib/stereo_core.py:234-272
+//   fill nearest  fill_holes(method='nearest')                       depthlib/postprocess.py:106-116
 // The float chain uses explicit round-to-nearest intrinsics (no FMA contraction, no fast math).
 #include "common.cuh"
 
@@ -315,4 +316,51 @@ void launch_resize_area_tab(const uint8_t* src, int sW, int cn, const int* xo, c
                             uint8_t* dst, int dH, int dW, cudaStream_t st) {
     const size_t n = (size_t)dH * dW * cn;
     k_resize_area_tab<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, sW, cn, xo, xt, yo, yt, dst, dH, dW);
+}
+
+// ---- fill_holes(method='nearest'): one dilation by the k x k ellipse, applied under the hole mask -----------------------
+// out = mask ? max over the element (anchored at its centre, pixels outside the image ignored) : in. The element is
+// given per row as its half-width (EllipseRows::ext, -1 = empty row); even sizes are clipped on the right (k - 1 - r).
+struct EllipseRows { int k; int ext[31]; };
+__global__ void __launch_bounds__(256) k_dilate_masked(const float* __restrict__ in, const uint8_t* __restrict__ mask, int H, int W,
+                                                       EllipseRows el, float* __restrict__ out) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= W) return;
+    const int r = el.k / 2;
+    const int yb = blockIdx.y * ROWS_PER_CTA, ye = min(yb + ROWS_PER_CTA, H);
+    for (int y = yb; y < ye; y++) {
+        const size_t i0 = (size_t)y * W + x;
+        float v = in[i0];
+        if (mask[i0]) {
+            bool have = false;
+            float m = 0.0f;
+            for (int i = 0; i < el.k; i++) {
+                const int yy = y + i - r, e = el.ext[i];
+                if (e < 0 || yy < 0 || yy >= H) continue;
+                const int x1 = min(x + min(e, el.k - 1 - r), W - 1);
+                for (int xx = max(x - e, 0); xx <= x1; xx++) {
+                    const float u = in[(size_t)yy * W + xx];
+                    if (!have || u > m) { m = u; have = true; }
+                }
+            }
+            if (have) v = m;
+        }
+        out[i0] = v;
+    }
+}
+int launch_fill_nearest(float* a, float* b, const uint8_t* mask, int H, int W, int k, cudaStream_t st) {
+    if (k < 1 || k > 31) return -1;
+    EllipseRows el;
+    el.k = k;
+    const int r = k / 2;
+    const double inv_r2 = r ? 1.0 / ((double)r * r) : 0.0;
+    for (int i = 0; i < 31; i++) {
+        const int dy = i - r;
+        el.ext[i] = (i < k && abs(dy) <= r) ? (int)lrint(r * sqrt((r * r - dy * dy) * inv_r2)) : -1;
+    }
+    dim3 grid((W + 255) / 256, (H + ROWS_PER_CTA - 1) / ROWS_PER_CTA, 1);
+    for (int it = 0; it < k; it++) {       // ping-pong a -> b -> a ...; the result of k passes is in (k odd ? b : a)
+        k_dilate_masked<<<grid, 256, 0, st>>>((it & 1) ? b : a, mask, H, W, el, (it & 1) ? a : b);
+    }
+    return k;
 }

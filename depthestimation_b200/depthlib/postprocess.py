@@ -33,12 +33,17 @@ def detect_outliers(disparity, threshold=3.0, kernel_size=5, engine=None):
     return (masked != d) & (d > 0)
 
 
-def fill_holes(disparity, mask=None, method='inpaint', kernel_size=5):
-    """Host-side hole filling (postprocess.py:72-118): Telea inpainting or iterated dilation."""
-    import cv2
+def fill_holes(disparity, mask=None, method='inpaint', kernel_size=5, engine=None):
+    """Hole filling (postprocess.py:72-118). method='nearest' (iterated dilation under the hole mask) runs on the GPU
+    (``b200s_fill_nearest``, bit-exact for float32 maps); method='inpaint' (Telea, a sequential fast-marching method)
+    stays host cv2, as does 'nearest' for element sizes the kernel does not take (> 31) or non-float32 input."""
     filled = disparity.copy()
     if mask is None:
         mask = (disparity <= 0)
+    if method == 'nearest' and 1 <= int(kernel_size) <= 31 and np.asarray(disparity).dtype == np.float32 \
+            and np.asarray(disparity).ndim == 2:
+        return _engine(engine).fill_nearest(disparity, mask, int(kernel_size))
+    import cv2
     hole_mask = mask.astype(np.uint8) * 255
     if method == 'inpaint':
         filled = cv2.inpaint(filled.astype(np.float32), hole_mask, kernel_size, cv2.INPAINT_TELEA)
@@ -67,5 +72,5 @@ def postprocess_disparity(disparity, **kwargs):
     pp = make_post_params(False, speckle, max_diff, thr, outl)
     pp.fastMode = 4  # speckle (+ outliers), no median
     result = eng.postprocess(d, pp)
-    result = fill_holes(result, method=kwargs.get('fill_method', 'inpaint'), kernel_size=kwargs.get('fill_kernel', 3))
+    result = fill_holes(result, method=kwargs.get('fill_method', 'inpaint'), kernel_size=kwargs.get('fill_kernel', 3), engine=eng)
     return eng.postprocess(result.astype(np.float32), make_post_params(True))

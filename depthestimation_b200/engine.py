@@ -220,6 +220,19 @@ class StereoEngine:
                                                     C.byref(pp)), "b200s_postprocess")
         return out
 
+    def fill_nearest(self, disp, mask=None, kernel_size: int = 5) -> np.ndarray:
+        """== fill_holes(disp, mask, method='nearest', kernel_size) of depthlib/postprocess.py:72-118 (mask None: disp <= 0)."""
+        out = np.array(disp, dtype=np.float32, order="C", copy=True)
+        if out.ndim != 2:
+            raise ValueError("fill_nearest expects a 2-D disparity map")
+        m = None if mask is None else np.ascontiguousarray(np.asarray(mask, bool), dtype=np.uint8)
+        if m is not None and m.shape != out.shape:
+            raise ValueError("fill_nearest: mask and disparity shapes differ")
+        if out.size:
+            self._check(self._lib.b200s_fill_nearest(self._h, out.ctypes.data, None if m is None else m.ctypes.data,
+                                                     out.shape[0], out.shape[1], int(kernel_size)), "b200s_fill_nearest")
+        return out
+
     def disp_to_depth(self, disp, dp: B200sDepthParams) -> np.ndarray:
         a = np.ascontiguousarray(disp, dtype=np.float32)
         out = np.empty_like(a)

@@ -133,6 +133,13 @@ int b200s_sgbm_compute(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H
  * fastMode, cv2.medianBlur(d, 3) (stereo_core.py:173). In place on a dense float32 H x W. */
 int b200s_postprocess(B200sHandle* h, float* disp, int H, int W, const B200sPostParams* pp);
 
+/* fill_holes(disparity, mask, method='nearest', kernel_size) (depthlib/postprocess.py:72-118, the dilation branch
+ * :106-116): kernel_size times, every hole pixel takes the maximum over the kernel_size x kernel_size ellipse
+ * (cv2.getStructuringElement(MORPH_ELLIPSE) / cv2.dilate). mask: H x W bytes, non-zero = hole, or NULL for the
+ * reference's default (disparity <= 0). In place on a dense float32 H x W; 1 <= kernel_size <= 31.
+ * (method='inpaint', Telea fast marching, stays host cv2: see DESIGN.md.) */
+int b200s_fill_nearest(B200sHandle* h, float* disp, const uint8_t* mask, int H, int W, int kernel_size);
+
 /* StereoCore.disparity_to_depth (depthlib/stereo_core.py:234-272) on n dense float32 values. */
 int b200s_disp_to_depth(B200sHandle* h, const float* disp, size_t n, const B200sDepthParams* dp,
                         float* depth);

@@ -166,6 +166,18 @@ def resize_area(img: np.ndarray, dsize) -> np.ndarray:
     return out
 
 
+def fill_nearest(disp: np.ndarray, mask=None, kernel_size: int = 5) -> np.ndarray:
+    """fill_holes(disparity, mask, method='nearest', kernel_size) of depthlib/postprocess.py:72-118 (mask None: disparity <= 0)."""
+    d = np.ascontiguousarray(disp, dtype=np.float32).copy()
+    m = np.ascontiguousarray((d <= 0) if mask is None else np.asarray(mask, bool), dtype=np.uint8)
+    fn = lib().orc_fill_nearest_f32
+    fn.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_uint8), ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    fn.restype = ctypes.c_int
+    if fn(_p(d, ctypes.c_float), _p(m, ctypes.c_uint8), d.shape[0], d.shape[1], int(kernel_size)):
+        raise ValueError("fill_nearest: kernel_size must be in 1..63")
+    return d
+
+
 def median3_f32(a: np.ndarray) -> np.ndarray:
     a = np.ascontiguousarray(a, dtype=np.float32)
     out = np.empty_like(a)

@@ -8,6 +8,7 @@
  *   orc_box5_mean      cv2.boxFilter(f32, -1, (5,5))                  depthlib/postprocess.py:59,63
  *   orc_postprocess    postprocess_disparity (hole filling off)       depthlib/postprocess.py:120-171
  *   orc_disp_to_depth  StereoCore.disparity_to_depth                  depthlib/stereo_core.py:234-272
+ *   orc_fill_nearest   fill_holes(method='nearest'): k x dilate(ellipse k x k) under the hole mask   depthlib/postprocess.py:106-116
  * The arithmetic of the cv2 calls lives in the opencv-python wheel (not under /root/reference); it is
  * restated from SURVEY.md Appendix B and pinned against the live cv2 binary by tests/test_oracle_vs_cv2.py.
  * Compile with -ffp-contract=off: the float32 chain must not be fused into FMAs.
@@ -211,5 +212,60 @@ int orc_resize_area_u8(const uint8_t *src, int sH, int sW, int cn, uint8_t *dst,
                 dst[((size_t)y * dW + x) * cn + c] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
             }
     free(xt); free(yt); free(xo); free(yo);
+    return 0;
+}
+
+/* ---- fill_holes(method='nearest') (depthlib/postprocess.py:106-116) -------------------------------------------
+ * kernel = cv2.getStructuringElement(MORPH_ELLIPSE, (k, k)); k times: filled = where(mask, cv2.dilate(filled, kernel), filled).
+ * The ellipse rows follow OpenCV's getStructuringElement: with r = c = k / 2, row i (dy = i - r) holds ones in
+ * [c - dx, min(c + dx, k - 1)] with dx = round(c * sqrt((r*r - dy*dy) / (r*r))) (k = 1: the single pixel). cv2.dilate = maximum over
+ * the element anchored at its centre; pixels outside the image do not take part. (The distance transform the reference
+ * also computes there is never used.) ext[i] = dx of row i, or -1 for an empty row. */
+int orc_ellipse_rows(int k, int *ext)
+{
+    if (k < 1) return -1;
+    int r = k / 2, c = k / 2;
+    double inv_r2 = r ? 1.0 / ((double)r * r) : 0.0;
+    for (int i = 0; i < k; i++) {
+        int dy = i - r;
+        ext[i] = -1;
+        if (abs(dy) <= r) ext[i] = (int)lrint(c * sqrt((r * r - dy * dy) * inv_r2));
+    }
+    return 0;
+}
+
+int orc_fill_nearest_f32(float *img, const uint8_t *mask, int H, int W, int k)
+{
+    if (k < 1 || k > 63) return -1;
+    int ext[64];
+    orc_ellipse_rows(k, ext);
+    size_t n = (size_t)H * W;
+    float *tmp = (float *)malloc(n * sizeof(float));
+    if (!tmp) return -2;
+    int r = k / 2;
+    for (int it = 0; it < k; it++) {
+        for (int y = 0; y < H; y++)
+            for (int x = 0; x < W; x++) {
+                float v = img[(size_t)y * W + x];
+                if (mask[(size_t)y * W + x]) {
+                    int have = 0;
+                    float m = 0.0f;
+                    for (int i = 0; i < k; i++) {
+                        int yy = y + i - r;
+                        if (ext[i] < 0 || yy < 0 || yy >= H) continue;
+                        const int right = ext[i] < k - 1 - r ? ext[i] : k - 1 - r;   /* even k: the element is clipped on the right */
+                        for (int xx = x - ext[i]; xx <= x + right; xx++) {
+                            if (xx < 0 || xx >= W) continue;
+                            float u = img[(size_t)yy * W + xx];
+                            if (!have || u > m) { m = u; have = 1; }
+                        }
+                    }
+                    if (have) v = m;
+                }
+                tmp[(size_t)y * W + x] = v;
+            }
+        memcpy(img, tmp, n * sizeof(float));
+    }
+    free(tmp);
     return 0;
 }

@@ -214,3 +214,30 @@ def test_batch_submit_wait_overlapped_chunks(engine):
     engine.pipeline_batch_wait(t1)
     with pytest.raises((EngineError, KeyError)):
         engine.pipeline_batch_wait(t1)
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 5, 7, 11, 31])
+def test_fill_nearest(engine, k):
+    """b200s_fill_nearest == fill_holes(method='nearest') (oracle pinned against cv2), default and explicit masks,
+    holes wider than the element and on the border, a ragged width."""
+    rng = np.random.default_rng(70 + k)
+    H, W = 61, 301
+    d = (rng.random((H, W)) * 60).astype(np.float32)
+    d[rng.random((H, W)) < 0.35] = 0.0
+    d[10:40, 20:90] = 0.0
+    d[:, :2] = 0.0
+    d[-3:, :] = -1.0
+    assert np.array_equal(engine.fill_nearest(d, None, k), oracle.fill_nearest(d, None, k))
+    mask = rng.random((H, W)) < 0.3
+    assert np.array_equal(engine.fill_nearest(d, mask, k), oracle.fill_nearest(d, mask, k))
+
+
+def test_fill_nearest_through_depthlib(engine):
+    """depthlib.postprocess.fill_holes(method='nearest') routes to the engine; bad sizes are rejected by the C ABI."""
+    from depthestimation_b200.depthlib.postprocess import fill_holes
+    rng = np.random.default_rng(5)
+    d = (rng.random((40, 50)) * 30).astype(np.float32)
+    d[rng.random((40, 50)) < 0.4] = 0.0
+    assert np.array_equal(fill_holes(d, method='nearest', kernel_size=5, engine=engine), oracle.fill_nearest(d, None, 5))
+    with pytest.raises(Exception):
+        engine.fill_nearest(d, None, 33)

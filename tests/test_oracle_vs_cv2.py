@@ -93,3 +93,23 @@ def test_resize_area_matches_cv2(H, W, f, cn):
     dsize = (int(W * f), int(H * f))
     ref = cv2.resize(img, dsize, interpolation=cv2.INTER_AREA)
     assert np.array_equal(oracle.resize_area(img, dsize), ref)
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 5, 7, 9, 11])
+def test_fill_nearest_matches_cv2(k):
+    """fill_holes(method='nearest') exactly as depthlib/postprocess.py:106-116 spells it with cv2 (ellipse element, k dilations
+    under the hole mask), default mask (disparity <= 0) and an explicit one."""
+    import cv2
+    rng = np.random.default_rng(40 + k)
+    H, W = 57, 83
+    d = (rng.random((H, W)) * 60).astype(np.float32)
+    d[rng.random((H, W)) < 0.35] = 0.0
+    d[10:30, 20:50] = 0.0                      # a hole wider than the element
+    d[0:3, :] = 0.0                            # holes on the border
+    for mask in (None, rng.random((H, W)) < 0.3):
+        m = (d <= 0) if mask is None else mask
+        kernel = cv2.getStructuringElement(cv2.MORPH_ELLIPSE, (k, k))
+        ref = d.copy()
+        for _ in range(k):
+            ref = np.where(m, cv2.dilate(ref, kernel), ref)
+        assert np.array_equal(oracle.fill_nearest(d, mask, k), ref)
