@@ -49,6 +49,7 @@ SYMBOLS = {
     "b200s_set_maps": (C.c_int, [_H, _VP, _VP, _VP, _VP, C.c_int, C.c_int]),
     "b200s_bgr2gray": (C.c_int, [_H, _VP, C.c_int, C.c_int, C.c_size_t, _VP]),
     "b200s_resize_area_u8": (C.c_int, [_H, _VP, C.c_int, C.c_int, C.c_int, C.c_size_t, _VP, C.c_int, C.c_int]),
+    "b200s_resize_linear_u8": (C.c_int, [_H, _VP, C.c_int, C.c_int, C.c_int, C.c_size_t, _VP, C.c_int, C.c_int]),
     "b200s_remap_u8": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_size_t, _VP, _VP]),
     "b200s_sgbm_compute": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_size_t, _VP]),
     "b200s_postprocess": (C.c_int, [_H, _VP, C.c_int, C.c_int, _PP]),

@@ -558,6 +558,49 @@ int b200s_resize_area_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int
     return check_launch(h, "resize_area");
 }
 
+// per-axis taps of cv2's INTER_LINEAR for uint8 (see oracle/imgops_oracle.c: orc_linear_tab)
+static void linear_table(int ssize, int dsize, bool snap, std::vector<int4>& tab) {
+    const double scale = 1.0 / ((double)dsize / ssize);
+    tab.resize(dsize);
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= (float)s;
+        if (snap) {
+            if (s < 0) { f = 0.f; s = 0; }
+            if (s >= ssize - 1) { f = 0.f; s = ssize - 1; }
+        }
+        int c0 = (int)lrintf((1.f - f) * 2048.f), c1 = (int)lrintf(f * 2048.f);
+        if (c0 > 32767) c0 = 32767;
+        if (c1 > 32767) c1 = 32767;
+        tab[d] = make_int4(s, c0, c1, 0);
+    }
+}
+
+int b200s_resize_linear_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int cn, size_t stride, uint8_t* dst, int dH, int dW) {
+    if (!h) return B200S_E_INVALID;
+    if (!src || !dst || sH <= 0 || sW <= 0 || dH <= 0 || dW <= 0 || (cn != 1 && cn != 3) || stride < (size_t)cn * sW) { h->set_error(B200S_E_INVALID, "resize_linear: bad arguments"); return B200S_E_INVALID; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const size_t ns = (size_t)sH * sW * cn, nd = (size_t)dH * dW * cn;
+    CUDA_TRY(h, h->hostio.ensure(ns));
+    CUDA_TRY(h, h->imgL.ensure(nd));
+    CUDA_TRY(h, cudaMemcpy2DAsync(h->hostio.p, (size_t)cn * sW, src, stride, (size_t)cn * sW, sH, cudaMemcpyHostToDevice, h->stream));
+    std::vector<int4> tx, ty;
+    linear_table(sW, dW, true, tx);
+    linear_table(sH, dH, false, ty);
+    CUDA_TRY(h, h->imgR.ensure((tx.size() + ty.size()) * sizeof(int4)));
+    int4* dtx = h->imgR.as<int4>();
+    int4* dty = dtx + tx.size();
+    CUDA_TRY(h, cudaMemcpyAsync(dtx, tx.data(), tx.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(dty, ty.data(), ty.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));     // the host vectors go out of scope below
+    launch_resize_linear(h->hostio.as<uint8_t>(), sH, sW, cn, dtx, dty, h->imgL.as<uint8_t>(), dH, dW, h->stream);
+    h->launches++;
+    CUDA_TRY(h, cudaMemcpyAsync(dst, h->imgL.p, nd, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "resize_linear");
+}
+
 int b200s_remap_u8(B200sHandle* h, const uint8_t* L, const uint8_t* R, int srcH, int srcW, size_t stride, uint8_t* outL, uint8_t* outR) {
     if (!h) return B200S_E_INVALID;
     if (!L || !R || !outL || !outR || srcH <= 0 || srcW <= 0 || stride < (size_t)srcW) { h->set_error(B200S_E_INVALID, "remap: bad arguments"); return B200S_E_INVALID; }

@@ -127,6 +127,8 @@ void launch_outliers_s16(const int16_t* d16, float* out, int B, int H, int W, fl
 void launch_crop_s16(const int16_t* d16, int B, int H, int W, int x0, int16_t* out, cudaStream_t st);
 void launch_median3_f32_depth(const float* src, float* dst, int B, int H, int W, const B200sDepthParams& dp, float* Z, cudaStream_t st);
 void launch_median3_f32(const float* src, float* dst, int B, int H, int W, cudaStream_t st);
+void launch_resize_linear(const uint8_t* src, int sH, int sW, int cn, const int4* tx, const int4* ty, uint8_t* dst, int dH, int dW,
+                          cudaStream_t st);
 // k masked dilations (ping-pong a <-> b, result in b when k is odd, else a); returns the launch count or -1
 int launch_fill_nearest(float* a, float* b, const uint8_t* mask, int H, int W, int k, cudaStream_t st);
 void launch_depth(const float* disp, size_t n, const B200sDepthParams& dp, float* Z, cudaStream_t st);

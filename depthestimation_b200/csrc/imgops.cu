@@ -6,6 +6,7 @@
 //   outliers      detect_outliers + masking                          depthlib/postprocess.py:37-70,151-158
 //   median3 f32   cv2.medianBlur(float32, 3)                         depthlib/postprocess.py:169, stereo_core.py:173
 //   depth         StereoCore.disparity_to_depth                      depthlib/stereo_core.py:234-272
+//   resize lin    cv2.resize(img, size, INTER_LINEAR) (size fix-up)  depthlib/rectify.py:92-105
 //   fill nearest  fill_holes(method='nearest')                       depthlib/postprocess.py:106-116
 // The float chain uses explicit round-to-nearest intrinsics (no FMA contraction, no fast math).
 #include "common.cuh"
@@ -363,4 +364,33 @@ int launch_fill_nearest(float* a, float* b, const uint8_t* mask, int H, int W, i
         k_dilate_masked<<<grid, 256, 0, st>>>((it & 1) ? b : a, mask, H, W, el, (it & 1) ? a : b);
     }
     return k;
+}
+
+// ---- cv2.resize(INTER_LINEAR) for uint8: 11-bit fixed-point bilinear, per-axis tap tables built on the host ----------
+// tap = {source index, coefficient of it, coefficient of the next one}; x indices are already snapped to the border,
+// y indices are clipped here with their weights kept (that is how cv2 treats the two axes, see the oracle).
+__global__ void __launch_bounds__(256) k_resize_linear(const uint8_t* __restrict__ src, int sH, int sW, int cn,
+                                                       const int4* __restrict__ tx, const int4* __restrict__ ty,
+                                                       uint8_t* __restrict__ dst, int dH, int dW) {
+    const size_t n = (size_t)dH * dW * cn;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const size_t i = ((size_t)blockIdx.x * 4 + k) * 256 + threadIdx.x;
+        if (i >= n) return;
+        const int c = (int)(i % cn), x = (int)((i / cn) % dW), y = (int)(i / ((size_t)cn * dW));
+        const int4 ax = tx[x], ay = ty[y];
+        const int x0 = ax.x, x1 = min(x0 + 1, sW - 1);
+        const int y0 = min(max(ay.x, 0), sH - 1), y1 = min(max(ay.x + 1, 0), sH - 1);
+        const uint8_t* r0 = src + (size_t)y0 * sW * cn + c;
+        const uint8_t* r1 = src + (size_t)y1 * sW * cn + c;
+        const int h0 = r0[(size_t)x0 * cn] * ax.y + r0[(size_t)x1 * cn] * ax.z;
+        const int h1 = r1[(size_t)x0 * cn] * ax.y + r1[(size_t)x1 * cn] * ax.z;
+        const int v = (((ay.y * (h0 >> 4)) >> 16) + ((ay.z * (h1 >> 4)) >> 16) + 2) >> 2;
+        dst[i] = (uint8_t)min(max(v, 0), 255);
+    }
+}
+void launch_resize_linear(const uint8_t* src, int sH, int sW, int cn, const int4* tx, const int4* ty, uint8_t* dst, int dH, int dW,
+                          cudaStream_t st) {
+    const size_t n = (size_t)dH * dW * cn;
+    k_resize_linear<<<(unsigned)((n + 1023) / 1024), 256, 0, st>>>(src, sH, sW, cn, tx, ty, dst, dH, dW);
 }

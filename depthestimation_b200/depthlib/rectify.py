@@ -4,7 +4,7 @@ Per frame (hot path): gray conversion and the two bilinear remaps run on the GPU
 ``b200s_bgr2gray`` / ``b200s_remap_u8``; reference: rectify.py:108-119, 185-186).
 Once per calibration (cold): the maps themselves come from host ``cv2.stereoRectify`` +
 ``cv2.initUndistortRectifyMap`` exactly as rectify.py:63-73 does (double-precision camera math,
-out of the hot path — SURVEY.md §2 row 2). Size fix-up (rectify.py:92-105) stays host ``cv2.resize``.
+out of the hot path — SURVEY.md §2 row 2). The size fix-up (rectify.py:92-105) runs on the GPU too (``b200s_resize_linear_u8``).
 """
 from __future__ import annotations
 
@@ -96,13 +96,17 @@ def _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
     return {'map1_L': map1_L, 'map2_L': map2_L, 'map1_R': map1_R, 'map2_R': map2_R}
 
 
-def _ensure_image_size(image: np.ndarray, size: Tuple[int, int]) -> np.ndarray:
-    """Warn and resize (INTER_LINEAR, host) when the image does not match the calibration size."""
+def _ensure_image_size(image: np.ndarray, size: Tuple[int, int], engine=None) -> np.ndarray:
+    """Warn and resize (INTER_LINEAR) when the image does not match the calibration size (rectify.py:92-105): uint8
+    gray / 3-channel images on the GPU (b200s_resize_linear_u8, bit-exact), anything else through host cv2."""
     height, width = image.shape[:2]
     if (width, height) == tuple(size):
         return image
     warnings.warn("Input image size %sx%s does not match calibration %sx%s; resizing for rectification." %
                   (width, height, size[0], size[1]), RuntimeWarning, stacklevel=2)
+    if image.dtype == np.uint8 and (image.ndim == 2 or (image.ndim == 3 and image.shape[2] in (1, 3))):
+        out = _engine(engine).resize_linear(image, tuple(size))
+        return out[:, :, 0] if (image.ndim == 3 and image.shape[2] == 1) else out   # cv2.resize drops a singleton channel
     return _cv2().resize(image, tuple(size), interpolation=_cv2().INTER_LINEAR)
 
 
@@ -131,9 +135,9 @@ def rectify_images(img_L: np.ndarray, img_R: np.ndarray, cam_matrix_L: np.ndarra
         maps = _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
                            dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
     size = (image_width, image_height)
-    img_L = _ensure_image_size(img_L, size)
-    img_R = _ensure_image_size(img_R, size)
     eng = _engine(engine)
+    img_L = _ensure_image_size(img_L, size, eng)
+    img_R = _ensure_image_size(img_R, size, eng)
     gray_L = np.ascontiguousarray(_to_grayscale(img_L, eng))
     gray_R = np.ascontiguousarray(_to_grayscale(img_R, eng))
     if getattr(eng, "_maps_id", None) != id(maps):

@@ -191,6 +191,19 @@ class StereoEngine:
                                                    img.strides[0], out.ctypes.data, dH, dW), "b200s_resize_area_u8")
         return out
 
+    def resize_linear(self, img, dsize):
+        """== cv2.resize(img, (dW, dH), interpolation=cv2.INTER_LINEAR) for uint8 HxW or HxWx3 (rectify.py:92-105)."""
+        img = np.asarray(img)
+        if img.dtype != np.uint8 or img.ndim not in (2, 3) or (img.ndim == 3 and img.shape[2] not in (1, 3)):
+            raise ValueError("resize_linear expects a uint8 HxW or HxWx3 image")
+        img = np.ascontiguousarray(img)
+        cn = 1 if img.ndim == 2 else img.shape[2]
+        dW, dH = int(dsize[0]), int(dsize[1])
+        out = np.empty((dH, dW) if img.ndim == 2 else (dH, dW, cn), np.uint8)
+        self._check(self._lib.b200s_resize_linear_u8(self._h, img.ctypes.data, img.shape[0], img.shape[1], cn,
+                                                     img.strides[0], out.ctypes.data, dH, dW), "b200s_resize_linear_u8")
+        return out
+
     def remap(self, left, right):
         if self.maps_shape is None:
             raise EngineError("remap: rectification maps not set")

@@ -120,6 +120,12 @@ int b200s_bgr2gray(B200sHandle* h, const uint8_t* img, int H, int W, size_t stri
 int b200s_resize_area_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int cn, size_t stride,
                          uint8_t* dst, int dH, int dW);
 
+/* cv2.resize(image, size, interpolation=cv2.INTER_LINEAR) at depthlib/rectify.py:92-105 (_ensure_image_size: the
+ * input does not match the calibration size): uint8, cn = 1 or 3 interleaved channels, any scale. OpenCV's 11-bit
+ * fixed-point bilinear, bit-exact. dst is dense dH x dW x cn. */
+int b200s_resize_linear_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int cn, size_t stride,
+                           uint8_t* dst, int dH, int dW);
+
 /* 2x cv2.remap(gray, map1, map2, INTER_LINEAR) at depthlib/rectify.py:185-186. Source images
  * are srcH x srcW; outputs have the size of the maps (dense). */
 int b200s_remap_u8(B200sHandle* h, const uint8_t* L, const uint8_t* R, int srcH, int srcW,

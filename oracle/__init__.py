@@ -166,6 +166,21 @@ def resize_area(img: np.ndarray, dsize) -> np.ndarray:
     return out
 
 
+def resize_linear(img: np.ndarray, dsize) -> np.ndarray:
+    """cv2.resize(img, (dW, dH), interpolation=cv2.INTER_LINEAR) for uint8 [H,W] or [H,W,C] (depthlib/rectify.py:92-105)."""
+    img = np.ascontiguousarray(img, np.uint8)
+    dW, dH = int(dsize[0]), int(dsize[1])
+    cn = 1 if img.ndim == 2 else img.shape[2]
+    out = np.empty((dH, dW) if img.ndim == 2 else (dH, dW, cn), np.uint8)
+    fn = lib().orc_resize_linear_u8
+    fn.argtypes = [ctypes.POINTER(ctypes.c_uint8), ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                   ctypes.POINTER(ctypes.c_uint8), ctypes.c_int, ctypes.c_int]
+    fn.restype = ctypes.c_int
+    if fn(_p(img, ctypes.c_uint8), img.shape[0], img.shape[1], cn, _p(out, ctypes.c_uint8), dH, dW):
+        raise ValueError("resize_linear: bad arguments")
+    return out
+
+
 def fill_nearest(disp: np.ndarray, mask=None, kernel_size: int = 5) -> np.ndarray:
     """fill_holes(disparity, mask, method='nearest', kernel_size) of depthlib/postprocess.py:72-118 (mask None: disparity <= 0)."""
     d = np.ascontiguousarray(disp, dtype=np.float32).copy()

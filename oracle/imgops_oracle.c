@@ -8,6 +8,7 @@
  *   orc_box5_mean      cv2.boxFilter(f32, -1, (5,5))                  depthlib/postprocess.py:59,63
  *   orc_postprocess    postprocess_disparity (hole filling off)       depthlib/postprocess.py:120-171
  *   orc_disp_to_depth  StereoCore.disparity_to_depth                  depthlib/stereo_core.py:234-272
+ *   orc_resize_linear  cv2.resize(img, size, INTER_LINEAR), uint8 (the size fix-up)   depthlib/rectify.py:92-105
  *   orc_fill_nearest   fill_holes(method='nearest'): k x dilate(ellipse k x k) under the hole mask   depthlib/postprocess.py:106-116
  * The arithmetic of the cv2 calls lives in the opencv-python wheel (not under /root/reference); it is
  * restated from SURVEY.md Appendix B and pinned against the live cv2 binary by tests/test_oracle_vs_cv2.py.
@@ -267,5 +268,52 @@ int orc_fill_nearest_f32(float *img, const uint8_t *mask, int H, int W, int k)
         memcpy(img, tmp, n * sizeof(float));
     }
     free(tmp);
+    return 0;
+}
+
+/* ---- cv2.resize(img, (dW, dH), interpolation=cv2.INTER_LINEAR) for uint8 (depthlib/rectify.py:92-105) ---------------
+ * OpenCV's fixed-point bilinear: per axis f = (float)((d + 0.5) * scale - 0.5), s = floor(f), f -= s, 11-bit
+ * coefficients cvRound((1 - f) * 2048), cvRound(f * 2048). Along x an index outside [0, sW-1) snaps to the border
+ * with f = 0; along y only the row INDEX is clipped (the weights stay), which rounds differently at the border.
+ * Horizontal pass in int (no shift), vertical pass ((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2. */
+typedef struct { int ofs; int c0, c1; } OrcLinTap;
+static int orc_round_half_even(float v) { return (int)lrintf(v); }
+void orc_linear_tab(int ssize, int dsize, int snap, OrcLinTap *tab)
+{
+    const double scale = 1.0 / ((double)dsize / ssize);
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= (float)s;
+        if (snap) {
+            if (s < 0) { f = 0.f; s = 0; }
+            if (s >= ssize - 1) { f = 0.f; s = ssize - 1; }
+        }
+        int c0 = orc_round_half_even((1.f - f) * 2048.f), c1 = orc_round_half_even(f * 2048.f);
+        if (c0 > 32767) c0 = 32767;
+        if (c1 > 32767) c1 = 32767;
+        tab[d].ofs = s; tab[d].c0 = c0; tab[d].c1 = c1;
+    }
+}
+int orc_resize_linear_u8(const uint8_t *src, int sH, int sW, int cn, uint8_t *dst, int dH, int dW)
+{
+    if (sH <= 0 || sW <= 0 || dH <= 0 || dW <= 0 || cn < 1) return -1;
+    OrcLinTap *tx = (OrcLinTap *)malloc(sizeof(OrcLinTap) * (size_t)dW), *ty = (OrcLinTap *)malloc(sizeof(OrcLinTap) * (size_t)dH);
+    if (!tx || !ty) { free(tx); free(ty); return -2; }
+    orc_linear_tab(sW, dW, 1, tx);
+    orc_linear_tab(sH, dH, 0, ty);
+    for (int y = 0; y < dH; y++) {
+        const int y0 = clampi(ty[y].ofs, 0, sH - 1), y1 = clampi(ty[y].ofs + 1, 0, sH - 1);
+        for (int x = 0; x < dW; x++) {
+            const int x0 = tx[x].ofs, x1 = x0 + 1 < sW ? x0 + 1 : sW - 1;
+            for (int c = 0; c < cn; c++) {
+                const int h0 = src[((size_t)y0 * sW + x0) * cn + c] * tx[x].c0 + src[((size_t)y0 * sW + x1) * cn + c] * tx[x].c1;
+                const int h1 = src[((size_t)y1 * sW + x0) * cn + c] * tx[x].c0 + src[((size_t)y1 * sW + x1) * cn + c] * tx[x].c1;
+                int v = (((ty[y].c0 * (h0 >> 4)) >> 16) + ((ty[y].c1 * (h1 >> 4)) >> 16) + 2) >> 2;
+                dst[((size_t)y * dW + x) * cn + c] = (uint8_t)clampi(v, 0, 255);
+            }
+        }
+    }
+    free(tx); free(ty);
     return 0;
 }

@@ -241,3 +241,29 @@ def test_fill_nearest_through_depthlib(engine):
     assert np.array_equal(fill_holes(d, method='nearest', kernel_size=5, engine=engine), oracle.fill_nearest(d, None, 5))
     with pytest.raises(Exception):
         engine.fill_nearest(d, None, 33)
+
+
+def test_resize_linear(engine):
+    """b200s_resize_linear_u8 == cv2.resize(INTER_LINEAR) (oracle pinned against cv2): up / down / mixed scales, the
+    exact 2x case, identity, 1 and 3 channels, a strided source."""
+    rng = np.random.default_rng(21)
+    cases = [(100, 200, 50, 100), (99, 200, 49, 100), (40, 50, 160, 200), (7, 9, 70, 90), (64, 64, 64, 64), (5, 5, 1, 1),
+             (375, 1242, 370, 1226), (370, 1226, 375, 1242), (88, 283, 247, 84)]
+    for i, (sH, sW, dH, dW) in enumerate(cases):
+        cn = 3 if i % 2 else 1
+        img = rng.integers(0, 256, (sH, sW, cn) if cn == 3 else (sH, sW), dtype=np.uint8)
+        assert np.array_equal(engine.resize_linear(img, (dW, dH)), oracle.resize_linear(img, (dW, dH))), (sH, sW, dH, dW, cn)
+    big = rng.integers(0, 256, (60, 100), dtype=np.uint8)
+    view = big[:, 10:90]                       # row stride 100, width 80
+    assert np.array_equal(engine.resize_linear(view, (50, 33)), oracle.resize_linear(np.ascontiguousarray(view), (50, 33)))
+
+
+def test_size_fixup_through_depthlib(engine):
+    """rectify._ensure_image_size warns and resizes on the GPU exactly like the reference's cv2.resize(INTER_LINEAR)."""
+    from depthestimation_b200.depthlib.rectify import _ensure_image_size
+    rng = np.random.default_rng(22)
+    img = rng.integers(0, 256, (90, 150, 3), dtype=np.uint8)
+    with pytest.warns(RuntimeWarning):
+        out = _ensure_image_size(img, (160, 96), engine)
+    assert np.array_equal(out, oracle.resize_linear(img, (160, 96)))
+    assert _ensure_image_size(img, (150, 90), engine) is img

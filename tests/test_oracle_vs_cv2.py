@@ -113,3 +113,20 @@ def test_fill_nearest_matches_cv2(k):
         for _ in range(k):
             ref = np.where(m, cv2.dilate(ref, kernel), ref)
         assert np.array_equal(oracle.fill_nearest(d, mask, k), ref)
+
+
+def test_resize_linear_matches_cv2():
+    """INTER_LINEAR resize of uint8 images as rectify.py:92-105 calls it (the size fix-up): random up / down scales, the
+    exact 2x case (which cv2 may route to INTER_AREA), identity, 1- and 3-channel."""
+    import cv2
+    rng = np.random.default_rng(11)
+    cases = [(100, 200, 50, 100), (99, 200, 49, 100), (90, 120, 30, 40), (40, 50, 160, 200), (7, 9, 70, 90),
+             (64, 64, 64, 64), (5, 5, 1, 1), (6, 8, 3, 4), (375, 1242, 370, 1226), (370, 1226, 375, 1242)]
+    for _ in range(40):
+        cases.append((int(rng.integers(5, 200)), int(rng.integers(5, 300)), int(rng.integers(3, 260)), int(rng.integers(3, 400))))
+    for i, (sH, sW, dH, dW) in enumerate(cases):
+        cn = 3 if i % 2 else 1
+        img = rng.integers(0, 256, (sH, sW, cn) if cn == 3 else (sH, sW), dtype=np.uint8)
+        ref = cv2.resize(img, (dW, dH), interpolation=cv2.INTER_LINEAR)
+        got = oracle.resize_linear(img, (dW, dH))
+        assert np.array_equal(got, ref), f"{(sH, sW)} -> {(dH, dW)} x{cn}: {(got != ref).sum()} of {ref.size} differ"
