@@ -51,11 +51,11 @@ struct B200sHandle {
     DevBuf maps;  // 4 x H x W float
     // scratch
     DevBuf imgL, imgR, rectL, rectR, recL, recR, C, S, Calt, raw, med, labels, sizes, f0, f1, s16c, hostio, ck, keys;
-    // asynchronous host-batch pipeline: three slots, copies on their own streams so that the H2D of chunk k+1 and
+    // asynchronous host-batch pipeline: four slots, copies on their own streams so that the H2D of chunk k+1 and
     // the D2H of chunk k-1 overlap the kernels of chunk k
-    // (the third slot lets chunk k+1 be uploaded while chunk k-1 is still being downloaded: with two, a download slower
-    // than the kernels - eight GPUs sharing the host's PCIe / memory throughput - stalled the next upload and the GPU)
-    enum { NSLOT = 3 };
+    // (more than two slots let chunks k+1, k+2 be uploaded while chunk k-1 is still being downloaded: with two, a download
+    // slower than the kernels - eight GPUs sharing the host's PCIe / memory throughput - stalled the next upload and the GPU)
+    enum { NSLOT = 4 };
     struct Slot {
         DevBuf inL, inR, out;
         cudaEvent_t in_done = nullptr, compute_done = nullptr, out_done = nullptr;

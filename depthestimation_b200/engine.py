@@ -300,7 +300,7 @@ class StereoEngine:
 
     def pipeline_batch_submit(self, lefts, rights, pp, dp, use_maps=False, out_disp=None, out_depth=None):
         """Asynchronous pipeline_batch: enqueue H2D -> kernels -> D2H for one chunk and return a ticket at once.
-        At most three chunks in flight; the arrays (pinned for real overlap) must not be touched until
+        At most four chunks in flight; the arrays (pinned for real overlap) must not be touched until
         pipeline_batch_wait(ticket) returns (disp, depth)."""
         lefts, rights = np.asarray(lefts), np.asarray(rights)
         if lefts.dtype != np.uint8 or rights.dtype != np.uint8 or lefts.ndim != 3 or lefts.shape != rights.shape:

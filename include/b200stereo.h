@@ -175,7 +175,7 @@ int b200s_pipeline_batch(B200sHandle* h, const uint8_t* L, const uint8_t* R, int
 /* The same call split in two, for a frame loop that keeps the GPU busy (the generator of
  * depthlib/StereoDepthEstimatorVideo.py:84-148 reads chunk k+1 while chunk k is computed): submit enqueues
  * H2D -> kernels -> D2H and returns a ticket at once; wait blocks until that chunk's results are in disp/depth.
- * At most three chunks may be in flight (submit k+3 requires wait k); the copies run on their own streams, so
+ * At most four chunks may be in flight (submit k+4 requires wait k); the copies run on their own streams, so
  * the H2D of chunk k+1 and the D2H of chunk k-1 overlap the kernels of chunk k. L/R/disp/depth must stay
  * valid (and should be page-locked for the copies to be asynchronous) until the ticket has been waited for. */
 int b200s_pipeline_batch_submit(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W,

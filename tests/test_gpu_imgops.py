@@ -205,15 +205,17 @@ def test_batch_submit_wait_overlapped_chunks(engine):
     got.append(engine.pipeline_batch_wait(tk))
     for (d0, z0), (d1, z1) in zip(want, got):
         assert np.array_equal(d0, d1) and np.array_equal(z0, z1)
-    # three chunks may be in flight; a fourth submit without waiting, and a wait on a ticket that is not in flight
+    # four chunks may be in flight; a fifth submit without waiting, and a wait on a ticket that is not in flight
     t0 = engine.pipeline_batch_submit(*chunks[0], pp, dp)
     t1 = engine.pipeline_batch_submit(*chunks[1], pp, dp)
     t2 = engine.pipeline_batch_submit(*chunks[2], pp, dp)
+    t3 = engine.pipeline_batch_submit(*chunks[3], pp, dp)
     with pytest.raises(EngineError):
         engine.pipeline_batch_submit(*chunks[0], pp, dp)
     engine.pipeline_batch_wait(t0)
     engine.pipeline_batch_wait(t1)
     engine.pipeline_batch_wait(t2)
+    engine.pipeline_batch_wait(t3)
     with pytest.raises((EngineError, KeyError)):
         engine.pipeline_batch_wait(t1)
 
