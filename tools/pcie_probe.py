@@ -35,8 +35,10 @@ for it in range(2):
         with torch.cuda.stream(s2): d_in.copy_(ins[k % 3], non_blocking=True)
     torch.cuda.synchronize(); dt = time.perf_counter() - t0
 t = torch.tensor([6 * (n + n // 4) / 1e9 / dt], device="cuda")
+per = [torch.zeros_like(t) for _ in range(world)]
+if world > 1: dist.all_gather(per, t)
 if world > 1: dist.all_reduce(t)
-if rank == 0: print(f"both, 3 rotating sets: {float(t):.1f} GB/s aggregate over {world} GPU(s)")
+if rank == 0: print(f"both, 3 rotating sets: {float(t):.1f} GB/s aggregate over {world} GPU(s); per rank: " + " ".join(f"{float(x):.1f}" for x in per))
 # ... and with a bandwidth-bound kernel running beside the copies
 big = torch.empty(2 << 30, dtype=torch.uint8, device="cuda")
 s3 = torch.cuda.Stream()
