@@ -62,6 +62,8 @@ SYMBOLS = {
     "b200s_pipeline_batch": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _PP, _DP, _VP, _VP]),
     "b200s_pipeline_batch_submit": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _PP, _DP, _VP, _VP, _IP]),
     "b200s_pipeline_batch_wait": (C.c_int, [_H, C.c_int]),
+    "b200s_filter_speckles_noalloc": (C.c_int, [_VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _VP,
+                                                C.c_char_p, C.c_size_t]),
     "b200s_stage_times": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.c_int]),
     "b200s_reset_stage_times": (C.c_int, [_H]),
     "b200s_geometry": (C.c_int, [_H, C.c_int, _IP, _IP, _IP, _IP]),

@@ -186,3 +186,76 @@ void launch_speckle(int16_t* img, int B, int H, int W, int newVal, int maxSize, 
     k_ccl_apply<<<blocks, 256, 0, st>>>(img, n, newVal, maxSize, labels, sizes);
     if (launches) *launches += nl;
 }
+
+// ---- allocation-free entry point -----------------------------------------------------------------
+// b200s_filter_speckles_noalloc (include/b200stereo.h): the same four kernels, with labels + sizes in a file-scope
+// device array instead of the handle's cudaMalloc'd scratch, for callers that may not allocate (CUDA graph capture,
+// serving loops). No counterpart in the reference.
+//
+// g_noalloc_scratch is a HOST-side stand-in in host code, not a device address: the device address is taken once per
+// device with cudaGetSymbolAddress (below) and that pointer is what the kernels receive. Every GPU that loads the
+// library holds the array (2 x 4 B x B200S_NOALLOC_MAX_PIXELS = 16 MiB) until the process exits. All calls on a
+// device share it: k_ccl_tile writes every label and size the later kernels read (nothing has to start at zero, so
+// the previous call's contents are harmless), but two calls whose kernels overlap on the GPU race on it.
+#include <mutex>
+#include <stdarg.h>
+
+static __device__ __align__(256) int g_noalloc_scratch[2 * (size_t)B200S_NOALLOC_MAX_PIXELS];
+
+#define NOALLOC_MAX_DEVICES 64
+static std::mutex g_noalloc_mu;
+static int* g_noalloc_ptr[NOALLOC_MAX_DEVICES];   // device address of g_noalloc_scratch, per device ordinal
+
+static int noalloc_fail(char* err, size_t cap, int code, const char* fmt, ...) {
+    if (err && cap) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, cap, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+// once per device, with that device current
+static cudaError_t noalloc_scratch(int dev, int** out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        int* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return cudaSuccess;
+}
+
+extern "C" int b200s_filter_speckles_noalloc(const int16_t* d_src, int16_t* d_dst, int H, int W, int new_val, int max_size,
+                                             int max_diff, void* cuda_stream, char* err, size_t err_cap) {
+    if (err && err_cap) err[0] = 0;
+    if (!d_src || !d_dst) return noalloc_fail(err, err_cap, B200S_E_INVALID, "filter_speckles_noalloc: null device pointer");
+    if (H <= 0 || W <= 0) return noalloc_fail(err, err_cap, B200S_E_INVALID, "filter_speckles_noalloc: bad size %dx%d", W, H);
+    if ((long long)H * W > (long long)B200S_NOALLOC_MAX_PIXELS)
+        return noalloc_fail(err, err_cap, B200S_E_INVALID,
+                            "filter_speckles_noalloc: %dx%d = %lld pixels exceeds the static scratch (B200S_NOALLOC_MAX_PIXELS = %d); "
+                            "use b200s_postprocess / b200s_sgbm_compute, which allocate",
+                            W, H, (long long)H * W, (int)B200S_NOALLOC_MAX_PIXELS);
+    if (new_val < -32768 || new_val > 32767 || max_diff < 0)
+        return noalloc_fail(err, err_cap, B200S_E_INVALID, "filter_speckles_noalloc: new_val %d / max_diff %d out of range", new_val, max_diff);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return noalloc_fail(err, err_cap, B200S_E_CUDA, "cudaGetDevice failed: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return noalloc_fail(err, err_cap, B200S_E_INVALID, "filter_speckles_noalloc: device ordinal %d not supported", dev);
+    int* scratch = nullptr;
+    e = noalloc_scratch(dev, &scratch);
+    if (e != cudaSuccess) return noalloc_fail(err, err_cap, B200S_E_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const size_t n = (size_t)H * W;
+    if (d_dst != d_src) {
+        e = cudaMemcpyAsync(d_dst, d_src, n * sizeof(int16_t), cudaMemcpyDeviceToDevice, st);
+        if (e != cudaSuccess) return noalloc_fail(err, err_cap, B200S_E_CUDA, "device-to-device copy failed: %s", cudaGetErrorString(e));
+    }
+    launch_speckle(d_dst, 1, H, W, new_val, max_size, max_diff, scratch, scratch + B200S_NOALLOC_MAX_PIXELS, st, nullptr);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return noalloc_fail(err, err_cap, B200S_E_CUDA, "speckle kernels failed to launch: %s", cudaGetErrorString(e));
+    return B200S_OK;
+}

@@ -183,6 +183,25 @@ int b200s_pipeline_batch_submit(B200sHandle* h, const uint8_t* L, const uint8_t*
                                 float* disp, float* depth, int* ticket);
 int b200s_pipeline_batch_wait(B200sHandle* h, int ticket);
 
+/* ---- allocation-free variant ---------------------------------------------------------------- */
+
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * cv2.filterSpeckles(img16, new_val, max_size, max_diff) on ONE dense int16 H x W image in DEVICE memory, the same
+ * kernels as the speckle stage of b200s_sgbm_compute / b200s_postprocess, but the labels + sizes scratch lives in a
+ * file-scope static __device__ array (16 MiB, held by every GPU that loads the library until the process exits)
+ * instead of the handle's allocations. The call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine) and needs no handle: it enqueues on `cuda_stream` (a cudaStream_t, NULL = default stream) of the calling
+ * thread's CURRENT device, which must own d_src and d_dst; d_dst may equal d_src (in place). It does not synchronise.
+ * Limit: H * W <= B200S_NOALLOC_MAX_PIXELS (2 Mi pixels, e.g. 1920 x 1080); larger images are rejected with
+ * B200S_E_INVALID. All calls on a device share the scratch: calls whose kernels overlap on the GPU (different streams
+ * without ordering, or several threads) race on it; serialise them. The first call per device resolves the array's
+ * device address (cudaGetSymbolAddress); make that call outside a graph capture.
+ * On failure a message is written to err (caller buffer of err_cap bytes, may be NULL). */
+#define B200S_NOALLOC_MAX_PIXELS (1 << 21)
+int b200s_filter_speckles_noalloc(const int16_t* d_src, int16_t* d_dst, int H, int W, int new_val, int max_size,
+                                  int max_diff, void* cuda_stream, char* err, size_t err_cap);
+
 /* ---- introspection used by tests / bench -------------------------------------------------- */
 
 /* Cost-domain geometry for width W: W1 = columns with a full disparity range, minX1 = first of
