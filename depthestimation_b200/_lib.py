@@ -14,6 +14,7 @@ CSRC = _PKG / "csrc"
 MODES = {"sgbm": 0, "hh": 1, "sgbm_3way": 2, "hh4": 3}
 
 OK, E_INVALID, E_CUDA, E_STATE = 0, -1, -2, -3
+FLOW_VERT_DOWN, FLOW_VERT_UP, FLOW_PATH_VERTICAL, FLOW_ROWS_FUSED = 1, 2, 4, 8
 STAGES = ("remap", "prefilter", "cost", "paths", "wta", "median", "speckle", "post", "depth")
 
 
@@ -26,6 +27,12 @@ class B200sParams(C.Structure):
 class B200sPostParams(C.Structure):
     _fields_ = [("fastMode", C.c_int32), ("maxSpeckleSize", C.c_int32), ("maxDiff16", C.c_int32),
                 ("outlierThreshold", C.c_float), ("applyOutlierRemoval", C.c_int32)]
+
+
+class B200sFrameIO(C.Structure):
+    _fields_ = [("L", C.c_void_p), ("R", C.c_void_p), ("B", C.c_int32), ("srcH", C.c_int32), ("srcW", C.c_int32),
+                ("channels", C.c_int32), ("areaH", C.c_int32), ("areaW", C.c_int32), ("H", C.c_int32), ("W", C.c_int32),
+                ("use_maps", C.c_int32), ("disp", C.c_void_p), ("disp16", C.c_void_p), ("depth", C.c_void_p)]
 
 
 class B200sDepthParams(C.Structure):
@@ -62,6 +69,11 @@ SYMBOLS = {
     "b200s_pipeline_batch": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _PP, _DP, _VP, _VP]),
     "b200s_pipeline_batch_submit": (C.c_int, [_H, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _PP, _DP, _VP, _VP, _IP]),
     "b200s_pipeline_batch_wait": (C.c_int, [_H, C.c_int]),
+    "b200s_pipeline_frames_submit": (C.c_int, [_H, C.POINTER(B200sFrameIO), _PP, _DP, _IP]),
+    "b200s_pipeline_frames": (C.c_int, [_H, C.POINTER(B200sFrameIO), _PP, _DP]),
+    "b200s_last_flow": (C.c_int, [_H]),
+    "b200s_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    "b200s_host_free": (C.c_int, [C.c_void_p]),
     "b200s_filter_speckles_noalloc": (C.c_int, [_VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _VP,
                                                 C.c_char_p, C.c_size_t]),
     "b200s_stage_times": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.c_int]),

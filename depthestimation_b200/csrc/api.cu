@@ -51,6 +51,12 @@ struct B200sHandle {
     DevBuf maps;  // 4 x H x W float
     // scratch
     DevBuf imgL, imgR, rectL, rectR, recL, recR, C, S, Calt, raw, med, labels, sizes, f0, f1, s16c, hostio, ck, keys;
+    // input preparation of the frame pipeline (INTER_AREA / INTER_LINEAR results per side, gray images) and the
+    // per-axis tap tables of the two resizes, cached by (source size, target size)
+    DevBuf prepL[2], prepR[2], grayL, grayR, tabArea, tabLin;
+    int tabAreaKey[4] = {0, 0, 0, 0}, tabLinKey[4] = {0, 0, 0, 0};
+    size_t tabAreaOff[4] = {0, 0, 0, 0};
+    int last_flow = 0;        // B200S_FLOW_* bits of the last matcher call
     // asynchronous host-batch pipeline: four slots, copies on their own streams so that the H2D of chunk k+1 and
     // the D2H of chunk k-1 overlap the kernels of chunk k
     // (more than two slots let chunks k+1, k+2 be uploaded while chunk k-1 is still being downloaded: with two, a download
@@ -79,7 +85,8 @@ struct B200sHandle {
     }
     void release_all() {
         DevBuf* all[] = {&maps, &imgL, &imgR, &rectL, &rectR, &recL, &recR, &C, &S, &Calt, &raw, &med,
-                         &labels, &sizes, &f0, &f1, &s16c, &hostio, &ck, &keys};
+                         &labels, &sizes, &f0, &f1, &s16c, &hostio, &ck, &keys, &prepL[0], &prepL[1], &prepR[0], &prepR[1],
+                         &grayL, &grayR, &tabArea, &tabLin};
         for (DevBuf* b : all) b->release();
         for (Slot& sl : slot) { sl.inL.release(); sl.inR.release(); sl.out.release(); }
     }
@@ -279,12 +286,12 @@ static int check_launch(B200sHandle* h, const char* what) {
     return B200S_OK;
 }
 
-static int dev_remap(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int sH, int sW, uint8_t* oL, uint8_t* oR) {
+static int dev_remap(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int sH, int sW, int cn, uint8_t* oL, uint8_t* oR) {
     if (!h->maps.p) { h->set_error(B200S_E_STATE, "remap: rectification maps not set (call b200s_set_maps)"); return B200S_E_STATE; }
     size_t n = (size_t)h->mapH * h->mapW;
     const float* m = h->maps.as<float>();
-    launch_remap(dL, B, sH, sW, m, m + n, h->mapH, h->mapW, oL, h->stream);
-    launch_remap(dR, B, sH, sW, m + 2 * n, m + 3 * n, h->mapH, h->mapW, oR, h->stream);
+    launch_remap(dL, B, sH, sW, cn, m, m + n, h->mapH, h->mapW, oL, h->stream);
+    launch_remap(dR, B, sH, sW, cn, m + 2 * n, m + 3 * n, h->mapH, h->mapW, oR, h->stream);
     h->launches += 2;
     mark(h, B200S_STAGE_REMAP);
     return check_launch(h, "remap");
@@ -296,6 +303,7 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
     Eff e = make_eff(h->params, H, W);
     const size_t npx = (size_t)B * H * W;
     h->last_eff = e; h->last_B = B; h->have_last = true;
+    h->last_flow = 0;
     if (e.W1 <= 0) {  // no column has a full disparity range: everything invalid (A.0)
         CUDA_TRY(h, h->raw.ensure(npx * 2));
         // rare path: host-side fill
@@ -326,13 +334,14 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
     h->launches++;
     mark(h, B200S_STAGE_COST);
     if (h->debug_flow) {
-        rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches, 0);
+        rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches, 0, &h->last_flow);
         if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
         mark(h, B200S_STAGE_PATHS);
         launch_wta(e, B, h->S.as<uint16_t>(), h->raw.as<int16_t>(), h->stream);
         h->launches++;
     } else {
-        rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches, 1);
+        rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches, 1, &h->last_flow);
+        if (rc == -4) { h->set_error(B200S_E_CUDA, "vertical cluster kernel: planned but the launch failed on device %d (see stderr)", h->device); return B200S_E_CUDA; }
         if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
         mark(h, B200S_STAGE_PATHS);
         CUDA_TRY(h, h->ck.ensure(rows_ck_bytes(e, B)));
@@ -341,6 +350,7 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
                          h->raw.as<int16_t>(), h->stream);
         if (rc) { h->set_error(B200S_E_INVALID, "row kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
         h->launches++;
+        h->last_flow |= B200S_FLOW_ROWS_FUSED;
     }
     mark(h, B200S_STAGE_WTA);
     launch_median3_s16(h->raw.as<int16_t>(), dDisp, B, H, W, h->stream);
@@ -414,12 +424,24 @@ static int dev_post(B200sHandle* h, const float* dIn, int B, int H, int W, const
     return dev_post_impl(h, dIn, nullptr, B, H, W, pp, out, nullptr, nullptr, nullptr);
 }
 
-static int dev_pipeline(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B, int H, int W, int use_maps,
+// dL / dR: dense batches of H x W frames with cn interleaved channels (1 = gray, 3 = as stored, converted with the
+// BGR weights like cv2.cvtColor(COLOR_BGR2GRAY) at depthlib/rectify.py:116 / stereo_core.py:157-159)
+static int dev_pipeline(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int cn, int B, int H, int W, int use_maps,
                         const B200sPostParams& pp, const B200sDepthParams& dp, float* dDisp, float* dDepth,
                         const uint8_t** rectLout, const uint8_t** rectRout) {
     const size_t npx = (size_t)B * H * W;
     const uint8_t* mL = dL;
     const uint8_t* mR = dR;
+    if (cn == 3 && !use_maps) {      // no calibration: gray only (stereo_core.py:156-159)
+        CUDA_TRY(h, h->grayL.ensure(npx));
+        CUDA_TRY(h, h->grayR.ensure(npx));
+        launch_bgr2gray(dL, npx, h->grayL.as<uint8_t>(), h->stream);
+        launch_bgr2gray(dR, npx, h->grayR.as<uint8_t>(), h->stream);
+        h->launches += 2;
+        mark(h, B200S_STAGE_REMAP);
+        mL = h->grayL.as<uint8_t>();
+        mR = h->grayR.as<uint8_t>();
+    }
     if (use_maps) {
         if (h->mapH != H || h->mapW != W) {
             h->set_error(B200S_E_INVALID, "pipeline: image size %dx%d does not match the rectification maps %dx%d", W, H, h->mapW, h->mapH);
@@ -427,7 +449,7 @@ static int dev_pipeline(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, in
         }
         CUDA_TRY(h, h->rectL.ensure(npx));
         CUDA_TRY(h, h->rectR.ensure(npx));
-        int rc = dev_remap(h, dL, dR, B, H, W, h->rectL.as<uint8_t>(), h->rectR.as<uint8_t>());
+        int rc = dev_remap(h, dL, dR, B, H, W, cn, h->rectL.as<uint8_t>(), h->rectR.as<uint8_t>());
         if (rc) return rc;
         mL = h->rectL.as<uint8_t>();
         mR = h->rectR.as<uint8_t>();
@@ -536,7 +558,7 @@ int b200s_resize_area_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int
     CUDA_TRY(h, cudaMemcpy2DAsync(h->hostio.p, (size_t)cn * sW, src, stride, (size_t)cn * sW, sH, cudaMemcpyHostToDevice, h->stream));
     const int ix = sW / dW, iy = sH / dH;
     if (ix * dW == sW && iy * dH == sH) {
-        launch_resize_area_int(h->hostio.as<uint8_t>(), sW, cn, ix, iy, h->imgL.as<uint8_t>(), dH, dW, h->stream);
+        launch_resize_area_int(h->hostio.as<uint8_t>(), 1, sH, sW, cn, ix, iy, h->imgL.as<uint8_t>(), dH, dW, h->stream);
     } else {
         std::vector<int> xo, yo; std::vector<int2> xt, yt;
         area_table(sW, dW, xo, xt);
@@ -552,7 +574,7 @@ int b200s_resize_area_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, int
         CUDA_TRY(h, cudaMemcpyAsync(dxt, xt.data(), tx, cudaMemcpyHostToDevice, h->stream));
         CUDA_TRY(h, cudaMemcpyAsync(dyt, yt.data(), ty, cudaMemcpyHostToDevice, h->stream));
         CUDA_TRY(h, cudaStreamSynchronize(h->stream));     // the host vectors go out of scope below
-        launch_resize_area_tab(h->hostio.as<uint8_t>(), sW, cn, dxo, dxt, dyo, dyt, h->imgL.as<uint8_t>(), dH, dW, h->stream);
+        launch_resize_area_tab(h->hostio.as<uint8_t>(), 1, sH, sW, cn, dxo, dxt, dyo, dyt, h->imgL.as<uint8_t>(), dH, dW, h->stream);
     }
     h->launches++;
     CUDA_TRY(h, cudaMemcpyAsync(dst, h->imgL.p, nd, cudaMemcpyDeviceToHost, h->stream));
@@ -596,7 +618,7 @@ int b200s_resize_linear_u8(B200sHandle* h, const uint8_t* src, int sH, int sW, i
     CUDA_TRY(h, cudaMemcpyAsync(dtx, tx.data(), tx.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(h, cudaMemcpyAsync(dty, ty.data(), ty.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));     // the host vectors go out of scope below
-    launch_resize_linear(h->hostio.as<uint8_t>(), sH, sW, cn, dtx, dty, h->imgL.as<uint8_t>(), dH, dW, h->stream);
+    launch_resize_linear(h->hostio.as<uint8_t>(), 1, sH, sW, cn, dtx, dty, h->imgL.as<uint8_t>(), dH, dW, h->stream);
     h->launches++;
     CUDA_TRY(h, cudaMemcpyAsync(dst, h->imgL.p, nd, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->stream));
@@ -613,7 +635,7 @@ int b200s_remap_u8(B200sHandle* h, const uint8_t* L, const uint8_t* R, int srcH,
     size_t n = (size_t)h->mapH * h->mapW;
     CUDA_TRY(h, h->rectL.ensure(n));
     CUDA_TRY(h, h->rectR.ensure(n));
-    rc = dev_remap(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), 1, srcH, srcW, h->rectL.as<uint8_t>(), h->rectR.as<uint8_t>());
+    rc = dev_remap(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), 1, srcH, srcW, 1, h->rectL.as<uint8_t>(), h->rectR.as<uint8_t>());
     if (rc) return rc;
     CUDA_TRY(h, cudaMemcpyAsync(outL, h->rectL.p, n, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(h, cudaMemcpyAsync(outR, h->rectR.p, n, cudaMemcpyDeviceToHost, h->stream));
@@ -696,7 +718,8 @@ int b200s_disp_to_depth(B200sHandle* h, const float* disp, size_t n, const B200s
 int b200s_pipeline(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H, int W, size_t stride, int use_maps,
                    const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth, uint8_t* rectL, uint8_t* rectR) {
     if (!h) return B200S_E_INVALID;
-    if (!L || !R || !pp || !dp || !disp || H <= 0 || W <= 0 || stride < (size_t)W) { h->set_error(B200S_E_INVALID, "pipeline: bad arguments"); return B200S_E_INVALID; }
+    if (!L || !R || !pp || !dp || H <= 0 || W <= 0 || stride < (size_t)W) { h->set_error(B200S_E_INVALID, "pipeline: bad arguments"); return B200S_E_INVALID; }
+    if (!disp && !(dp->enabled && depth)) { h->set_error(B200S_E_INVALID, "pipeline: no output requested (disp is NULL and depth is NULL or disabled)"); return B200S_E_INVALID; }
     CUDA_TRY(h, cudaSetDevice(h->device));
     int rc = upload_u8(h, h->imgL, L, H, W, stride); if (rc) return rc;
     rc = upload_u8(h, h->imgR, R, H, W, stride); if (rc) return rc;
@@ -708,10 +731,10 @@ int b200s_pipeline(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H, in
     float* dDepth = dDisp + nc;
     const uint8_t *rl = nullptr, *rr = nullptr;
     Timed t(h);
-    rc = dev_pipeline(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), 1, H, W, use_maps, *pp, *dp, dDisp, dDepth, &rl, &rr);
+    rc = dev_pipeline(h, h->imgL.as<uint8_t>(), h->imgR.as<uint8_t>(), 1, 1, H, W, use_maps, *pp, *dp, dDisp, dDepth, &rl, &rr);
     if (rc) return rc;
     t.stop();
-    CUDA_TRY(h, cudaMemcpyAsync(disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (disp) CUDA_TRY(h, cudaMemcpyAsync(disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
     if (dp->enabled && depth) CUDA_TRY(h, cudaMemcpyAsync(depth, dDepth, nc * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
     if (rectL) CUDA_TRY(h, cudaMemcpyAsync(rectL, rl, (size_t)H * W, cudaMemcpyDeviceToHost, h->stream));
     if (rectR) CUDA_TRY(h, cudaMemcpyAsync(rectR, rr, (size_t)H * W, cudaMemcpyDeviceToHost, h->stream));
@@ -736,7 +759,7 @@ int b200s_pipeline_batch_dev(B200sHandle* h, const uint8_t* dL, const uint8_t* d
     if (!dL || !dR || !pp || !dp || !dDisp) { h->set_error(B200S_E_INVALID, "pipeline_batch_dev: bad arguments"); return B200S_E_INVALID; }
     CUDA_TRY(h, cudaSetDevice(h->device));
     Timed t(h);
-    int rc = dev_pipeline(h, dL, dR, B, H, W, use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
+    int rc = dev_pipeline(h, dL, dR, 1, B, H, W, use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
     if (rc) return rc;
     t.stop();
     return B200S_OK;
@@ -779,48 +802,163 @@ int b200s_reset_stage_times(B200sHandle* h) {
     return B200S_OK;
 }
 
-int b200s_pipeline_batch_submit(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W, int use_maps,
-                                const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth,
-                                int* ticket) {
+// ---- input preparation on the device ---------------------------------------------------------------
+}  // extern "C"
+
+// per-axis tables of the two resizes, built on the host once per (source, target) size and kept on the device
+static int prep_area_tables(B200sHandle* h, int sH, int sW, int dH, int dW) {
+    const int key[4] = {sH, sW, dH, dW};
+    if (!memcmp(key, h->tabAreaKey, sizeof(key))) return B200S_OK;
+    std::vector<int> xo, yo; std::vector<int2> xt, yt;
+    area_table(sW, dW, xo, xt);
+    area_table(sH, dH, yo, yt);
+    auto al = [](size_t v) { return (v + 15) & ~(size_t)15; };
+    const size_t bx = xo.size() * 4, by = yo.size() * 4, tx = xt.size() * 8, ty = yt.size() * 8;
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));              // an earlier call may still read the old tables
+    CUDA_TRY(h, h->tabArea.ensure(al(bx) + al(by) + al(tx) + al(ty)));
+    h->tabAreaOff[0] = 0; h->tabAreaOff[1] = al(bx); h->tabAreaOff[2] = al(bx) + al(by); h->tabAreaOff[3] = al(bx) + al(by) + al(tx);
+    char* base = h->tabArea.as<char>();
+    CUDA_TRY(h, cudaMemcpyAsync(base + h->tabAreaOff[0], xo.data(), bx, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(base + h->tabAreaOff[1], yo.data(), by, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(base + h->tabAreaOff[2], xt.data(), tx, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(base + h->tabAreaOff[3], yt.data(), ty, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));              // the host vectors go out of scope
+    memcpy(h->tabAreaKey, key, sizeof(key));
+    return B200S_OK;
+}
+static int prep_linear_tables(B200sHandle* h, int sH, int sW, int dH, int dW) {
+    const int key[4] = {sH, sW, dH, dW};
+    if (!memcmp(key, h->tabLinKey, sizeof(key))) return B200S_OK;
+    std::vector<int4> tx, ty;
+    linear_table(sW, dW, true, tx);
+    linear_table(sH, dH, false, ty);
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    CUDA_TRY(h, h->tabLin.ensure((tx.size() + ty.size()) * sizeof(int4)));
+    CUDA_TRY(h, cudaMemcpyAsync(h->tabLin.as<int4>(), tx.data(), tx.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(h->tabLin.as<int4>() + tx.size(), ty.data(), ty.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    memcpy(h->tabLinKey, key, sizeof(key));
+    return B200S_OK;
+}
+
+// One side of a batch: src (B x sH x sW x cn) -> [INTER_AREA to aH x aW] -> [INTER_LINEAR to H x W], channels kept
+// (gray conversion happens in the remap taps or in dev_pipeline). *out = the prepared frames (src itself if nothing ran).
+static int dev_prep_side(B200sHandle* h, const uint8_t* src, int B, int sH, int sW, int cn, int aH, int aW, int H, int W,
+                         DevBuf (&tmp)[2], const uint8_t** out) {
+    const uint8_t* cur = src;
+    int cH = sH, cW = sW;
+    if (aH != cH || aW != cW) {            // cv2.resize(img, (aW, aH), INTER_AREA): depthlib/input.py:39-43, threaded_stereo.py:41-46
+        CUDA_TRY(h, tmp[0].ensure((size_t)B * aH * aW * cn));
+        const int ix = cW / aW, iy = cH / aH;
+        if (ix * aW == cW && iy * aH == cH) {
+            launch_resize_area_int(cur, B, cH, cW, cn, ix, iy, tmp[0].as<uint8_t>(), aH, aW, h->stream);
+        } else {
+            int rc = prep_area_tables(h, cH, cW, aH, aW);
+            if (rc) return rc;
+            char* base = h->tabArea.as<char>();
+            launch_resize_area_tab(cur, B, cH, cW, cn, (const int*)(base + h->tabAreaOff[0]), (const int2*)(base + h->tabAreaOff[2]),
+                                   (const int*)(base + h->tabAreaOff[1]), (const int2*)(base + h->tabAreaOff[3]),
+                                   tmp[0].as<uint8_t>(), aH, aW, h->stream);
+        }
+        h->launches++;
+        cur = tmp[0].as<uint8_t>(); cH = aH; cW = aW;
+    }
+    if (H != cH || W != cW) {              // _ensure_image_size: cv2.resize(image, size, INTER_LINEAR), depthlib/rectify.py:92-105
+        int rc = prep_linear_tables(h, cH, cW, H, W);
+        if (rc) return rc;
+        CUDA_TRY(h, tmp[1].ensure((size_t)B * H * W * cn));
+        launch_resize_linear(cur, B, cH, cW, cn, h->tabLin.as<int4>(), h->tabLin.as<int4>() + W, tmp[1].as<uint8_t>(), H, W, h->stream);
+        h->launches++;
+        cur = tmp[1].as<uint8_t>();
+    }
+    *out = cur;
+    return B200S_OK;
+}
+
+static int frames_validate(B200sHandle* h, const B200sFrameIO* io, const B200sPostParams* pp, const B200sDepthParams* dp, int* aH, int* aW) {
+    if (!io || !pp || !dp || !io->L || !io->R || io->B <= 0 || io->srcH <= 0 || io->srcW <= 0 || io->H <= 0 || io->W <= 0 ||
+        (io->channels != 1 && io->channels != 3)) { h->set_error(B200S_E_INVALID, "pipeline_frames: bad arguments"); return B200S_E_INVALID; }
+    *aH = io->areaH > 0 ? io->areaH : io->srcH;
+    *aW = io->areaW > 0 ? io->areaW : io->srcW;
+    if (*aH > io->srcH || *aW > io->srcW) { h->set_error(B200S_E_INVALID, "pipeline_frames: INTER_AREA only shrinks (%dx%d -> %dx%d)", io->srcW, io->srcH, *aW, *aH); return B200S_E_INVALID; }
+    if (!io->disp && !io->disp16 && !(dp->enabled && io->depth)) { h->set_error(B200S_E_INVALID, "pipeline_frames: no output requested"); return B200S_E_INVALID; }
+    if (io->W - h->params.numDisparities <= 0) { h->set_error(B200S_E_INVALID, "pipeline_frames: numDisparities >= image width"); return B200S_E_INVALID; }
+    return B200S_OK;
+}
+
+extern "C" {
+
+int b200s_pipeline_frames_submit(B200sHandle* h, const B200sFrameIO* io, const B200sPostParams* pp, const B200sDepthParams* dp,
+                                 int* ticket) {
     if (!h) return B200S_E_INVALID;
-    if (!L || !R || !pp || !dp || !disp || !ticket || B <= 0 || H <= 0 || W <= 0) { h->set_error(B200S_E_INVALID, "pipeline_batch: bad arguments"); return B200S_E_INVALID; }
+    if (!ticket) { h->set_error(B200S_E_INVALID, "pipeline_frames: ticket is NULL"); return B200S_E_INVALID; }
+    int aH = 0, aW = 0;
+    int rc = frames_validate(h, io, pp, dp, &aH, &aW);
+    if (rc) return rc;
     CUDA_TRY(h, cudaSetDevice(h->device));
+    const int B = io->B, H = io->H, W = io->W, cn = io->channels;
     const int Wc = W - h->params.numDisparities;
-    if (Wc <= 0) { h->set_error(B200S_E_INVALID, "pipeline_batch: numDisparities >= image width"); return B200S_E_INVALID; }
-    const size_t npx = (size_t)B * H * W, nc = (size_t)B * H * Wc;
+    const size_t nin = (size_t)B * io->srcH * io->srcW * cn, nc = (size_t)B * H * Wc;
     const unsigned tk = h->next_ticket;
     B200sHandle::Slot& sl = h->slot[tk % B200sHandle::NSLOT];
-    if (sl.busy) { h->set_error(B200S_E_STATE, "pipeline_batch_submit: ticket %u of this slot has not been waited for", tk - B200sHandle::NSLOT); return B200S_E_STATE; }
+    if (sl.busy) { h->set_error(B200S_E_STATE, "pipeline submit: ticket %u of this slot has not been waited for", tk - B200sHandle::NSLOT); return B200S_E_STATE; }
+    // slot output: float disparity, float depth, int16 disparity
+    const size_t out_bytes = 2 * nc * sizeof(float) + nc * sizeof(int16_t);
     // growing a buffer frees device memory: nothing of this handle may still be running on it
-    if (npx > sl.inL.cap || npx > sl.inR.cap || 2 * nc * sizeof(float) > sl.out.cap) {
+    if (nin > sl.inL.cap || nin > sl.inR.cap || out_bytes > sl.out.cap) {
         CUDA_TRY(h, cudaStreamSynchronize(h->stream));
         CUDA_TRY(h, cudaStreamSynchronize(h->s_out));
-        CUDA_TRY(h, sl.inL.ensure(npx));
-        CUDA_TRY(h, sl.inR.ensure(npx));
-        CUDA_TRY(h, sl.out.ensure(2 * nc * sizeof(float)));
+        CUDA_TRY(h, sl.inL.ensure(nin));
+        CUDA_TRY(h, sl.inR.ensure(nin));
+        CUDA_TRY(h, sl.out.ensure(out_bytes));
     }
     // H2D on the copy-in stream (the slot's previous user has been waited for, so its kernels are done)
-    CUDA_TRY(h, cudaMemcpyAsync(sl.inL.p, L, npx, cudaMemcpyHostToDevice, h->s_in));
-    CUDA_TRY(h, cudaMemcpyAsync(sl.inR.p, R, npx, cudaMemcpyHostToDevice, h->s_in));
+    CUDA_TRY(h, cudaMemcpyAsync(sl.inL.p, io->L, nin, cudaMemcpyHostToDevice, h->s_in));
+    CUDA_TRY(h, cudaMemcpyAsync(sl.inR.p, io->R, nin, cudaMemcpyHostToDevice, h->s_in));
     CUDA_TRY(h, cudaEventRecord(sl.in_done, h->s_in));
     CUDA_TRY(h, cudaStreamWaitEvent(h->stream, sl.in_done, 0));
     float* dDisp = sl.out.as<float>();
     float* dDepth = dDisp + nc;
+    int16_t* dDisp16 = (int16_t*)(dDepth + nc);
     {
         Timed t(h);
-        int rc = dev_pipeline(h, sl.inL.as<uint8_t>(), sl.inR.as<uint8_t>(), B, H, W, use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
+        const uint8_t *pL = nullptr, *pR = nullptr;
+        rc = dev_prep_side(h, sl.inL.as<uint8_t>(), B, io->srcH, io->srcW, cn, aH, aW, H, W, h->prepL, &pL);
         if (rc) return rc;
+        rc = dev_prep_side(h, sl.inR.as<uint8_t>(), B, io->srcH, io->srcW, cn, aH, aW, H, W, h->prepR, &pR);
+        if (rc) return rc;
+        rc = dev_pipeline(h, pL, pR, cn, B, H, W, io->use_maps, *pp, *dp, dDisp, dDepth, nullptr, nullptr);
+        if (rc) return rc;
+        if (io->disp16) {   // every post stage selects among the matcher's x16 values (or 0): the float map is exactly s16 / 16
+            launch_f32_to_s16x16(dDisp, nc, dDisp16, h->stream);
+            h->launches++;
+            rc = check_launch(h, "disp16");
+            if (rc) return rc;
+        }
         t.stop();
     }
     CUDA_TRY(h, cudaEventRecord(sl.compute_done, h->stream));
     CUDA_TRY(h, cudaStreamWaitEvent(h->s_out, sl.compute_done, 0));
-    CUDA_TRY(h, cudaMemcpyAsync(disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
-    if (dp->enabled && depth) CUDA_TRY(h, cudaMemcpyAsync(depth, dDepth, nc * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
+    // one plain copy per requested plane; planes nobody asked for stay on the device
+    if (io->disp) CUDA_TRY(h, cudaMemcpyAsync(io->disp, dDisp, nc * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
+    if (io->disp16) CUDA_TRY(h, cudaMemcpyAsync(io->disp16, dDisp16, nc * sizeof(int16_t), cudaMemcpyDeviceToHost, h->s_out));
+    if (dp->enabled && io->depth) CUDA_TRY(h, cudaMemcpyAsync(io->depth, dDepth, nc * sizeof(float), cudaMemcpyDeviceToHost, h->s_out));
     CUDA_TRY(h, cudaEventRecord(sl.out_done, h->s_out));
     sl.busy = true;
     *ticket = (int)tk;
     h->next_ticket = tk + 1;
     return B200S_OK;
+}
+
+int b200s_pipeline_batch_submit(B200sHandle* h, const uint8_t* L, const uint8_t* R, int B, int H, int W, int use_maps,
+                                const B200sPostParams* pp, const B200sDepthParams* dp, float* disp, float* depth,
+                                int* ticket) {
+    if (!h) return B200S_E_INVALID;
+    B200sFrameIO io;
+    memset(&io, 0, sizeof(io));
+    io.L = L; io.R = R; io.B = B; io.srcH = H; io.srcW = W; io.channels = 1; io.H = H; io.W = W; io.use_maps = use_maps;
+    io.disp = disp; io.depth = depth;
+    return b200s_pipeline_frames_submit(h, &io, pp, dp, ticket);
 }
 
 int b200s_pipeline_batch_wait(B200sHandle* h, int ticket) {
@@ -829,8 +967,8 @@ int b200s_pipeline_batch_wait(B200sHandle* h, int ticket) {
     const unsigned tk = (unsigned)ticket;
     if (!sl.busy || tk >= h->next_ticket || h->next_ticket - tk > B200sHandle::NSLOT) { h->set_error(B200S_E_STATE, "pipeline_batch_wait: ticket %d is not in flight", ticket); return B200S_E_STATE; }
     CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, cudaEventSynchronize(sl.out_done));   // on failure the slot stays busy: its copies may still be pending
     sl.busy = false;
-    CUDA_TRY(h, cudaEventSynchronize(sl.out_done));
     return check_launch(h, "pipeline_batch");
 }
 
@@ -840,6 +978,27 @@ int b200s_pipeline_batch(B200sHandle* h, const uint8_t* L, const uint8_t* R, int
     int rc = b200s_pipeline_batch_submit(h, L, R, B, H, W, use_maps, pp, dp, disp, depth, &ticket);
     if (rc) return rc;
     return b200s_pipeline_batch_wait(h, ticket);
+}
+
+int b200s_pipeline_frames(B200sHandle* h, const B200sFrameIO* io, const B200sPostParams* pp, const B200sDepthParams* dp) {
+    int ticket = 0;
+    int rc = b200s_pipeline_frames_submit(h, io, pp, dp, &ticket);
+    if (rc) return rc;
+    return b200s_pipeline_batch_wait(h, ticket);
+}
+
+int b200s_last_flow(const B200sHandle* h) { return h ? h->last_flow : 0; }
+
+int b200s_host_alloc(size_t bytes, void** out) {
+    if (!out || bytes == 0) return B200S_E_INVALID;
+    *out = nullptr;
+    if (cudaHostAlloc(out, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); *out = nullptr; return B200S_E_CUDA; }
+    return B200S_OK;
+}
+int b200s_host_free(void* p) {
+    if (!p) return B200S_OK;
+    if (cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return B200S_E_CUDA; }
+    return B200S_OK;
 }
 
 }  // extern "C"

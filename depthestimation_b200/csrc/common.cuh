@@ -102,8 +102,8 @@ int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uin
                 uint16_t* Calt, cudaStream_t st);
 // all path directions of the mode, accumulated into S
 int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, const uint16_t* Calt, uint16_t* S,
-                 cudaStream_t st, long long* launches, int vertical_only);
-// fused vertical family (vert.cu): 0 = launched, 1 = configuration does not fit (use launch_paths)
+                 cudaStream_t st, long long* launches, int vertical_only, int* flow);
+// fused vertical family (vert.cu): 0 = launched, 1 = configuration does not fit (use launch_paths), -1 = launch error
 int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, int accumulate, cudaStream_t st,
                        int* clusters_out);
 // fused horizontal paths + winner selection (rows.cu): C', Sv -> raw disparity
@@ -116,7 +116,8 @@ void launch_median3_s16(const int16_t* src, int16_t* dst, int B, int H, int W, c
 // speckle filter (B.3) in place; labels/sizes are int32 scratch of B*H*W each
 void launch_speckle(int16_t* img, int B, int H, int W, int newVal, int maxSize, int maxDiff, int* labels, int* sizes,
                     cudaStream_t st, long long* launches);
-void launch_remap(const uint8_t* src, int B, int sH, int sW, const float* m1, const float* m2, int H, int W,
+// cn = 3: interleaved 3-channel source, gray conversion (B.2) fused into the taps
+void launch_remap(const uint8_t* src, int B, int sH, int sW, int cn, const float* m1, const float* m2, int H, int W,
                   uint8_t* dst, cudaStream_t st);
 void launch_bgr2gray(const uint8_t* img, size_t npix, uint8_t* dst, cudaStream_t st);
 void launch_disp16_to_f32_crop(const int16_t* d16, int B, int H, int W, int x0, float* out, cudaStream_t st);
@@ -127,12 +128,14 @@ void launch_outliers_s16(const int16_t* d16, float* out, int B, int H, int W, fl
 void launch_crop_s16(const int16_t* d16, int B, int H, int W, int x0, int16_t* out, cudaStream_t st);
 void launch_median3_f32_depth(const float* src, float* dst, int B, int H, int W, const B200sDepthParams& dp, float* Z, cudaStream_t st);
 void launch_median3_f32(const float* src, float* dst, int B, int H, int W, cudaStream_t st);
-void launch_resize_linear(const uint8_t* src, int sH, int sW, int cn, const int4* tx, const int4* ty, uint8_t* dst, int dH, int dW,
-                          cudaStream_t st);
+void launch_resize_linear(const uint8_t* src, int B, int sH, int sW, int cn, const int4* tx, const int4* ty, uint8_t* dst, int dH,
+                          int dW, cudaStream_t st);
 // k masked dilations (ping-pong a <-> b, result in b when k is odd, else a); returns the launch count or -1
 int launch_fill_nearest(float* a, float* b, const uint8_t* mask, int H, int W, int k, cudaStream_t st);
 void launch_depth(const float* disp, size_t n, const B200sDepthParams& dp, float* Z, cudaStream_t st);
-void launch_resize_area_int(const uint8_t* src, int sW, int cn, int ix, int iy, uint8_t* dst, int dH, int dW, cudaStream_t st);
-void launch_resize_area_tab(const uint8_t* src, int sW, int cn, const int* xo, const int2* xt, const int* yo, const int2* yt,
-                            uint8_t* dst, int dH, int dW, cudaStream_t st);
+// dense batches of B frames (blockIdx.y = frame)
+void launch_resize_area_int(const uint8_t* src, int B, int sH, int sW, int cn, int ix, int iy, uint8_t* dst, int dH, int dW,
+                            cudaStream_t st);
+void launch_resize_area_tab(const uint8_t* src, int B, int sH, int sW, int cn, const int* xo, const int2* xt, const int* yo,
+                            const int2* yt, uint8_t* dst, int dH, int dW, cudaStream_t st);
 void launch_debug_volume(const uint16_t* V, int H, int W1, int Dp, int D, int add, int16_t* out, cudaStream_t st);

@@ -15,11 +15,21 @@
 // Every O(N) kernel below gives a thread several pixels (or a CTA several rows): with one pixel per thread a batch is
 // ~140 000 tiny CTAs per launch and the launch rate of CTAs (~0.7 per clock), not memory, sets the time (~95 us).
 #define REMAP_PPT 4
+// CN = 3: the source is the interleaved 3-channel frame and every tap is converted to gray on the fly (B.2), which
+// is what remap of the cvtColor result reads at that tap (depthlib/rectify.py:182-186) without the gray image ever
+// going to memory.
+template <int CN>
+__device__ __forceinline__ int remap_tap(const uint8_t* r, int x) {
+    if (CN == 1) return r[x];
+    const uint8_t* p = r + 3 * (size_t)x;
+    return (3735 * p[0] + 19235 * p[1] + 9798 * p[2] + 16384) >> 15;
+}
+template <int CN>
 __global__ void __launch_bounds__(256) k_remap(const uint8_t* __restrict__ src, int sH, int sW,
                                                const float* __restrict__ m1, const float* __restrict__ m2, int H, int W,
                                                uint8_t* __restrict__ dst) {
     const size_t n = (size_t)H * W;
-    const uint8_t* s = src + (size_t)blockIdx.y * sH * sW;
+    const uint8_t* s = src + (size_t)blockIdx.y * sH * sW * CN;
 #pragma unroll
     for (int k = 0; k < REMAP_PPT; k++) {
         const size_t i = ((size_t)blockIdx.x * REMAP_PPT + k) * 256 + threadIdx.x;
@@ -30,24 +40,25 @@ __global__ void __launch_bounds__(256) k_remap(const uint8_t* __restrict__ src, 
         int p00 = 0, p01 = 0, p10 = 0, p11 = 0;
         const bool x0 = (ix >= 0 && ix < sW), x1 = (ix + 1 >= 0 && ix + 1 < sW);
         if (iy >= 0 && iy < sH) {
-            const uint8_t* r = s + (size_t)iy * sW;
-            if (x0) p00 = r[ix];
-            if (x1) p01 = r[ix + 1];
+            const uint8_t* r = s + (size_t)iy * sW * CN;
+            if (x0) p00 = remap_tap<CN>(r, ix);
+            if (x1) p01 = remap_tap<CN>(r, ix + 1);
         }
         if (iy + 1 >= 0 && iy + 1 < sH) {
-            const uint8_t* r = s + (size_t)(iy + 1) * sW;
-            if (x0) p10 = r[ix];
-            if (x1) p11 = r[ix + 1];
+            const uint8_t* r = s + (size_t)(iy + 1) * sW * CN;
+            if (x0) p10 = remap_tap<CN>(r, ix);
+            if (x1) p11 = remap_tap<CN>(r, ix + 1);
         }
         int acc = (32 - fy) * ((32 - fx) * p00 + fx * p01) + fy * ((32 - fx) * p10 + fx * p11);
         dst[(size_t)blockIdx.y * n + i] = (uint8_t)((acc * 32 + 16384) >> 15);
     }
 }
 
-void launch_remap(const uint8_t* src, int B, int sH, int sW, const float* m1, const float* m2, int H, int W,
+void launch_remap(const uint8_t* src, int B, int sH, int sW, int cn, const float* m1, const float* m2, int H, int W,
                   uint8_t* dst, cudaStream_t st) {
     dim3 grid((unsigned)(((size_t)H * W + 256 * REMAP_PPT - 1) / (256 * REMAP_PPT)), B);
-    k_remap<<<grid, 256, 0, st>>>(src, sH, sW, m1, m2, H, W, dst);
+    if (cn == 3) k_remap<3><<<grid, 256, 0, st>>>(src, sH, sW, m1, m2, H, W, dst);
+    else k_remap<1><<<grid, 256, 0, st>>>(src, sH, sW, m1, m2, H, W, dst);
 }
 
 // ---- B.2 gray ------------------------------------------------------------------------------------
@@ -275,9 +286,11 @@ void launch_debug_volume(const uint16_t* V, int H, int W1, int Dp, int D, int ad
 // tables built on the host (double precision, as the reference's dependency does): row value = sum_x S * alpha in
 // float32 in table order, pixel = sum_y beta * row value, rint, clamp. No FMA anywhere (--fmad=false + explicit _rn).
 __global__ void __launch_bounds__(256) k_resize_area_int(const uint8_t* __restrict__ src, int sW, int cn, int ix, int iy,
-                                                         float scale, uint8_t* __restrict__ dst, int dH, int dW) {
+                                                         float scale, uint8_t* __restrict__ dst, int dH, int dW, size_t sframe) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t)dH * dW * cn) return;
+    src += (size_t)blockIdx.y * sframe;                      // blockIdx.y = frame of a dense batch
+    dst += (size_t)blockIdx.y * dH * dW * cn;
     const int c = (int)(i % cn), x = (int)((i / cn) % dW), y = (int)(i / ((size_t)cn * dW));
     int sum = 0;
     for (int j = 0; j < iy; j++) {
@@ -290,9 +303,11 @@ __global__ void __launch_bounds__(256) k_resize_area_int(const uint8_t* __restri
 __global__ void __launch_bounds__(256) k_resize_area_tab(const uint8_t* __restrict__ src, int sW, int cn,
                                                          const int* __restrict__ xo, const int2* __restrict__ xt,
                                                          const int* __restrict__ yo, const int2* __restrict__ yt,
-                                                         uint8_t* __restrict__ dst, int dH, int dW) {
+                                                         uint8_t* __restrict__ dst, int dH, int dW, size_t sframe) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t)dH * dW * cn) return;
+    src += (size_t)blockIdx.y * sframe;
+    dst += (size_t)blockIdx.y * dH * dW * cn;
     const int c = (int)(i % cn), x = (int)((i / cn) % dW), y = (int)(i / ((size_t)cn * dW));
     const int x0 = xo[x], x1 = xo[x + 1], y0 = yo[y], y1 = yo[y + 1];
     float sum = 0.f;
@@ -309,14 +324,17 @@ __global__ void __launch_bounds__(256) k_resize_area_tab(const uint8_t* __restri
     }
     dst[i] = (uint8_t)min(max(__float2int_rn(sum), 0), 255);
 }
-void launch_resize_area_int(const uint8_t* src, int sW, int cn, int ix, int iy, uint8_t* dst, int dH, int dW, cudaStream_t st) {
+void launch_resize_area_int(const uint8_t* src, int B, int sH, int sW, int cn, int ix, int iy, uint8_t* dst, int dH, int dW,
+                            cudaStream_t st) {
     const size_t n = (size_t)dH * dW * cn;
-    k_resize_area_int<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, sW, cn, ix, iy, (float)(1.0 / (ix * iy)), dst, dH, dW);
+    dim3 grid((unsigned)((n + 255) / 256), B);
+    k_resize_area_int<<<grid, 256, 0, st>>>(src, sW, cn, ix, iy, (float)(1.0 / (ix * iy)), dst, dH, dW, (size_t)sH * sW * cn);
 }
-void launch_resize_area_tab(const uint8_t* src, int sW, int cn, const int* xo, const int2* xt, const int* yo, const int2* yt,
-                            uint8_t* dst, int dH, int dW, cudaStream_t st) {
+void launch_resize_area_tab(const uint8_t* src, int B, int sH, int sW, int cn, const int* xo, const int2* xt, const int* yo,
+                            const int2* yt, uint8_t* dst, int dH, int dW, cudaStream_t st) {
     const size_t n = (size_t)dH * dW * cn;
-    k_resize_area_tab<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, sW, cn, xo, xt, yo, yt, dst, dH, dW);
+    dim3 grid((unsigned)((n + 255) / 256), B);
+    k_resize_area_tab<<<grid, 256, 0, st>>>(src, sW, cn, xo, xt, yo, yt, dst, dH, dW, (size_t)sH * sW * cn);
 }
 
 // ---- fill_holes(method='nearest'): one dilation by the k x k ellipse, applied under the hole mask -----------------------
@@ -373,6 +391,8 @@ __global__ void __launch_bounds__(256) k_resize_linear(const uint8_t* __restrict
                                                        const int4* __restrict__ tx, const int4* __restrict__ ty,
                                                        uint8_t* __restrict__ dst, int dH, int dW) {
     const size_t n = (size_t)dH * dW * cn;
+    src += (size_t)blockIdx.y * sH * sW * cn;                // blockIdx.y = frame of a dense batch
+    dst += (size_t)blockIdx.y * n;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const size_t i = ((size_t)blockIdx.x * 4 + k) * 256 + threadIdx.x;
@@ -389,8 +409,9 @@ __global__ void __launch_bounds__(256) k_resize_linear(const uint8_t* __restrict
         dst[i] = (uint8_t)min(max(v, 0), 255);
     }
 }
-void launch_resize_linear(const uint8_t* src, int sH, int sW, int cn, const int4* tx, const int4* ty, uint8_t* dst, int dH, int dW,
-                          cudaStream_t st) {
+void launch_resize_linear(const uint8_t* src, int B, int sH, int sW, int cn, const int4* tx, const int4* ty, uint8_t* dst, int dH,
+                          int dW, cudaStream_t st) {
     const size_t n = (size_t)dH * dW * cn;
-    k_resize_linear<<<(unsigned)((n + 1023) / 1024), 256, 0, st>>>(src, sH, sW, cn, tx, ty, dst, dH, dW);
+    dim3 grid((unsigned)((n + 1023) / 1024), B);
+    k_resize_linear<<<grid, 256, 0, st>>>(src, sH, sW, cn, tx, ty, dst, dH, dW);
 }

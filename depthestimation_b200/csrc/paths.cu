@@ -164,7 +164,7 @@ static void launch_one(const PathArgs& a, int B, cudaStream_t st) {
 }
 
 int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, const uint16_t* Calt, uint16_t* S,
-                 cudaStream_t st, long long* launches, int vertical_only) {
+                 cudaStream_t st, long long* launches, int vertical_only, int* flow) {
     if (e.Dp > 256) return -2;
     PathArgs a;
     a.C = C; a.Calt = nullptr; a.S = S;
@@ -190,12 +190,20 @@ int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, c
     // (vert.cu) when the strip state fits in shared memory; otherwise one generic launch per direction
     bool fused_down = false, fused_up = false;
     if (vertical_only && (e.mode == B200S_MODE_SGBM || e.mode == B200S_MODE_HH)) {
-        if (launch_vert_family(e, B, C, S, +1, 0, st, nullptr) == 0) {
+        int rv = launch_vert_family(e, B, C, S, +1, 0, st, nullptr);
+        if (rv < 0) return -4;                         // the cluster kernel was planned but its launch failed
+        if (rv == 0) {
             fused_down = true; first = false;
             if (launches) (*launches)++;
-            if (e.mode == B200S_MODE_HH && launch_vert_family(e, B, C, S, -1, 1, st, nullptr) == 0) {
-                fused_up = true;
-                if (launches) (*launches)++;
+            if (flow) *flow |= B200S_FLOW_VERT_DOWN;
+            if (e.mode == B200S_MODE_HH) {
+                rv = launch_vert_family(e, B, C, S, -1, 1, st, nullptr);
+                if (rv < 0) return -4;
+                if (rv == 0) {
+                    fused_up = true;
+                    if (launches) (*launches)++;
+                    if (flow) *flow |= B200S_FLOW_VERT_UP;
+                }
             }
         }
     }
@@ -218,6 +226,7 @@ int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, c
         }
         launch_one(a, B, st);
         if (launches) (*launches)++;
+        if (flow && a.py != 0) *flow |= B200S_FLOW_PATH_VERTICAL;
     }
     return 0;
 }

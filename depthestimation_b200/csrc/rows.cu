@@ -501,8 +501,9 @@ static size_t rows_smem() {   // L / S records + C of the chunk
 
 template <int LW, int NR, bool PAD, bool W3, bool NS>
 static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t st) {
-    static int sms = 0;
-    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    int sms = 0, dev = 0;   // per call: the current device is the handle's, and a process may drive several
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaFuncSetAttribute(k_rows<LW, NR, PAD, W3, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     // a single frame (or a few small ones) leaves most SMs without a CTA at 128 threads: spread the lines one warp per CTA
     if (grid < 2 * sms) {

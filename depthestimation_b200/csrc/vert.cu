@@ -20,6 +20,7 @@
 #include <cooperative_groups.h>
 #include <stdlib.h>
 
+#include <mutex>
 #include <type_traits>
 
 #include "sgm_step.cuh"
@@ -43,6 +44,7 @@ struct VertArgs {
 #define VERT_THREADS_WIDE 512
 #define VERT_THREADS_NARROW 288
 #define VERT_KMAX 4
+#define VERT_MAX_DEVICES 64
 #ifndef VERT_UREG
 #define VERT_UREG 1   // 1: keep the vertical path's L in registers instead of shared memory
 #endif
@@ -310,8 +312,11 @@ template <int LW, int NR, int VT>
 static bool plan_vert(const Eff& e, VertPlan& best) {
     using VL = VertLayout<LW, NR, VT>;
     constexpr int G = VL::G;
-    static bool configured = false;
-    if (!configured) {
+    // function attributes are per DEVICE: opt every device in once (a process may drive several GPUs from several threads)
+    static bool configured[VERT_MAX_DEVICES] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= VERT_MAX_DEVICES) { cudaGetLastError(); return false; }
+    if (!configured[dev]) {
         auto cfgk = [](auto kern) {
             if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) { cudaGetLastError(); return false; }
             if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return false; }
@@ -319,7 +324,7 @@ static bool plan_vert(const Eff& e, VertPlan& best) {
         };
         if (!cfgk(k_vert<LW, NR, true, VT, false>) || !cfgk(k_vert<LW, NR, false, VT, false>) ||
             !cfgk(k_vert<LW, NR, true, VT, true>) || !cfgk(k_vert<LW, NR, false, VT, true>)) return false;
-        configured = true;
+        configured[dev] = true;
     }
     static int cs_env = -1;
     if (cs_env < 0) { const char* v = getenv("B200S_VERT_CS"); cs_env = v ? atoi(v) : 0; }
@@ -359,20 +364,33 @@ static cudaError_t launch_vert_vt(const VertPlan& pl, const VertArgs& a, int B, 
 template <int LW, int NR>
 static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, int accumulate, cudaStream_t st,
                          int* clusters_out) {
-    // the plan depends on (W1, Dp) only; cache the last one
-    static VertPlan cached; static int cW1 = -1, cDp = -1; static bool cok = false;
-    if (cW1 != e.W1 || cDp != e.Dp) {
-        static int vt_env = -1;
-        if (vt_env < 0) { const char* v = getenv("B200S_VERT_VT"); vt_env = v ? atoi(v) : 0; }
-        VertPlan wide, narrow;
-        const bool okw = (vt_env == 0 || vt_env == VERT_THREADS_WIDE) && plan_vert<LW, NR, VERT_THREADS_WIDE>(e, wide);
-        const bool okn = (vt_env == 0 || vt_env == VERT_THREADS_NARROW) && plan_vert<LW, NR, VERT_THREADS_NARROW>(e, narrow);
-        cok = okw || okn;
-        if (cok) cached = (okn && (!okw || narrow.score > wide.score)) ? narrow : wide;
-        cW1 = e.W1; cDp = e.Dp;
-        if (getenv("B200S_VERBOSE") && cok)
-            fprintf(stderr, "[b200s] k_vert<%d,%d>: W1=%d Dp=%d -> %d threads, cluster %d x %d cols (%d per thread group), %zu B smem%s, %d clusters co-resident\n",
-                    LW, NR, e.W1, e.Dp, cached.threads, cached.CS, cached.NC, cached.KIT, cached.smem, cached.clamp ? " (clamped records)" : "", cached.clusters);
+    // the plan depends on (device, W1, Dp) only; the last one per device is cached. Several host threads (one handle per
+    // thread, possibly on different GPUs) come through here: the cache is guarded and used through a local copy.
+    struct Cache { VertPlan plan; int W1 = -1, Dp = -1; bool ok = false; };
+    static Cache cache[VERT_MAX_DEVICES];
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= VERT_MAX_DEVICES) { cudaGetLastError(); return 1; }
+    VertPlan cached;
+    bool cok;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        Cache& c = cache[dev];
+        if (c.W1 != e.W1 || c.Dp != e.Dp) {
+            static int vt_env = -1;
+            if (vt_env < 0) { const char* v = getenv("B200S_VERT_VT"); vt_env = v ? atoi(v) : 0; }
+            VertPlan wide, narrow;
+            const bool okw = (vt_env == 0 || vt_env == VERT_THREADS_WIDE) && plan_vert<LW, NR, VERT_THREADS_WIDE>(e, wide);
+            const bool okn = (vt_env == 0 || vt_env == VERT_THREADS_NARROW) && plan_vert<LW, NR, VERT_THREADS_NARROW>(e, narrow);
+            c.ok = okw || okn;
+            if (c.ok) c.plan = (okn && (!okw || narrow.score > wide.score)) ? narrow : wide;
+            c.W1 = e.W1; c.Dp = e.Dp;
+            if (getenv("B200S_VERBOSE") && c.ok)
+                fprintf(stderr, "[b200s] dev %d k_vert<%d,%d>: W1=%d Dp=%d -> %d threads, cluster %d x %d cols (%d per thread group), %zu B smem%s, %d clusters co-resident\n",
+                        dev, LW, NR, e.W1, e.Dp, c.plan.threads, c.plan.CS, c.plan.NC, c.plan.KIT, c.plan.smem, c.plan.clamp ? " (clamped records)" : "", c.plan.clusters);
+        }
+        cached = c.plan;
+        cok = c.ok;
     }
     if (!cok) return 1;                                            // does not fit: caller falls back to k_path
     if (clusters_out) *clusters_out = cached.clusters;
@@ -384,11 +402,16 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     const bool pad = e.D != LW * 2 * NR;
     cudaError_t le = (cached.threads == VERT_THREADS_WIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_WIDE>(cached, a, B, pad, st)
                                                            : launch_vert_vt<LW, NR, VERT_THREADS_NARROW>(cached, a, B, pad, st);
-    if (le != cudaSuccess) { cudaGetLastError(); return 1; }
+    if (le != cudaSuccess) {   // the planner said it fits: a failed launch is an error, not a reason to fall back silently
+        fprintf(stderr, "[b200s] k_vert launch failed on device %d: %s\n", dev, cudaGetErrorString(le));
+        cudaGetLastError();
+        return -1;
+    }
     return 0;
 }
 
-// returns 0 when launched, 1 when the configuration does not fit this kernel (use the generic kernel).
+// returns 0 when launched, 1 when the configuration does not fit this kernel (use the generic kernel), -1 when the
+// launch itself failed (a CUDA error the caller must report).
 // B == 0 only plans; *clusters_out = frames this kernel processes concurrently (preferred batch granule).
 int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, int accumulate, cudaStream_t st,
                        int* clusters_out) {

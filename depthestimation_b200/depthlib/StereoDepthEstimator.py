@@ -20,7 +20,7 @@ class StereoDepthEstimator:
         self.right_source = None
         if left_source is not None and right_source is not None:
             self.left_source, self.right_source = load_stereo_pair(left_source, right_source,
-                                                                   downscale_factor=downscale_factor)
+                                                                   downscale_factor=downscale_factor, device=device)
         self.sgbm = None
         self.disparity_map = None
         self.depth_map = None

@@ -5,27 +5,93 @@ a generator that yields one depth map per stereo frame, with threaded capture, `
 * the HighGUI window / waitKey calls of the reference (:81-82, :111, :138) are left out — display is
   "unavailable on this box"; ``visualize_live=True`` raises when the first frame would be drawn
 * ``devices=[...]`` (new, optional) shards chunks of frames across several B200s through
-  ``sharding.ThreadedSharder`` and still yields in frame order
+  ``sharding.ThreadedSharder`` and still yields in frame order. Each GPU worker feeds the frames AS CAPTURED
+  (3-channel, full resolution) to ``b200s_pipeline_frames_submit``: INTER_AREA downscale, size fix-up, gray conversion,
+  remap, matcher, post-filters and depth all run on that worker's device, up to three chunks in flight per GPU, page-
+  locked chunk buffers, and only the depth plane (what this generator yields, :103,:130) comes back over PCIe.
 """
 from __future__ import annotations
 
 import time
+import warnings
+from concurrent.futures import ThreadPoolExecutor
 from typing import Optional, Sequence
 
 import numpy as np
 
 from ..sharding import ThreadedSharder
 from .input import stereo_stream
-from .rectify import _ensure_image_size
 from .stereo_core import StereoCore
 from .threaded_stereo import ThreadedStereoCapture
 from .visualizations import visualize_depth_live, visualize_depth_live_gray
 
 
+class _FrameWorker:
+    """One GPU of the sharded generator: engine + maps + a ring of page-locked chunk buffers (sharding.ThreadedSharder's
+    submit / wait protocol)."""
+    max_inflight = 3
+
+    def __init__(self, device, matcher_kw, maps, pp, dp, use_maps, size, area, copy_threads=4):
+        from ..engine import StereoEngine
+        self.eng = StereoEngine(device, **matcher_kw)
+        if maps is not None:
+            self.eng.set_maps(maps['map1_L'], maps['map2_L'], maps['map1_R'], maps['map2_R'])
+        self.pp, self.dp, self.use_maps, self.size, self.area = pp, dp, use_maps, size, area
+        self.want_depth = bool(dp.enabled)
+        self._free = []          # page-locked (L, R, out) triples of the current chunk geometry
+        self._geom = None
+        self._pool = ThreadPoolExecutor(max(1, int(copy_threads)))
+
+    def _buffers(self, B, shape):
+        from ..engine import pinned_empty
+        geom = (B, tuple(shape))
+        if self._geom is None or B > self._geom[0] or tuple(shape) != self._geom[1]:
+            self._free, self._geom = [], geom          # buffers in flight stay alive through their tokens
+        if not self._free:
+            cap = self._geom[0]
+            aW, aH = self.area if self.area is not None else (shape[1], shape[0])
+            W, H = self.size if self.size is not None else (aW, aH)
+            Wc = W - self.eng.params.numDisparities
+            out = pinned_empty((cap, H, Wc), np.float32)
+            return pinned_empty((cap,) + tuple(shape), np.uint8), pinned_empty((cap,) + tuple(shape), np.uint8), out
+        return self._free.pop()
+
+    def submit(self, Ls, Rs):
+        B, shape = len(Ls), Ls[0].shape
+        if any(f.shape != shape or f.dtype != np.uint8 for f in Ls) or any(f.shape != shape or f.dtype != np.uint8 for f in Rs):
+            raise ValueError("sharded video path: every frame of a stream must be uint8 and of one size")
+        bufs = self._buffers(B, shape)
+        bL, bR, out = bufs
+
+        def put(k):
+            np.copyto(bL[k], Ls[k]); np.copyto(bR[k], Rs[k])
+        list(self._pool.map(put, range(B)))            # numpy releases the GIL while copying
+        want_depth = self.want_depth
+        tk = self.eng.pipeline_frames_submit(
+            bL[:B], bR[:B], self.pp, self.dp, size=self.size, area=self.area, use_maps=self.use_maps,
+            want_disp=not want_depth, want_depth=want_depth,
+            out_disp=None if want_depth else out[:B], out_depth=out[:B] if want_depth else None)
+        return tk, bufs, B, self._geom
+
+    def wait(self, token):
+        tk, bufs, B, geom = token
+        self.eng.pipeline_batch_wait(tk)
+        src = bufs[2]
+        res = np.empty((B,) + src.shape[1:], np.float32)      # the caller owns what the generator yields
+
+        def get(k):
+            np.copyto(res[k], src[k])
+        list(self._pool.map(get, range(B)))
+        if geom == self._geom:
+            self._free.append(bufs)
+        return (None, res) if self.want_depth else (res, None)
+
+
 class StereoDepthEstimatorVideo:
     def __init__(self, left_source=None, right_source=None, downscale_factor=1.0, visualize_live=False,
                  saving_path=None, fast_mode=False, use_threading=True, target_fps=30, drop_frames=False,
-                 visualize_gray=False, devices: Optional[Sequence[int]] = None, chunk: int = 8) -> None:
+                 visualize_gray=False, devices: Optional[Sequence[int]] = None, chunk: Optional[int] = None,
+                 max_chunk: int = 256) -> None:
         self.left_source, self.right_source = left_source, right_source
         self.downscale_factor = downscale_factor
         self.visualize_live = visualize_live
@@ -37,7 +103,8 @@ class StereoDepthEstimatorVideo:
         self.drop_frames = drop_frames
         self.visualize_gray = visualize_gray
         self.devices = list(devices) if devices else None
-        self.chunk = chunk
+        self.chunk = chunk              # frames per GPU call; None: the engine's preferred batch for the frame size,
+        self.max_chunk = max_chunk      # bounded by max_chunk (the latency knob: a frame waits for its chunk to fill)
         self.core = StereoCore(downscale_factor=downscale_factor, fast_mode=fast_mode,
                                device=self.devices[0] if self.devices else 0)
 
@@ -45,10 +112,11 @@ class StereoDepthEstimatorVideo:
         self.core.configure_sgbm(**kwargs)
 
     # -- frame sources ----------------------------------------------------------------------------
-    def _frames(self):
+    def _frames(self, downscale_factor=None):
+        f = self.downscale_factor if downscale_factor is None else downscale_factor
         if self.use_threading:
-            cap = ThreadedStereoCapture(self.left_source, self.right_source, downscale_factor=self.downscale_factor,
-                                        drop_frames=self.drop_frames)
+            cap = ThreadedStereoCapture(self.left_source, self.right_source, downscale_factor=f,
+                                        drop_frames=self.drop_frames, device=self.core.device)
             cap.start()
             try:
                 while True:
@@ -59,7 +127,7 @@ class StereoDepthEstimatorVideo:
             finally:
                 cap.stop()
         else:
-            yield from stereo_stream(self.left_source, self.right_source, downscale_factor=self.downscale_factor)
+            yield from stereo_stream(self.left_source, self.right_source, downscale_factor=f, device=self.core.device)
 
     def _pace(self, t0):
         if self._frame_interval > 0:
@@ -79,7 +147,9 @@ class StereoDepthEstimatorVideo:
         # the reference re-applies the (already scaled) parameters here, which scales num_disp /
         # focal_length / doffs a second time when downscale_factor != 1 (:78) — kept for parity
         self.core.configure_sgbm(**self.core.get_sgbm_params())
-        if self.devices and (len(self.devices) > 1 or self.chunk > 1):
+        # the batched multi-GPU path runs the fused pipeline only; anything it cannot express (Telea hole filling on the
+        # host, a replaced compute_disparity / _process_pair) goes frame by frame through StereoCore like the reference
+        if self.devices and self.core._can_fuse(None, None) and (len(self.devices) > 1 or self.chunk is None or self.chunk > 1):
             yield from self._estimate_sharded()
             return
         t0 = time.time()
@@ -91,7 +161,6 @@ class StereoDepthEstimatorVideo:
 
     def _estimate_sharded(self):
         """Chunks of frames round-robin over ``self.devices``; host gather in frame order."""
-        from ..engine import StereoEngine
         core = self.core
         p = core.get_sgbm_params()
         use_maps = core._calibration()
@@ -101,27 +170,34 @@ class StereoDepthEstimatorVideo:
                                              p['image_height'], p.get('dist_coeff_L'), p.get('dist_coeff_R'),
                                              p.get('rotation'), p.get('translation'), 1.0)
         pp, dp, kw = core._post_params(), core._depth_params(), core._matcher_kwargs()
+        # frames are taken as captured (downscale_factor = 1 in the capture); the INTER_AREA downscale of
+        # input.py:39-43 / threaded_stereo.py:41-46 runs on the worker's device inside the pipeline call
+        frames = iter(self._frames(downscale_factor=1.0))
+        first = next(frames, None)
+        if first is None:
+            return
+        sh, sw = first[0].shape[:2]
+        f = self.downscale_factor
+        area = (int(sw * f), int(sh * f)) if f != 1.0 else None
+        aw, ah = area if area is not None else (sw, sh)
+        size = (int(p['image_width']), int(p['image_height'])) if use_maps else None
+        if size is not None and size != (aw, ah):
+            warnings.warn("Input image size %sx%s does not match calibration %sx%s; resizing for rectification." %
+                          (aw, ah, size[0], size[1]), RuntimeWarning, stacklevel=2)
+        W, H = size if size is not None else (aw, ah)
+        chunk = self.chunk
+        if chunk is None:
+            chunk = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
 
         def make_worker(dev):
-            eng = StereoEngine(dev, **kw)
-            if maps is not None:
-                eng.set_maps(maps['map1_L'], maps['map2_L'], maps['map1_R'], maps['map2_R'])
-            return lambda L, R: eng.pipeline_batch(L, R, pp, dp, use_maps=use_maps)
+            return _FrameWorker(dev, kw, maps, pp, dp, use_maps, size, area)
 
-        def gray_pairs():
-            eng0 = core.sgbm.engine
-            for left, right in self._frames():
-                if use_maps:
-                    size = (p['image_width'], p['image_height'])
-                    left, right = _ensure_image_size(left, size), _ensure_image_size(right, size)
-                if left.ndim == 3:
-                    left = eng0.bgr2gray(left)
-                if right.ndim == 3:
-                    right = eng0.bgr2gray(right)
-                yield left, right
+        def pairs():
+            yield first
+            yield from frames
 
         t0 = time.time()
-        for _disp, depth_m in ThreadedSharder(self.devices, make_worker, self.chunk).run(gray_pairs()):
+        for _disp, depth_m in ThreadedSharder(self.devices, make_worker, chunk, max_inflight=4).run(pairs()):
             yield depth_m
             self._show(depth_m)
             t0 = self._pace(t0)

@@ -2,8 +2,9 @@
 
 ``filter_speckles``, ``detect_outliers`` and ``postprocess_disparity`` run on the GPU through the C ABI
 (``b200s_postprocess``; reference: postprocess.py:6-70, 120-171). ``fill_holes`` (off by default,
-``hole_filling=True`` in the parameter dict) stays on the host: cv2.inpaint(TELEA) is a sequential
-fast-marching method — it is applied between the GPU outlier mask and the GPU median.
+``hole_filling=True`` in the parameter dict): the 'nearest' branch runs on the GPU (``b200s_fill_nearest``); 'inpaint'
+is cv2.inpaint(TELEA), a sequential fast-marching method that SURVEY.md §8f.2 keeps on host cv2 — applied between
+the GPU outlier mask and the GPU median. Nothing else in this module touches the host.
 """
 from __future__ import annotations
 
@@ -33,24 +34,30 @@ def detect_outliers(disparity, threshold=3.0, kernel_size=5, engine=None):
     return (masked != d) & (d > 0)
 
 
+_FILL_NEAREST_MAX_K = 31
+
+
 def fill_holes(disparity, mask=None, method='inpaint', kernel_size=5, engine=None):
     """Hole filling (postprocess.py:72-118). method='nearest' (iterated dilation under the hole mask) runs on the GPU
-    (``b200s_fill_nearest``, bit-exact for float32 maps); method='inpaint' (Telea, a sequential fast-marching method)
-    stays host cv2, as does 'nearest' for element sizes the kernel does not take (> 31) or non-float32 input."""
-    filled = disparity.copy()
+    (``b200s_fill_nearest``, bit-exact) for 2-D float32 maps and element sizes 1..31; anything else raises (no silent
+    host fallback). method='inpaint' is Telea fast marching, a sequential method that SURVEY 8(f2) keeps on host cv2:
+    that is the one documented host step of this module. Other methods return an unchanged copy, as upstream."""
     if mask is None:
         mask = (disparity <= 0)
-    if method == 'nearest' and 1 <= int(kernel_size) <= 31 and np.asarray(disparity).dtype == np.float32 \
-            and np.asarray(disparity).ndim == 2:
-        return _engine(engine).fill_nearest(disparity, mask, int(kernel_size))
-    import cv2
-    hole_mask = mask.astype(np.uint8) * 255
+    if method == 'nearest':
+        d = np.asarray(disparity)
+        if d.dtype != np.float32 or d.ndim != 2:
+            raise ValueError("fill_holes(method='nearest') runs on the GPU for 2-D float32 disparity maps only "
+                             f"(got {d.dtype}, {d.ndim}-D); there is no CPU fallback")
+        if not 1 <= int(kernel_size) <= _FILL_NEAREST_MAX_K:
+            raise ValueError(f"fill_holes(method='nearest'): kernel_size must be in [1, {_FILL_NEAREST_MAX_K}] "
+                             f"(got {kernel_size}); there is no CPU fallback")
+        return _engine(engine).fill_nearest(d, mask, int(kernel_size))
+    filled = disparity.copy()
     if method == 'inpaint':
+        import cv2
+        hole_mask = mask.astype(np.uint8) * 255
         filled = cv2.inpaint(filled.astype(np.float32), hole_mask, kernel_size, cv2.INPAINT_TELEA)
-    elif method == 'nearest':
-        kernel = cv2.getStructuringElement(cv2.MORPH_ELLIPSE, (kernel_size, kernel_size))
-        for _ in range(kernel_size):
-            filled = np.where(mask, cv2.dilate(filled, kernel), filled)
     return filled
 
 

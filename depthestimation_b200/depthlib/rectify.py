@@ -15,18 +15,13 @@ import numpy as np
 
 __all__ = ["rectify_images", "RectificationCache"]
 
-_shared_engine = None
-
-
-def _engine(engine=None):
-    """The caller's engine, or a lazily created module-level one (device 0) for the free functions."""
-    global _shared_engine
+def _engine(engine=None, device: int = 0):
+    """The caller's engine, or the calling thread's own engine on ``device`` for the free functions (the reference's
+    free cv2 calls are thread-safe; a handle owns a stream and scratch, so it is never shared between threads)."""
     if engine is not None:
         return engine
-    if _shared_engine is None:
-        from ..engine import StereoEngine
-        _shared_engine = StereoEngine(0)
-    return _shared_engine
+    from ..engine import thread_engine
+    return thread_engine(device)
 
 
 def _cv2():
@@ -97,17 +92,19 @@ def _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
 
 
 def _ensure_image_size(image: np.ndarray, size: Tuple[int, int], engine=None) -> np.ndarray:
-    """Warn and resize (INTER_LINEAR) when the image does not match the calibration size (rectify.py:92-105): uint8
-    gray / 3-channel images on the GPU (b200s_resize_linear_u8, bit-exact), anything else through host cv2."""
+    """Warn and resize (INTER_LINEAR) when the image does not match the calibration size (rectify.py:92-105). Runs on
+    the GPU (b200s_resize_linear_u8, bit-exact) for what the stereo path carries: uint8 gray / 3-channel images.
+    There is no host fallback: any other dtype or layout raises."""
     height, width = image.shape[:2]
     if (width, height) == tuple(size):
         return image
     warnings.warn("Input image size %sx%s does not match calibration %sx%s; resizing for rectification." %
                   (width, height, size[0], size[1]), RuntimeWarning, stacklevel=2)
-    if image.dtype == np.uint8 and (image.ndim == 2 or (image.ndim == 3 and image.shape[2] in (1, 3))):
-        out = _engine(engine).resize_linear(image, tuple(size))
-        return out[:, :, 0] if (image.ndim == 3 and image.shape[2] == 1) else out   # cv2.resize drops a singleton channel
-    return _cv2().resize(image, tuple(size), interpolation=_cv2().INTER_LINEAR)
+    if image.dtype != np.uint8 or not (image.ndim == 2 or (image.ndim == 3 and image.shape[2] in (1, 3))):
+        raise ValueError("size fix-up runs on the GPU for uint8 HxW / HxWx1 / HxWx3 images only (got %s %s); "
+                         "there is no CPU fallback" % (image.dtype, image.shape))
+    out = _engine(engine).resize_linear(image, tuple(size))
+    return out[:, :, 0] if (image.ndim == 3 and image.shape[2] == 1) else out   # cv2.resize drops a singleton channel
 
 
 def _to_grayscale(image: np.ndarray, engine=None) -> np.ndarray:

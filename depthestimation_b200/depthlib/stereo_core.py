@@ -203,7 +203,7 @@ class StereoCore:
                                              p['image_height'], p.get('dist_coeff_L'), p.get('dist_coeff_R'),
                                              p.get('rotation'), p.get('translation'), 1.0)
             size = (p['image_width'], p['image_height'])
-            left, right = _ensure_image_size(left, size), _ensure_image_size(right, size)
+            left, right = _ensure_image_size(left, size, eng), _ensure_image_size(right, size, eng)
             if getattr(eng, "_maps_id", None) != id(maps):
                 eng.set_maps(maps['map1_L'], maps['map2_L'], maps['map1_R'], maps['map2_R'])
                 eng._maps_id, eng._maps_ref = id(maps), maps

@@ -12,8 +12,9 @@ from .input import _area_downscale, open_capture
 
 
 class ThreadedStereoCapture:
-    def __init__(self, left_source, right_source, downscale_factor=1.0, buffer_size=2, drop_frames=True):
+    def __init__(self, left_source, right_source, downscale_factor=1.0, buffer_size=2, drop_frames=True, device=0):
         self.left_source, self.right_source = left_source, right_source
+        self.device = device            # GPU that runs the INTER_AREA downscale of this capture thread
         self.downscale_factor = downscale_factor
         self.buffer_size = buffer_size
         self.drop_frames = drop_frames
@@ -33,7 +34,7 @@ class ThreadedStereoCapture:
         ok, frame = cap.read()
         if not ok or frame is None:
             return None
-        return _area_downscale(frame, self.downscale_factor)
+        return _area_downscale(frame, self.downscale_factor, self.device)
 
     def _capture_loop(self):
         while not self._stop_event.is_set():

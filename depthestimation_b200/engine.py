@@ -13,9 +13,10 @@ import threading
 import numpy as np
 
 from . import _lib
-from ._lib import B200sDepthParams, B200sParams, B200sPostParams, MODES
+from ._lib import B200sDepthParams, B200sFrameIO, B200sParams, B200sPostParams, MODES
 
-__all__ = ["StereoEngine", "EngineError", "make_params", "make_post_params", "make_depth_params", "thread_engine"]
+__all__ = ["StereoEngine", "EngineError", "make_params", "make_post_params", "make_depth_params", "thread_engine",
+           "pinned_empty"]
 
 
 class EngineError(RuntimeError):
@@ -67,6 +68,21 @@ def _pair(left, right):
     if left.strides != right.strides:
         left, right = np.ascontiguousarray(left), np.ascontiguousarray(right)
     return left, right
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """numpy array in page-locked host memory (b200s_host_alloc): the host side of the asynchronous batch calls.
+    Freed when the array (and every view of it) is gone."""
+    import weakref
+    lib = _lib.load()
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    ptr = C.c_void_p()
+    if n == 0 or lib.b200s_host_alloc(n, C.byref(ptr)) != 0:
+        raise EngineError(f"b200s_host_alloc({n}) failed: no usable CUDA device or out of page-locked memory")
+    buf = (C.c_ubyte * n).from_address(ptr.value)
+    weakref.finalize(buf, lib.b200s_host_free, C.c_void_p(ptr.value))
+    return np.frombuffer(buf, dtype=dtype).reshape(shape)
 
 
 _tls = threading.local()
@@ -281,8 +297,9 @@ class StereoEngine:
         self._check(self._lib.b200s_pipeline_batch_dev(self._h, dL, dR, B, H, W, int(bool(use_maps)), C.byref(pp),
                                                        C.byref(dp), dDisp, dDepth), "b200s_pipeline_batch_dev")
 
-    def pipeline_batch(self, lefts, rights, pp, dp, use_maps=False, out_disp=None, out_depth=None):
-        """Host batch: lefts/rights uint8 [B,H,W] C-contiguous (pinned for best speed) -> float32 [B,H,W-D]."""
+    def pipeline_batch(self, lefts, rights, pp, dp, use_maps=False, out_disp=None, out_depth=None, want_disp=True):
+        """Host batch: lefts/rights uint8 [B,H,W] C-contiguous (pinned for best speed) -> float32 [B,H,W-D].
+        want_disp=False: depth only (the disparity plane is not copied back; returns (None, depth))."""
         lefts, rights = np.asarray(lefts), np.asarray(rights)
         if lefts.dtype != np.uint8 or rights.dtype != np.uint8 or lefts.ndim != 3 or lefts.shape != rights.shape:
             raise ValueError("pipeline_batch expects two uint8 [B,H,W] arrays of equal shape")
@@ -291,14 +308,15 @@ class StereoEngine:
         Wc = W - self.params.numDisparities
         if Wc <= 0:
             raise ValueError("num_disp must be smaller than the image width")
-        disp = out_disp if out_disp is not None else np.empty((B, H, Wc), np.float32)
+        disp = (out_disp if out_disp is not None else np.empty((B, H, Wc), np.float32)) if want_disp else None
         depth = (out_depth if out_depth is not None else np.empty((B, H, Wc), np.float32)) if dp.enabled else None
         self._check(self._lib.b200s_pipeline_batch(
             self._h, lefts.ctypes.data, rights.ctypes.data, B, H, W, int(bool(use_maps)), C.byref(pp), C.byref(dp),
-            disp.ctypes.data, depth.ctypes.data if depth is not None else None), "b200s_pipeline_batch")
+            disp.ctypes.data if disp is not None else None, depth.ctypes.data if depth is not None else None),
+            "b200s_pipeline_batch")
         return disp, depth
 
-    def pipeline_batch_submit(self, lefts, rights, pp, dp, use_maps=False, out_disp=None, out_depth=None):
+    def pipeline_batch_submit(self, lefts, rights, pp, dp, use_maps=False, out_disp=None, out_depth=None, want_disp=True):
         """Asynchronous pipeline_batch: enqueue H2D -> kernels -> D2H for one chunk and return a ticket at once.
         At most four chunks in flight; the arrays (pinned for real overlap) must not be touched until
         pipeline_batch_wait(ticket) returns (disp, depth)."""
@@ -310,20 +328,68 @@ class StereoEngine:
         Wc = W - self.params.numDisparities
         if Wc <= 0:
             raise ValueError("num_disp must be smaller than the image width")
-        disp = out_disp if out_disp is not None else np.empty((B, H, Wc), np.float32)
+        disp = (out_disp if out_disp is not None else np.empty((B, H, Wc), np.float32)) if want_disp else None
         depth = (out_depth if out_depth is not None else np.empty((B, H, Wc), np.float32)) if dp.enabled else None
         ticket = C.c_int(0)
         self._check(self._lib.b200s_pipeline_batch_submit(
             self._h, lefts.ctypes.data, rights.ctypes.data, B, H, W, int(bool(use_maps)), C.byref(pp), C.byref(dp),
-            disp.ctypes.data, depth.ctypes.data if depth is not None else None, C.byref(ticket)),
-            "b200s_pipeline_batch_submit")
+            disp.ctypes.data if disp is not None else None, depth.ctypes.data if depth is not None else None,
+            C.byref(ticket)), "b200s_pipeline_batch_submit")
         self._inflight[ticket.value] = (lefts, rights, disp, depth, pp, dp)   # keep the buffers alive
         return ticket.value
 
     def pipeline_batch_wait(self, ticket: int):
         self._check(self._lib.b200s_pipeline_batch_wait(self._h, int(ticket)), "b200s_pipeline_batch_wait")
-        _, _, disp, depth, _, _ = self._inflight.pop(int(ticket))
+        held = self._inflight.pop(int(ticket))
+        if isinstance(held, dict):
+            return held["disp"], held["disp16"], held["depth"]
+        _, _, disp, depth, _, _ = held
         return disp, depth
+
+    def pipeline_frames_submit(self, lefts, rights, pp, dp, size=None, area=None, use_maps=False, want_disp=True,
+                               want_disp16=False, want_depth=True, out_disp=None, out_disp16=None, out_depth=None):
+        """The general asynchronous batch call (b200s_pipeline_frames_submit): ``lefts`` / ``rights`` are uint8
+        [B,h,w] or [B,h,w,3] frames as captured; ``area`` = (W, H) of the INTER_AREA downscale (input.py:39-43), ``size``
+        = (W, H) the matcher runs at (the calibration size; INTER_LINEAR fix-up when it differs, rectify.py:92-105);
+        gray conversion, remap, matching, post-filters and depth follow on the device. Only the requested planes are
+        copied back: float32 disparity, int16 x16 disparity, float32 depth. Returns a ticket for pipeline_batch_wait,
+        which returns (disp, disp16, depth) with None for planes not requested."""
+        lefts, rights = np.asarray(lefts), np.asarray(rights)
+        if lefts.dtype != np.uint8 or rights.dtype != np.uint8 or lefts.ndim not in (3, 4) or lefts.shape != rights.shape \
+                or (lefts.ndim == 4 and lefts.shape[3] not in (1, 3)):
+            raise ValueError("pipeline_frames expects two uint8 [B,H,W] or [B,H,W,3] arrays of equal shape")
+        lefts, rights = np.ascontiguousarray(lefts), np.ascontiguousarray(rights)
+        B, sH, sW = lefts.shape[:3]
+        cn = 1 if lefts.ndim == 3 else int(lefts.shape[3])
+        aW, aH = (int(area[0]), int(area[1])) if area is not None else (sW, sH)
+        W, H = (int(size[0]), int(size[1])) if size is not None else (aW, aH)
+        Wc = W - self.params.numDisparities
+        if Wc <= 0:
+            raise ValueError("num_disp must be smaller than the image width")
+        want_depth = bool(want_depth and dp.enabled)
+        disp = (out_disp if out_disp is not None else np.empty((B, H, Wc), np.float32)) if want_disp else None
+        disp16 = (out_disp16 if out_disp16 is not None else np.empty((B, H, Wc), np.int16)) if want_disp16 else None
+        depth = (out_depth if out_depth is not None else np.empty((B, H, Wc), np.float32)) if want_depth else None
+        for a, shp in ((disp, np.float32), (disp16, np.int16), (depth, np.float32)):
+            if a is not None and (a.dtype != shp or a.shape != (B, H, Wc) or not a.flags.c_contiguous):
+                raise ValueError("output buffers must be C-contiguous [B, H, W - num_disp] arrays of the plane's dtype")
+        io = B200sFrameIO(lefts.ctypes.data, rights.ctypes.data, B, sH, sW, cn, aH, aW, H, W, int(bool(use_maps)),
+                          disp.ctypes.data if disp is not None else None,
+                          disp16.ctypes.data if disp16 is not None else None,
+                          depth.ctypes.data if depth is not None else None)
+        ticket = C.c_int(0)
+        self._check(self._lib.b200s_pipeline_frames_submit(self._h, C.byref(io), C.byref(pp), C.byref(dp),
+                                                           C.byref(ticket)), "b200s_pipeline_frames_submit")
+        self._inflight[ticket.value] = dict(L=lefts, R=rights, disp=disp, disp16=disp16, depth=depth, pp=pp, dp=dp)
+        return ticket.value
+
+    def pipeline_frames(self, lefts, rights, pp, dp, **kw):
+        return self.pipeline_batch_wait(self.pipeline_frames_submit(lefts, rights, pp, dp, **kw))
+
+    @property
+    def last_flow(self) -> int:
+        """B200S_FLOW_* bits of the last matcher call (which kernels ran)."""
+        return int(self._lib.b200s_last_flow(self._h))
 
     def stage_times(self, reset=False):
         """{stage: (device ms, kernel launches)} accumulated while timing is enabled."""

@@ -48,10 +48,15 @@ def gather_in_order(local: Dict[int, object], n_frames: int, group=None, dst: in
 class ThreadedSharder:
     """Chunks of frames -> GPUs round-robin, ordered results back.
 
-    ``make_worker(device) -> callable(lefts[B,H,W], rights[B,H,W]) -> (disp[B,...], depth[B,...] | None)``
-    is called once per device inside that device's worker thread (so each thread owns its handle, like one
-    cv2.StereoSGBM per thread in the reference). A failing worker re-queues its chunk for the others; when
-    every worker has failed the error is raised to the caller.
+    ``make_worker(device)`` is called once per device inside that device's worker thread (so each thread owns its
+    handle, like one cv2.StereoSGBM per thread in the reference) and returns either
+    * a callable ``fn(lefts[B,...], rights[B,...]) -> (disp[B,...] | None, depth[B,...] | None)`` (blocking), or
+    * an object with ``submit(lefts: list, rights: list) -> token`` and ``wait(token) -> (disp, depth)`` and an
+      optional ``max_inflight`` (default 3): the worker then keeps that many chunks in flight on its GPU, so uploads,
+      kernels and downloads of consecutive chunks overlap (b200s_pipeline_frames_submit / b200s_pipeline_batch_wait).
+      ``submit`` receives the chunk as two lists of frames (no host-side stacking on the dispatcher thread).
+    A failing worker re-queues its chunks for the others; when every worker has failed the error is raised to the
+    caller.
     """
 
     def __init__(self, devices: Sequence[int], make_worker: Callable[[int], Callable], chunk: int = 8,
@@ -69,29 +74,62 @@ class ThreadedSharder:
         alive = [G]
         errors: List[BaseException] = []
 
+        def fail(exc, items):
+            with cv:
+                errors.append(exc); alive[0] -= 1
+                if alive[0] > 0:
+                    for it_ in items:
+                        work.put(it_)            # another GPU picks the chunks up
+                cv.notify_all()
+
         def worker(dev):
             try:
                 fn = self.make_worker(dev)
             except BaseException as exc:  # noqa: BLE001
-                with cv:
-                    errors.append(exc); alive[0] -= 1; cv.notify_all()
+                fail(exc, [])
                 return
-            while True:
-                item = work.get()
-                if item is None:
-                    break
-                cid, L, R = item
-                try:
-                    res = fn(L, R)
-                except BaseException as exc:  # noqa: BLE001
+            if not hasattr(fn, "submit"):        # blocking worker: one chunk at a time
+                while True:
+                    item = work.get()
+                    if item is None:
+                        break
+                    cid, Ls, Rs = item
+                    try:
+                        res = fn(np.ascontiguousarray(np.stack(Ls)), np.ascontiguousarray(np.stack(Rs)))
+                    except BaseException as exc:  # noqa: BLE001
+                        fail(exc, [item])
+                        return
                     with cv:
-                        errors.append(exc); alive[0] -= 1
-                        if alive[0] > 0:
-                            work.put(item)       # another GPU picks the chunk up
+                        done[cid] = res
                         cv.notify_all()
+                return
+            cap = max(1, int(getattr(fn, "max_inflight", 3)))
+            flying = []                          # [(item, token)] oldest first
+            stop = False
+            while True:
+                try:
+                    while not stop and len(flying) < cap:
+                        try:
+                            item = work.get(block=not flying)
+                        except queue.Empty:
+                            break
+                        if item is None:
+                            stop = True
+                            break
+                        flying.append((item, None))
+                        flying[-1] = (item, fn.submit(item[1], item[2]))
+                    if not flying:
+                        if stop:
+                            break
+                        continue
+                    item, tok = flying[0]
+                    res = fn.wait(tok)
+                    flying.pop(0)
+                except BaseException as exc:  # noqa: BLE001
+                    fail(exc, [it_ for it_, _ in flying])
                     return
                 with cv:
-                    done[cid] = res
+                    done[item[0]] = res
                     cv.notify_all()
 
         threads = [threading.Thread(target=worker, args=(d,), daemon=True) for d in self.devices]
@@ -111,7 +149,7 @@ class ThreadedSharder:
                     if not Ls:
                         exhausted = True
                         break
-                    work.put((submitted, np.ascontiguousarray(np.stack(Ls)), np.ascontiguousarray(np.stack(Rs))))
+                    work.put((submitted, Ls, Rs))
                     submitted += 1
                     if len(Ls) < self.chunk:
                         exhausted = True
@@ -124,8 +162,9 @@ class ThreadedSharder:
                         cv.wait(timeout=0.5)
                     disp, depth = done.pop(emitted)
                 emitted += 1
-                for k in range(disp.shape[0]):
-                    yield disp[k], (depth[k] if depth is not None else None)
+                n = (disp if disp is not None else depth).shape[0]
+                for k in range(n):
+                    yield (disp[k] if disp is not None else None), (depth[k] if depth is not None else None)
         finally:
             for _ in threads:
                 work.put(None)

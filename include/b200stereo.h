@@ -152,7 +152,7 @@ int b200s_disp_to_depth(B200sHandle* h, const float* disp, size_t n, const B200s
 
 /* StereoCore.estimate_depth for an already-gray pair (depthlib/stereo_core.py:274-293):
  * [remap if maps are set and use_maps] -> sgbm -> crop [:, numDisparities:] -> post -> depth.
- * disp/depth are dense H x (W - numDisparities) float32; depth may be NULL when !dp->enabled.
+ * disp/depth are dense H x (W - numDisparities) float32; either may be NULL (not copied back).
  * rectL/rectR (dense HxW u8) may be NULL. */
 int b200s_pipeline(B200sHandle* h, const uint8_t* L, const uint8_t* R, int H, int W, size_t stride,
                    int use_maps, const B200sPostParams* pp, const B200sDepthParams* dp,
@@ -182,6 +182,40 @@ int b200s_pipeline_batch_submit(B200sHandle* h, const uint8_t* L, const uint8_t*
                                 int use_maps, const B200sPostParams* pp, const B200sDepthParams* dp,
                                 float* disp, float* depth, int* ticket);
 int b200s_pipeline_batch_wait(B200sHandle* h, int ticket);
+/* In b200s_pipeline, b200s_pipeline_batch and b200s_pipeline_batch_submit either output may be NULL: a plane nobody
+ * asked for is not copied back (disp == NULL with depth enabled = depth only, what the reference's video generator
+ * yields, depthlib/StereoDepthEstimatorVideo.py:103,130). Requesting nothing is B200S_E_INVALID. */
+
+/* The general form of the batch call: frames as they come from the capture / file (depthlib/input.py:26-43,
+ * depthlib/threaded_stereo.py:36-52), input preparation on the device, any subset of the outputs.
+ *   input prep, in the reference's order: [cv2.resize(INTER_AREA) to areaW x areaH  (input.py:39-43, threaded_stereo.py:41-46)]
+ *   -> [cv2.resize(INTER_LINEAR) to W x H when the size still differs from the calibration size  (_ensure_image_size,
+ *   rectify.py:92-105)] -> gray with the BGR weights on the channels as stored (rectify.py:108-119, stereo_core.py:156-159;
+ *   fused into the remap taps when use_maps) -> [remap] -> match -> crop -> post -> depth as b200s_pipeline.
+ *   L, R: B dense frames of srcH x srcW x channels uint8 (channels 1 or 3). areaH/areaW 0 = no downscale.
+ *   Outputs (host, each dense B x H x (W - numDisparities), each may be NULL): disp float32; disp16 int16 = disparity x 16
+ *   (exact: every post stage selects among the matcher's fixed-point values, 2 B/px instead of 4); depth float32.
+ * Asynchronous like b200s_pipeline_batch_submit (same slots, same tickets, wait with b200s_pipeline_batch_wait);
+ * b200s_pipeline_frames = submit + wait. */
+typedef struct B200sFrameIO {
+    const uint8_t* L;
+    const uint8_t* R;
+    int32_t B, srcH, srcW, channels;
+    int32_t areaH, areaW;
+    int32_t H, W;
+    int32_t use_maps;
+    float* disp;
+    int16_t* disp16;
+    float* depth;
+} B200sFrameIO;
+int b200s_pipeline_frames_submit(B200sHandle* h, const B200sFrameIO* io, const B200sPostParams* pp,
+                                 const B200sDepthParams* dp, int* ticket);
+int b200s_pipeline_frames(B200sHandle* h, const B200sFrameIO* io, const B200sPostParams* pp, const B200sDepthParams* dp);
+
+/* Page-locked host memory for the frame loop's chunk buffers ("pinned double buffers"): the copies of the
+ * asynchronous calls above only overlap the kernels when their host side is page-locked. Portable across devices. */
+int b200s_host_alloc(size_t bytes, void** out);
+int b200s_host_free(void* p);
 
 /* ---- allocation-free variant ---------------------------------------------------------------- */
 
@@ -219,6 +253,15 @@ int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch);
  * full aggregate S (needed for the S tap above; slower, same results). Default off: horizontal
  * paths + winner selection are fused (rows.cu) and S holds only the vertical-family aggregate. */
 int b200s_set_debug_flow(B200sHandle* h, int on);
+/* Which kernels the last matcher call of this handle ran (bit set of B200S_FLOW_*): tests use it to prove that the
+ * fused cluster kernel, not the generic per-direction fallback, ran on every device of a multi-GPU process. */
+enum {
+    B200S_FLOW_VERT_DOWN = 1,      /* k_vert, top-down family */
+    B200S_FLOW_VERT_UP = 2,        /* k_vert, bottom-up family (hh) */
+    B200S_FLOW_PATH_VERTICAL = 4,  /* generic k_path used for a vertical / diagonal direction */
+    B200S_FLOW_ROWS_FUSED = 8      /* k_rows (horizontal paths + selection) */
+};
+int b200s_last_flow(const B200sHandle* h);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 long long b200s_launch_count(const B200sHandle* h);
 /* Device time in ms of the last *_dev / host call, measured with CUDA events on the handle's

@@ -174,6 +174,42 @@ def test_full_size_4k_d256(engine):
     _flows_agree(engine, 2160, 3840, 256, "sgbm", 1005)        # BASELINE config #5 (one pair of the 64)
 
 
+def _full_size_vs_cv2(engine, H, W, D, mode, seed, **extra):
+    """The two largest BASELINE configurations against the REAL oracle at full size: cv2.StereoSGBM.compute on the host
+    (cv2 is on the GPU box; seconds per frame), then the whole per-frame pipeline (crop, speckles, outliers, median,
+    depth) against the same chain of cv2 calls. Volumes here are 0.9 - 4 GB per frame: pitch, padding and 32-bit offset
+    mistakes show up at this size and nowhere else."""
+    pytest.importorskip("cv2")
+    from oracle import cv2_reference as cr
+    from depthestimation_b200.engine import make_depth_params, make_post_params
+    L, R, _ = make_pair(H, W, D, seed=seed)
+    kw = dict(min_disp=0, num_disp=D, block_size=5, sgbm_mode=mode, **extra)
+    engine.configure(**kw)
+    engine.set_debug_flow(False)
+    got = engine.compute(L, R)
+    want = cr.compute_disparity16(L, R, **kw)
+    assert np.array_equal(got, want), f"{(got != want).sum()} of {got.size} px differ from cv2 ({mode} {W}x{H} D={D})"
+    pp = make_post_params(False, 100, 1.0, 2.5, True)
+    dp = make_depth_params(0.8 * W, 0.54, 0.0, eps=0, max_depth=100.0)
+    disp, depth, _, _ = engine.pipeline(L, R, pp, dp)
+    wd, wz = cr.Cv2StereoPipeline(kw, None, 1.0, False, 0.8 * W, 0.54, 0.0, 100.0)(L, R)
+    assert np.array_equal(disp, wd), f"{(disp != wd).sum()} px of the post-processed disparity differ"
+    fin = np.isfinite(wz)
+    assert np.array_equal(np.isfinite(depth), fin) and np.allclose(depth[fin], wz[fin], rtol=1e-4, atol=0)
+
+
+def test_full_size_1080p_hh_d256_vs_cv2(engine):
+    """BASELINE config #3: 1920x1080, D = 256, 8-path (hh) + LR check + speckle filter."""
+    _full_size_vs_cv2(engine, 1080, 1920, 256, "hh", 1003, disp12_max_diff=1, speckle_window_size=100, speckle_range=2)
+
+
+@pytest.mark.parametrize("mode", ["sgbm_3way", "sgbm"])
+def test_full_size_4k_d256_vs_cv2(engine, mode):
+    """BASELINE config #5 (one pair of the 64): 3840x2160, D = 256, in the mode tools/bench_configs.py measures
+    (sgbm_3way, vertical path through the generic kernel: the cluster kernel's 31-bit offset guard) and in sgbm."""
+    _full_size_vs_cv2(engine, 2160, 3840, 256, mode, 1005)
+
+
 _CLAMP_SCRIPT = r"""
 import sys, numpy as np
 sys.path.insert(0, {root!r})
