@@ -49,26 +49,14 @@ def make_inputs(batch: int):
 
 
 def make_maps():
-    """Rectification maps for the synthetic calibration: cv2 (as rectify.py:63-73) when importable,
-    else a numpy radial-distortion model of the same magnitude (map generation is host-side, once)."""
+    """Rectification maps for the synthetic calibration, built by the PRODUCT package exactly as StereoCore does per
+    calibration (depthestimation_b200.depthlib.rectify.RectificationCache, alpha = 1.0 as stereo_core.py:150)."""
+    from depthestimation_b200.depthlib.rectify import RectificationCache
     from depthestimation_b200.synth import make_calibration
     cal = make_calibration(H, W)
-    try:
-        from oracle import cv2_reference as cr
-        if cr.HAVE_CV2:
-            return cr.build_maps(cal, alpha=1.0), cal
-    except Exception:
-        pass
-    ys, xs = np.mgrid[0:H, 0:W].astype(np.float32)
-    f, cx, cy = 0.8 * W, W / 2, H / 2
-    xn, yn = (xs - cx) / f, (ys - cy) / f
-    r2 = xn * xn + yn * yn
-    out = {}
-    for side, k1 in (("L", -0.05), ("R", -0.04)):
-        s = 1 + k1 * r2 + 0.01 * r2 * r2
-        out[f"map1_{side}"] = (xn * s * f + cx).astype(np.float32)
-        out[f"map2_{side}"] = (yn * s * f + cy).astype(np.float32)
-    return out, cal
+    maps = RectificationCache().get_maps(cal["cam_matrix_L"], cal["cam_matrix_R"], cal["baseline"], W, H,
+                                         cal["dist_coeff_L"], cal["dist_coeff_R"], None, None, 1.0)
+    return maps, cal
 
 
 class ClockSampler:
@@ -152,6 +140,23 @@ class CpuReference:
         d = o.postprocess(d, 100, 1.0, 2.5)
         return d, o.disp_to_depth(d, self.cal["focal_length"], self.cal["baseline"], 0.0, eps=0)
 
+    def as_shipped(self, L, R, nframes: int) -> dict:
+        """BASELINE.md section 3's other CPU figure: ONE stream, cv2's default thread pool (what a user of the reference
+        gets from StereoDepthEstimator.estimate_depth in a loop), with the per-stage split of SURVEY section 6."""
+        if not self.have_cv2:
+            return {}
+        import cv2
+        cv2.setNumThreads(-1)
+        timers: dict = {}
+        self.pipes[0](L[0], R[0])
+        t0 = time.perf_counter()
+        for i in range(nframes):
+            self.pipes[0](L[i % len(L)], R[i % len(R)], timers)
+        t = time.perf_counter() - t0
+        cv2.setNumThreads(1)
+        return {"as_shipped_fps": nframes / t, "as_shipped_sample": f"{nframes} frames, one stream, cv2.setNumThreads(-1)",
+                "stage_ms_per_frame": {k: 1e3 * v / nframes for k, v in timers.items()}}
+
     def run_frames(self, L, R, nframes: int) -> float:
         """Process nframes (cycled from the batch) on all cores; returns seconds."""
         from concurrent.futures import ThreadPoolExecutor
@@ -218,6 +223,123 @@ def ncu_traffic(stage, batch):
         return float(t["dram_bytes_per_launch"]) * batch / float(t["batch"])
     except Exception:
         return None
+
+
+def parity_check(L, R, maps, cal, d_disp, d_depth, h_disp16, frames):
+    """Frames `frames` of the timed batch: device results against the reference chain (checker = oracle/, as in tests)."""
+    from oracle import cv2_reference as cr
+    disp, depth = d_disp.cpu().numpy(), d_depth.cpu().numpy()
+    mism = 0
+    if cr.HAVE_CV2:
+        pipe = cr.Cv2StereoPipeline(SGBM_KW, calib=None, downscale=1.0, fast_mode=False,
+                                    focal_length=cal["focal_length"], baseline=cal["baseline"])
+        pipe.maps = maps
+        checker = f"cv2 {cr.CV2_VERSION} as depthlib drives it"
+        ref = lambda l, r: pipe(l, r)
+    else:
+        import oracle
+        prm = oracle.make_params(**SGBM_KW)
+        checker = "C oracle"
+
+        def ref(l, r):
+            l = oracle.remap_u8(l, maps["map1_L"], maps["map2_L"]); r = oracle.remap_u8(r, maps["map1_R"], maps["map2_R"])
+            d = oracle.postprocess((oracle.sgbm_compute(l, r, prm).astype(np.float32) / 16.0)[:, D:], 100, 1.0, 2.5)
+            return d, oracle.disp_to_depth(d, cal["focal_length"], cal["baseline"], 0.0, eps=0)
+    for k in frames:
+        wd, wz = ref(L[k], R[k])
+        fin = np.isfinite(wz)
+        ok = (np.array_equal(disp[k], wd) and np.array_equal(h_disp16[k], np.rint(wd * 16).astype(np.int16)) and
+              np.array_equal(np.isfinite(depth[k]), fin) and np.allclose(depth[k][fin], wz[fin], rtol=1e-4, atol=0))
+        mism += 0 if ok else 1
+    return {"frames": len(frames), "mismatch": mism, "checker": checker,
+            "what": "float32 disparity and int16 x16 disparity bit-exact, depth within 1e-4 relative"}
+
+
+VH, VW, VD, VFRAMES = 720, 1280, 128, 240
+
+
+def video_api_leg(local, rank, world, barrier, dist, torch):
+    """BASELINE config #4 through the reference-shaped API: VFRAMES synthetic 1280x720 3-channel frames per rank (frame i
+    of the global stream goes to rank i mod world: weak scaling, like the rest of this line) through
+    StereoDepthEstimatorVideo(devices=[local]); the generator yields one depth map per frame, in order."""
+    from depthestimation_b200.depthlib import StereoDepthEstimatorVideo
+    from depthestimation_b200.synth import make_calibration, make_pair
+    distinct = []
+    for k in range(3):
+        l, r, _ = make_pair(VH, VW, VD, seed=1100 + k)
+        distinct.append((np.ascontiguousarray(np.stack([l] * 3, -1)), np.ascontiguousarray(np.stack([r] * 3, -1))))
+    lefts = [distinct[i % 3][0] for i in range(VFRAMES)]
+    rights = [distinct[i % 3][1] for i in range(VFRAMES)]
+    cal = make_calibration(VH, VW)
+    cfg = dict(cal)
+    cfg.update(num_disp=VD, max_depth=100.0)
+
+    vid = StereoDepthEstimatorVideo(lefts, rights, target_fps=0, devices=[local])
+    vid.configure_sgbm(**cfg)
+
+    def run():
+        n, sink = 0, 0.0
+        for depth_m in vid.estimate_depth():
+            n += 1
+            sink += float(depth_m[0, 0])
+        return n
+
+    run()                                         # warm-up: allocations, maps, page-locked buffers
+    barrier()
+    t0 = time.perf_counter()
+    n = run()
+    te = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    assert n == VFRAMES
+    # the 240-frame job of config #4 lasts ~0.1 s (three chunks): filling the first chunk and draining the last are
+    # a fifth of it. The same generator on a stream four times as long, for the steady-state rate:
+    vid.left_source, vid.right_source = lefts * 4, rights * 4
+    barrier()
+    t0 = time.perf_counter()
+    n4 = run()
+    t4 = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t4, op=dist.ReduceOp.MAX)
+    assert n4 == 4 * VFRAMES
+    # the same frames through the asynchronous C ABI directly (page-locked chunk buffers already filled, depth plane
+    # only, three chunks in flight): what the Python generator above is measured against
+    from depthestimation_b200.engine import pinned_empty
+    w = vid._worker_pool[local][0]
+    eng = w.eng
+    Bc = min(eng.preferred_batch(VH, VW), VFRAMES)
+    bufs = []
+    for _ in range(3):
+        bL, bR = pinned_empty((Bc, VH, VW, 3), np.uint8), pinned_empty((Bc, VH, VW, 3), np.uint8)
+        for k in range(Bc):
+            bL[k] = lefts[k]; bR[k] = rights[k]
+        bufs.append((bL, bR, pinned_empty((Bc, VH, VW - VD), np.float32)))
+
+    def cabi(nchunks):
+        fly = []
+        for i in range(nchunks):
+            if len(fly) == 3:
+                eng.pipeline_batch_wait(fly.pop(0))
+            bL, bR, out = bufs[i % 3]
+            fly.append(eng.pipeline_frames_submit(bL, bR, w.pp, w.dp, size=w.size, area=w.area, use_maps=w.use_maps,
+                                                  want_disp=False, want_depth=True, out_depth=out))
+        for tk in fly:
+            eng.pipeline_batch_wait(tk)
+
+    cabi(3)
+    barrier()
+    nch = 8
+    t0 = time.perf_counter()
+    cabi(nch)
+    tc = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(tc, op=dist.ReduceOp.MAX)
+    return {"value": world * VFRAMES / float(te.item()), "unit": UNIT, "frames_per_rank": VFRAMES,
+            "value_960_frames": world * n4 / float(t4.item()),
+            "cabi_async_same_shape_fps": world * nch * Bc / float(tc.item()), "cabi_chunk": Bc,
+            "workload": f"video_{VW}x{VH}_D{VD}_sgbm_3way_bgr_frames_rectify+match+post+depth",
+            "h2d_bytes_per_frame": 2 * VH * VW * 3, "d2h_bytes_per_frame": VH * (VW - VD) * 4,
+            "api": "depthlib.StereoDepthEstimatorVideo(devices=[gpu]).estimate_depth() generator, in-memory frame sources"}
 
 
 def run_b200(args):
@@ -317,49 +439,86 @@ def run_b200(args):
     # its own inputs host->device and its own results device->host inside the timed region; the copies of step k+1 /
     # k-1 overlap the kernels of step k (the extra slots keep the uploads of k+1, k+2 from waiting for the download of
     # k-1 when the host's PCIe throughput is shared by eight ranks). Four buffer sets rotate.
+    # Three output selections: float disparity + float depth (what StereoCore.estimate_depth returns: the headline
+    # `e2e`), depth only (what the reference's video generator yields, StereoDepthEstimatorVideo.py:103,130), and
+    # int16 x16 disparity + depth (what sgbm.compute itself returns, stereo_core.py:231, 2 B/px).
+    from depthestimation_b200.engine import pinned_empty
     DEPTH = 4
     sets = []
     for _ in range(DEPTH):
-        hL, hR = torch.from_numpy(L.copy()).pin_memory(), torch.from_numpy(R.copy()).pin_memory()
-        hDisp = torch.empty((B, H, Wc), dtype=torch.float32).pin_memory()
-        hDepth = torch.empty((B, H, Wc), dtype=torch.float32).pin_memory()
-        sets.append((hL, hR, hDisp, hDepth, hL.numpy(), hR.numpy(), hDisp.numpy(), hDepth.numpy()))
+        nL, nR = pinned_empty(L.shape, np.uint8), pinned_empty(R.shape, np.uint8)
+        nL[...] = L; nR[...] = R
+        sets.append(dict(L=nL, R=nR, disp=pinned_empty((B, H, Wc), np.float32), depth=pinned_empty((B, H, Wc), np.float32),
+                         disp16=pinned_empty((B, H, Wc), np.int16)))
 
-    def submit(i):
-        _, _, _, _, nL, nR, nDisp, nDepth = sets[i % DEPTH]
-        return eng.pipeline_batch_submit(nL, nR, pp, dp, use_maps=True, out_disp=nDisp, out_depth=nDepth)
+    def e2e_leg(want_disp, want_disp16, want_depth, n):
+        def submit(i):
+            st = sets[i % DEPTH]
+            return eng.pipeline_frames_submit(st["L"], st["R"], pp, dp, use_maps=True, want_disp=want_disp,
+                                              want_disp16=want_disp16, want_depth=want_depth, out_disp=st["disp"],
+                                              out_disp16=st["disp16"], out_depth=st["depth"])
+        probe = "depth" if want_depth else "disp"
 
-    def e2e_loop(n):
-        sink = 0.0
-        inflight = []                                   # (ticket, step)
-        for i in range(n):
-            if len(inflight) == DEPTH:                  # the slot / buffer set of step i is that of step i - DEPTH
-                tk, j = inflight.pop(0)
+        def loop(n):
+            sink = 0.0
+            inflight = []                                   # (ticket, step)
+            for i in range(n):
+                if len(inflight) == DEPTH:                  # the slot / buffer set of step i is that of step i - DEPTH
+                    tk, j = inflight.pop(0)
+                    eng.pipeline_batch_wait(tk)
+                    sink += float(sets[j % DEPTH][probe][0, 0, 0])  # device->host result is consumed
+                inflight.append((submit(i), i))
+            for tk, j in inflight:
                 eng.pipeline_batch_wait(tk)
-                sink += float(sets[j % DEPTH][7][0, 0, 0])  # device->host result is consumed
-            inflight.append((submit(i), i))
-        for tk, j in inflight:
-            eng.pipeline_batch_wait(tk)
-            sink += float(sets[j % DEPTH][7][0, 0, 0])
-        return sink
+                sink += float(sets[j % DEPTH][probe][0, 0, 0])
+            return sink
 
-    e2e_loop(max(DEPTH, min(args.warmup, 3)))
-    barrier()
+        loop(max(DEPTH, min(args.warmup, 3)))
+        barrier()
+        t0 = time.perf_counter()
+        loop(n)
+        torch.cuda.synchronize()
+        mine = time.perf_counter() - t0
+        te = torch.tensor([mine], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        d2h = B * H * Wc * (4 * int(want_disp) + 2 * int(want_disp16) + 4 * int(want_depth))
+        rates = torch.tensor([d2h * n / mine / 1e9], device="cuda", dtype=torch.float64)
+        allr = [torch.zeros_like(rates) for _ in range(world)]
+        if world > 1:
+            dist.all_gather(allr, rates)
+        else:
+            allr = [rates]
+        return {"value": world * B * n / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": int(2 * B * H * W),
+                "d2h_bytes_per_step": int(d2h), "steps": n,
+                "d2h_gbs_per_rank": [round(float(r.item()), 2) for r in allr]}
+
     ke = max(2, min(args.steps, 10))
-    t0 = time.perf_counter()
-    e2e_loop(ke)
-    torch.cuda.synchronize()
-    te = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_fps = world * B * ke / float(te.item())
-    same = bool(np.array_equal(sets[0][6], disp.cpu().numpy()) and np.array_equal(sets[1][6], sets[0][6]) and
-                np.array_equal(sets[2][6], sets[0][6]) and np.array_equal(sets[3][6], sets[0][6]))
+    e2e = e2e_leg(True, False, True, ke)
+    same = bool(all(np.array_equal(st["disp"], sets[0]["disp"]) for st in sets) and
+                np.array_equal(sets[0]["disp"], disp.cpu().numpy()) and np.array_equal(sets[0]["depth"], depth.cpu().numpy()))
+    e2e_depth = e2e_leg(False, False, True, ke)
+    same = same and bool(np.array_equal(sets[0]["depth"], depth.cpu().numpy()))
+    e2e_d16 = e2e_leg(False, True, True, ke)
+    same = same and bool(np.array_equal(sets[0]["disp16"].astype(np.float32) / np.float32(16), disp.cpu().numpy()))
+    e2e_fps = e2e["value"]
     # the blocking one-call form, for reference
     t0 = time.perf_counter()
     for i in range(ke):
-        eng.pipeline_batch(sets[0][4], sets[0][5], pp, dp, use_maps=True, out_disp=sets[0][6], out_depth=sets[0][7])
+        eng.pipeline_batch(sets[0]["L"], sets[0]["R"], pp, dp, use_maps=True, out_disp=sets[0]["disp"], out_depth=sets[0]["depth"])
     e2e_sync_fps = B * ke / (time.perf_counter() - t0)
+
+    # ---- the reference-shaped API: StereoDepthEstimatorVideo on BASELINE config #4 (1280x720 BGR frames, D = 128,
+    # default sgbm_3way, calibrated: rectify -> match -> post -> depth, depth maps yielded in frame order) ------------
+    video = None
+    if not args.no_video:
+        video = video_api_leg(local, rank, world, barrier, dist if world > 1 else None, torch)
+
+    # ---- parity of the TIMED workload (rank 0, outside every timed region): the first and the last frame of the batch
+    # this run just timed, against cv2 driven as depthlib drives it (C oracle if cv2 is missing) ------------------------
+    parity = None
+    if rank == 0 and not args.no_parity:
+        parity = parity_check(L, R, maps, cal, disp, depth, sets[0]["disp16"], [0, B - 1])
 
     # ---- CPU baseline beside it (rank 0, N=1 only): bounded sample of the same workload ----------
     cpu = None
@@ -374,6 +533,7 @@ def run_b200(args):
                 t = ref.run_frames(L, R, n)
             cpu = {"value": n / t, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
                    "sample": f"{n} frames of the same workload, frame-parallel on {ref.cores} threads, {ref.desc}"}
+            cpu.update(ref.as_shipped(L, R, 8))
         except Exception as exc:  # the baseline is a report, not a dependency of the GPU number
             cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
 
@@ -388,10 +548,13 @@ def run_b200(args):
                        "l2": "inputs larger than L2: C+S volumes are %.1f GB per step (L2 = 126 MB)" %
                              (2 * 2 * V * B / 1e9)},
             "mde_per_s": mde(fps),
-            "e2e": {"value": e2e_fps, "unit": UNIT, "h2d_bytes_per_step": int(2 * B * H * W),
-                    "d2h_bytes_per_step": int(2 * B * H * Wc * 4), "mde_per_s": mde(e2e_fps),
-                    "api": "b200s_pipeline_batch_submit/_wait, up to 4 chunks in flight (pinned host buffers)",
-                    "blocking_call_fps_rank0": e2e_sync_fps, "steps": ke, "matches_device_path": same},
+            "e2e": dict(e2e, mde_per_s=mde(e2e_fps), outputs="float32 disparity + float32 depth",
+                        api="b200s_pipeline_frames_submit / b200s_pipeline_batch_wait, up to 4 chunks in flight (page-locked host buffers)",
+                        blocking_call_fps_rank0=e2e_sync_fps, matches_device_path=same),
+            "e2e_depth_only": dict(e2e_depth, outputs="float32 depth (what the reference's video generator yields)"),
+            "e2e_disp16_depth": dict(e2e_d16, outputs="int16 x16 disparity + float32 depth"),
+            "e2e_video_api": video,
+            "parity_checked": parity,
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": kern[dominant],
@@ -407,6 +570,9 @@ def run_b200(args):
     if world > 1:
         dist.destroy_process_group()
     eng.close()
+    if rank == 0 and parity is not None and parity["mismatch"]:
+        print("bench.py: the timed workload does NOT match the oracle", file=sys.stderr)
+        return 3
     return 0
 
 
@@ -419,6 +585,8 @@ def main():
                     help="stereo pairs per step and GPU (0: the engine's preferred batch for this shape)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-video", action="store_true", help="skip the StereoDepthEstimatorVideo (config #4) leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the cv2 check of the timed batch")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -7,6 +7,7 @@
 
 #include <math.h>
 
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -70,6 +71,9 @@ struct B200sHandle {
     } slot[NSLOT];
     cudaStream_t s_in = nullptr, s_out = nullptr;
     unsigned next_ticket = 0;
+    // submit and wait may come from two host threads (a producer that uploads and enqueues, a consumer that waits and
+    // drains): the slot bookkeeping is guarded, the blocking event wait itself runs outside the lock
+    std::mutex slot_mu;
     bool debug_flow = false;  // materialise the full S volume with the generic per-direction kernels (stage taps)
     // geometry of the last sgbm call (for debug taps)
     Eff last_eff;
@@ -896,6 +900,7 @@ int b200s_pipeline_frames_submit(B200sHandle* h, const B200sFrameIO* io, const B
     int rc = frames_validate(h, io, pp, dp, &aH, &aW);
     if (rc) return rc;
     CUDA_TRY(h, cudaSetDevice(h->device));
+    std::lock_guard<std::mutex> lk(h->slot_mu);
     const int B = io->B, H = io->H, W = io->W, cn = io->channels;
     const int Wc = W - h->params.numDisparities;
     const size_t nin = (size_t)B * io->srcH * io->srcW * cn, nc = (size_t)B * H * Wc;
@@ -965,9 +970,13 @@ int b200s_pipeline_batch_wait(B200sHandle* h, int ticket) {
     if (!h) return B200S_E_INVALID;
     B200sHandle::Slot& sl = h->slot[(unsigned)ticket % B200sHandle::NSLOT];
     const unsigned tk = (unsigned)ticket;
-    if (!sl.busy || tk >= h->next_ticket || h->next_ticket - tk > B200sHandle::NSLOT) { h->set_error(B200S_E_STATE, "pipeline_batch_wait: ticket %d is not in flight", ticket); return B200S_E_STATE; }
+    {
+        std::lock_guard<std::mutex> lk(h->slot_mu);
+        if (!sl.busy || tk >= h->next_ticket || h->next_ticket - tk > B200sHandle::NSLOT) { h->set_error(B200S_E_STATE, "pipeline_batch_wait: ticket %d is not in flight", ticket); return B200S_E_STATE; }
+    }
     CUDA_TRY(h, cudaSetDevice(h->device));
     CUDA_TRY(h, cudaEventSynchronize(sl.out_done));   // on failure the slot stays busy: its copies may still be pending
+    std::lock_guard<std::mutex> lk(h->slot_mu);
     sl.busy = false;
     return check_launch(h, "pipeline_batch");
 }

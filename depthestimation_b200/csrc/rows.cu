@@ -194,8 +194,13 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         for (int q = 0; q < NR / 4; q++) {
             const uint4 t = rec[q * LW];
             if (nosat) {   // the sum of all paths provably stays below 32768: plain adds on the packed halves
+#if SGM_FMA_ADDS
+                Sc[4 * q] = __vadd2(__vadd2(Sc[4 * q], Lr[4 * q]), t.x); Sc[4 * q + 1] = __vadd2(__vadd2(Sc[4 * q + 1], Lr[4 * q + 1]), t.y);
+                Sc[4 * q + 2] = __vadd2(__vadd2(Sc[4 * q + 2], Lr[4 * q + 2]), t.z); Sc[4 * q + 3] = __vadd2(__vadd2(Sc[4 * q + 3], Lr[4 * q + 3]), t.w);
+#else
                 Sc[4 * q] += Lr[4 * q] + t.x; Sc[4 * q + 1] += Lr[4 * q + 1] + t.y;
                 Sc[4 * q + 2] += Lr[4 * q + 2] + t.z; Sc[4 * q + 3] += Lr[4 * q + 3] + t.w;
+#endif
             } else {
                 Sc[4 * q] = uaddmin2(uaddmin2(Sc[4 * q], Lr[4 * q], 0x7fff7fffu), t.x, 0x7fff7fffu);
                 Sc[4 * q + 1] = uaddmin2(uaddmin2(Sc[4 * q + 1], Lr[4 * q + 1], 0x7fff7fffu), t.y, 0x7fff7fffu);

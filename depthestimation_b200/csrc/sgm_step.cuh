@@ -9,6 +9,10 @@
 #pragma once
 #include "common.cuh"
 
+#ifndef SGM_FMA_ADDS
+#define SGM_FMA_ADDS 1
+#endif
+
 // ---- 16-byte global loads / stores of a lane's NR packed registers --------------------------------
 template <int NR>
 __device__ __forceinline__ void load_regs(const uint16_t* p, unsigned (&r)[NR]) {
@@ -78,13 +82,23 @@ __device__ __forceinline__ unsigned sgm_step_core(unsigned (&L)[NR], const unsig
     const unsigned mm = pk2(m);
     const unsigned dmp = pk2(m + P2mP1);
     unsigned Ln[NR];
+#if SGM_FMA_ADDS
+    const unsigned nmm = pk2(0x10000u - m);                                // -m per half (wraps inside the half)
+#endif
 #pragma unroll
     for (int j = 0; j < NR; j++) {
         unsigned bq = shift_pair(j == 0 ? up : L[j - 1], L[j]);            // (L[d-1], L[d])
         unsigned cn = shift_pair(L[j], j == NR - 1 ? dn : L[j + 1]);       // (L[d+1], L[d+2])
         unsigned tt = umin3_2(bq, cn, dmp);
         tt = uaddmin2(tt, P1P1, L[j]);
-        Ln[j] = PAD ? umax2(Cq[j] + tt - mm, pm[j]) : (Cq[j] + tt - mm);
+#if SGM_FMA_ADDS
+        // C + (tt - m) as two VIADD.16x2: they issue on the FMA pipe, which is idle, while the one IADD3 this replaces
+        // competes with the min / max / permute instructions for the half-rate ALU pipe (tools/ubench/pipes2.cu)
+        const unsigned ln = __vadd2(__vadd2(tt, nmm), Cq[j]);
+#else
+        const unsigned ln = Cq[j] + tt - mm;
+#endif
+        Ln[j] = PAD ? umax2(ln, pm[j]) : ln;
     }
     if (PAD && quirk) {
         // d0 is a multiple of 8, so it sits in register 0 or (NR == 8) register 4 of lane d0 / (2 NR)

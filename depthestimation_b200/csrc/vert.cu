@@ -270,7 +270,11 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
                         unsigned So[NR];
 #pragma unroll
                         for (int j = 0; j < NR; j++)
+#if SGM_FMA_ADDS
+                            So[j] = a.nosat ? __vadd2(__vadd2(LA[j], LU[j]), LB[j]) : uaddmin2(uaddmin2(LA[j], LU[j], 0x7fff7fffu), LB[j], 0x7fff7fffu);
+#else
                             So[j] = a.nosat ? LA[j] + LU[j] + LB[j] : uaddmin2(uaddmin2(LA[j], LU[j], 0x7fff7fffu), LB[j], 0x7fff7fffu);
+#endif
                         if (a.accumulate) {
                             unsigned Sold[NR];
                             load_regs<NR>(sp, Sold);

@@ -12,6 +12,7 @@ a generator that yields one depth map per stereo frame, with threaded capture, `
 """
 from __future__ import annotations
 
+import threading
 import time
 import warnings
 from concurrent.futures import ThreadPoolExecutor
@@ -20,18 +21,26 @@ from typing import Optional, Sequence
 import numpy as np
 
 from ..sharding import ThreadedSharder
-from .input import stereo_stream
+from .input import _area_downscale, stereo_stream
 from .stereo_core import StereoCore
 from .threaded_stereo import ThreadedStereoCapture
 from .visualizations import visualize_depth_live, visualize_depth_live_gray
 
 
+def _is_frame_sequence(src) -> bool:
+    """Neither a path nor a camera index but an iterable of frames."""
+    import os
+    return not isinstance(src, (str, bytes, int, os.PathLike)) and hasattr(src, "__iter__")
+
+
 class _FrameWorker:
     """One GPU of the sharded generator: engine + maps + a ring of page-locked chunk buffers (sharding.ThreadedSharder's
-    submit / wait protocol)."""
+    submit / wait protocol). Two host threads per GPU: a feeder (copies the chunk's frames into page-locked memory and
+    enqueues upload + kernels + download) and the sharder's worker thread (waits for a chunk, copies the depth maps into
+    an array the caller owns); the frame copies themselves fan out over a small pool (numpy releases the GIL)."""
     max_inflight = 3
 
-    def __init__(self, device, matcher_kw, maps, pp, dp, use_maps, size, area, copy_threads=4):
+    def __init__(self, device, matcher_kw, maps, pp, dp, use_maps, size, area, cap=1, copy_threads=8):
         from ..engine import StereoEngine
         self.eng = StereoEngine(device, **matcher_kw)
         if maps is not None:
@@ -40,41 +49,48 @@ class _FrameWorker:
         self.want_depth = bool(dp.enabled)
         self._free = []          # page-locked (L, R, out) triples of the current chunk geometry
         self._geom = None
+        self._cap = max(1, int(cap))   # frames per buffer: the full chunk, also for the shorter first and last chunks
+        self._lock = threading.Lock()
         self._pool = ThreadPoolExecutor(max(1, int(copy_threads)))
+        self._feeder = ThreadPoolExecutor(1)
 
     def _buffers(self, B, shape):
         from ..engine import pinned_empty
-        geom = (B, tuple(shape))
-        if self._geom is None or B > self._geom[0] or tuple(shape) != self._geom[1]:
-            self._free, self._geom = [], geom          # buffers in flight stay alive through their tokens
-        if not self._free:
-            cap = self._geom[0]
-            aW, aH = self.area if self.area is not None else (shape[1], shape[0])
-            W, H = self.size if self.size is not None else (aW, aH)
-            Wc = W - self.eng.params.numDisparities
-            out = pinned_empty((cap, H, Wc), np.float32)
-            return pinned_empty((cap,) + tuple(shape), np.uint8), pinned_empty((cap,) + tuple(shape), np.uint8), out
-        return self._free.pop()
+        with self._lock:
+            if self._geom is None or B > self._geom[0] or tuple(shape) != self._geom[1]:
+                self._free, self._geom = [], (max(B, self._cap), tuple(shape))   # buffers in flight stay alive through their tokens
+            geom = self._geom
+            if self._free:
+                return self._free.pop(), geom
+        aW, aH = self.area if self.area is not None else (shape[1], shape[0])
+        W, H = self.size if self.size is not None else (aW, aH)
+        Wc = W - self.eng.params.numDisparities
+        cap = geom[0]
+        return (pinned_empty((cap,) + tuple(shape), np.uint8), pinned_empty((cap,) + tuple(shape), np.uint8),
+                pinned_empty((cap, H, Wc), np.float32)), geom
 
-    def submit(self, Ls, Rs):
+    def _feed(self, Ls, Rs):
         B, shape = len(Ls), Ls[0].shape
         if any(f.shape != shape or f.dtype != np.uint8 for f in Ls) or any(f.shape != shape or f.dtype != np.uint8 for f in Rs):
             raise ValueError("sharded video path: every frame of a stream must be uint8 and of one size")
-        bufs = self._buffers(B, shape)
+        bufs, geom = self._buffers(B, shape)
         bL, bR, out = bufs
 
         def put(k):
             np.copyto(bL[k], Ls[k]); np.copyto(bR[k], Rs[k])
-        list(self._pool.map(put, range(B)))            # numpy releases the GIL while copying
+        list(self._pool.map(put, range(B)))
         want_depth = self.want_depth
         tk = self.eng.pipeline_frames_submit(
             bL[:B], bR[:B], self.pp, self.dp, size=self.size, area=self.area, use_maps=self.use_maps,
             want_disp=not want_depth, want_depth=want_depth,
             out_disp=None if want_depth else out[:B], out_depth=out[:B] if want_depth else None)
-        return tk, bufs, B, self._geom
+        return tk, bufs, B, geom
+
+    def submit(self, Ls, Rs):
+        return self._feeder.submit(self._feed, Ls, Rs)          # chunks are fed in submission order
 
     def wait(self, token):
-        tk, bufs, B, geom = token
+        tk, bufs, B, geom = token.result()
         self.eng.pipeline_batch_wait(tk)
         src = bufs[2]
         res = np.empty((B,) + src.shape[1:], np.float32)      # the caller owns what the generator yields
@@ -82,8 +98,9 @@ class _FrameWorker:
         def get(k):
             np.copyto(res[k], src[k])
         list(self._pool.map(get, range(B)))
-        if geom == self._geom:
-            self._free.append(bufs)
+        with self._lock:
+            if geom == self._geom:
+                self._free.append(bufs)
         return (None, res) if self.want_depth else (res, None)
 
 
@@ -114,6 +131,11 @@ class StereoDepthEstimatorVideo:
     # -- frame sources ----------------------------------------------------------------------------
     def _frames(self, downscale_factor=None):
         f = self.downscale_factor if downscale_factor is None else downscale_factor
+        if _is_frame_sequence(self.left_source) and _is_frame_sequence(self.right_source):
+            # in-memory sources (new): two iterables of frames, e.g. lists of HxWx3 arrays from another decoder
+            for left, right in zip(self.left_source, self.right_source):
+                yield _area_downscale(left, f, self.core.device), _area_downscale(right, f, self.core.device)
+            return
         if self.use_threading:
             cap = ThreadedStereoCapture(self.left_source, self.right_source, downscale_factor=f,
                                         drop_frames=self.drop_frames, device=self.core.device)
@@ -189,15 +211,33 @@ class StereoDepthEstimatorVideo:
         if chunk is None:
             chunk = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
 
+        # workers (engine handle with its device scratch, uploaded maps, page-locked chunk buffers) survive between
+        # calls of this generator as long as the configuration is the same
+        key = (tuple(sorted((k, str(v)) for k, v in kw.items())), id(maps), size, area, bytes(pp), bytes(dp), chunk)
+        if getattr(self, "_worker_key", None) != key:
+            self._worker_key, self._worker_pool = key, {}
+        pool, used, lock = self._worker_pool, [], threading.Lock()
+
         def make_worker(dev):
-            return _FrameWorker(dev, kw, maps, pp, dp, use_maps, size, area)
+            with lock:
+                w = pool.get(dev, []).pop() if pool.get(dev) else None
+            if w is None:
+                w = _FrameWorker(dev, kw, maps, pp, dp, use_maps, size, area, cap=chunk)
+            with lock:
+                used.append((dev, w))
+            return w
 
         def pairs():
             yield first
             yield from frames
 
         t0 = time.time()
-        for _disp, depth_m in ThreadedSharder(self.devices, make_worker, chunk, max_inflight=4).run(pairs()):
-            yield depth_m
-            self._show(depth_m)
-            t0 = self._pace(t0)
+        try:
+            for _disp, depth_m in ThreadedSharder(self.devices, make_worker, chunk, max_inflight=4, ramp=True).run(pairs()):
+                yield depth_m
+                self._show(depth_m)
+                t0 = self._pace(t0)
+        finally:
+            with lock:
+                for dev, w in used:
+                    pool.setdefault(dev, []).append(w)

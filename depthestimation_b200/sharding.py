@@ -60,11 +60,14 @@ class ThreadedSharder:
     """
 
     def __init__(self, devices: Sequence[int], make_worker: Callable[[int], Callable], chunk: int = 8,
-                 max_inflight: int = 4):
+                 max_inflight: int = 4, ramp: bool = False):
         if not devices:
             raise ValueError("ThreadedSharder needs at least one device")
         self.devices, self.make_worker, self.chunk = list(devices), make_worker, max(1, int(chunk))
         self.max_inflight = max(1, int(max_inflight))
+        # ramp: the first chunk of every GPU is a quarter, the second a half of `chunk`, so the GPUs start after a
+        # quarter of the fill time of a full chunk (a 240-frame job is only three full chunks of 78)
+        self.ramp = bool(ramp)
 
     def run(self, pairs: Iterable[Tuple[np.ndarray, np.ndarray]]) -> Iterator[Tuple[np.ndarray, Optional[np.ndarray]]]:
         G = len(self.devices)
@@ -141,17 +144,20 @@ class ThreadedSharder:
         try:
             while True:
                 while not exhausted and submitted - emitted < self.max_inflight * G:
+                    want = self.chunk
+                    if self.ramp and submitted < 2 * G:
+                        want = max(1, self.chunk // (4 if submitted < G else 2))
                     Ls, Rs = [], []
                     for l, r in it:
                         Ls.append(l); Rs.append(r)
-                        if len(Ls) == self.chunk:
+                        if len(Ls) == want:
                             break
                     if not Ls:
                         exhausted = True
                         break
                     work.put((submitted, Ls, Rs))
                     submitted += 1
-                    if len(Ls) < self.chunk:
+                    if len(Ls) < want:
                         exhausted = True
                 if emitted == submitted and exhausted:
                     break

@@ -195,7 +195,9 @@ int b200s_pipeline_batch_wait(B200sHandle* h, int ticket);
  *   L, R: B dense frames of srcH x srcW x channels uint8 (channels 1 or 3). areaH/areaW 0 = no downscale.
  *   Outputs (host, each dense B x H x (W - numDisparities), each may be NULL): disp float32; disp16 int16 = disparity x 16
  *   (exact: every post stage selects among the matcher's fixed-point values, 2 B/px instead of 4); depth float32.
- * Asynchronous like b200s_pipeline_batch_submit (same slots, same tickets, wait with b200s_pipeline_batch_wait);
+ * Asynchronous like b200s_pipeline_batch_submit (same slots, same tickets, wait with b200s_pipeline_batch_wait); the
+ * submit calls and b200s_pipeline_batch_wait may be issued from two different host threads of one handle (a producer
+ * and a consumer; every other entry point stays one-thread-per-handle);
  * b200s_pipeline_frames = submit + wait. */
 typedef struct B200sFrameIO {
     const uint8_t* L;
