@@ -72,6 +72,7 @@ SYMBOLS = {
     "b200s_pipeline_frames_submit": (C.c_int, [_H, C.POINTER(B200sFrameIO), _PP, _DP, _IP]),
     "b200s_pipeline_frames": (C.c_int, [_H, C.POINTER(B200sFrameIO), _PP, _DP]),
     "b200s_last_flow": (C.c_int, [_H]),
+    "b200s_build_maps": (C.c_int, [_H, _VP, _VP, C.c_int, _VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "b200s_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "b200s_host_free": (C.c_int, [C.c_void_p]),
     "b200s_filter_speckles_noalloc": (C.c_int, [_VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _VP,

@@ -998,6 +998,66 @@ int b200s_pipeline_frames(B200sHandle* h, const B200sFrameIO* io, const B200sPos
 
 int b200s_last_flow(const B200sHandle* h) { return h ? h->last_flow : 0; }
 
+// 3x3 inverse the way the reference's dependency inverts small matrices (cofactors over the determinant, double)
+static bool inv3(const double* a, double* o) {
+    const double d = a[0] * (a[4] * a[8] - a[5] * a[7]) - a[1] * (a[3] * a[8] - a[5] * a[6]) + a[2] * (a[3] * a[7] - a[4] * a[6]);
+    if (d == 0.0) return false;
+    const double r = 1.0 / d;
+    o[0] = (a[4] * a[8] - a[5] * a[7]) * r; o[1] = (a[2] * a[7] - a[1] * a[8]) * r; o[2] = (a[1] * a[5] - a[2] * a[4]) * r;
+    o[3] = (a[5] * a[6] - a[3] * a[8]) * r; o[4] = (a[0] * a[8] - a[2] * a[6]) * r; o[5] = (a[2] * a[3] - a[0] * a[5]) * r;
+    o[6] = (a[3] * a[7] - a[4] * a[6]) * r; o[7] = (a[1] * a[6] - a[0] * a[7]) * r; o[8] = (a[0] * a[4] - a[1] * a[3]) * r;
+    return true;
+}
+
+int b200s_build_maps(B200sHandle* h, const double* K, const double* dist, int ndist, const double* R, const double* P,
+                     int H, int W, float* map1, float* map2) {
+    if (!h) return B200S_E_INVALID;
+    if (!K || !map1 || !map2 || H <= 0 || W <= 0 || ndist < 0 || (ndist > 0 && !dist) ||
+        !(ndist == 0 || ndist == 4 || ndist == 5 || ndist == 8 || ndist == 12 || ndist == 14)) {
+        h->set_error(B200S_E_INVALID, "build_maps: bad arguments (distortion vectors of 0, 4, 5, 8, 12 or 14 coefficients)");
+        return B200S_E_INVALID;
+    }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    double q[34];
+    const double I3[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    const double* Rm = R ? R : I3;
+    double A[9];   // new camera matrix (first three columns of P, or K itself) times R
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) {
+            double acc = 0.0;
+            for (int k = 0; k < 3; k++) acc += (P ? P[r * 4 + k] : K[r * 3 + k]) * Rm[k * 3 + c];
+            A[r * 3 + c] = acc;
+        }
+    if (!inv3(A, q)) { h->set_error(B200S_E_INVALID, "build_maps: P[:, :3] * R is singular"); return B200S_E_INVALID; }
+    q[9] = K[0]; q[10] = K[4]; q[11] = K[2]; q[12] = K[5];
+    double d[14] = {0};
+    for (int i = 0; i < ndist; i++) d[i] = dist[i];
+    q[13] = d[0]; q[14] = d[1]; q[15] = d[2]; q[16] = d[3]; q[17] = d[4]; q[18] = d[5]; q[19] = d[6]; q[20] = d[7];
+    q[21] = d[8]; q[22] = d[9]; q[23] = d[10]; q[24] = d[11];
+    // tilt (tauX, tauY): projection of the tilted sensor, identity when both are zero
+    double* T = q + 25;
+    for (int i = 0; i < 9; i++) T[i] = I3[i];
+    if (d[12] != 0.0 || d[13] != 0.0) {
+        const double cx = cos(d[12]), sx = sin(d[12]), cy = cos(d[13]), sy = sin(d[13]);
+        const double RX[9] = {1, 0, 0, 0, cx, sx, 0, -sx, cx}, RY[9] = {cy, 0, -sy, 0, 1, 0, sy, 0, cy};
+        double RXY[9];
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) { double acc = 0.0; for (int k = 0; k < 3; k++) acc += RY[r * 3 + k] * RX[k * 3 + c]; RXY[r * 3 + c] = acc; }
+        const double PZ[9] = {RXY[8], 0, -RXY[2], 0, RXY[8], -RXY[5], 0, 0, 1};
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) { double acc = 0.0; for (int k = 0; k < 3; k++) acc += PZ[r * 3 + k] * RXY[k * 3 + c]; T[r * 3 + c] = acc; }
+    }
+    const size_t n = (size_t)H * W;
+    CUDA_TRY(h, h->f0.ensure(n * sizeof(float)));
+    CUDA_TRY(h, h->f1.ensure(n * sizeof(float)));
+    launch_init_undistort_rectify_map(q, H, W, h->f0.as<float>(), h->f1.as<float>(), h->stream);
+    h->launches++;
+    CUDA_TRY(h, cudaMemcpyAsync(map1, h->f0.p, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(map2, h->f1.p, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+    return check_launch(h, "build_maps");
+}
+
 int b200s_host_alloc(size_t bytes, void** out) {
     if (!out || bytes == 0) return B200S_E_INVALID;
     *out = nullptr;

@@ -138,4 +138,6 @@ void launch_resize_area_int(const uint8_t* src, int B, int sH, int sW, int cn, i
                             cudaStream_t st);
 void launch_resize_area_tab(const uint8_t* src, int B, int sH, int sW, int cn, const int* xo, const int2* xt, const int* yo,
                             const int2* yt, uint8_t* dst, int dH, int dW, cudaStream_t st);
+// cv2.initUndistortRectifyMap: params = MapParams of imgops.cu as 34 doubles (iR, fx, fy, u0, v0, k1 k2 p1 p2 k3 k4 k5 k6 s1..s4, tilt)
+void launch_init_undistort_rectify_map(const double* params34, int H, int W, float* m1, float* m2, cudaStream_t st);
 void launch_debug_volume(const uint16_t* V, int H, int W1, int Dp, int D, int add, int16_t* out, cudaStream_t st);

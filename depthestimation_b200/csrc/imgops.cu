@@ -9,6 +9,8 @@
 //   resize lin    cv2.resize(img, size, INTER_LINEAR) (size fix-up)  depthlib/rectify.py:92-105
 //   fill nearest  fill_holes(method='nearest')                       depthlib/postprocess.py:106-116
 // The float chain uses explicit round-to-nearest intrinsics (no FMA contraction, no fast math).
+#include <string.h>
+
 #include "common.cuh"
 
 // ---- B.1 remap: fixed-point bilinear, 5 fractional bits, constant-0 border ---------------------
@@ -414,4 +416,41 @@ void launch_resize_linear(const uint8_t* src, int B, int sH, int sW, int cn, con
     const size_t n = (size_t)dH * dW * cn;
     dim3 grid((unsigned)((n + 1023) / 1024), B);
     k_resize_linear<<<grid, 256, 0, st>>>(src, sH, sW, cn, tx, ty, dst, dH, dW);
+}
+
+// ---- cv2.initUndistortRectifyMap(K, dist, R, P, size, CV_32FC1) (depthlib/rectify.py:68-73, 229-234) --------------------
+// Per pixel, in double precision with the operation order of the reference's dependency (no FMA contraction): the ray
+// of rectified pixel (j, i) through iR = (P[:, :3] R)^-1, the distortion model (k1..k6, p1, p2, s1..s4, tilt), the
+// camera matrix; float32 maps out. p = {iR[9], fx, fy, u0, v0, k1, k2, p1, p2, k3, k4, k5, k6, s1, s2, s3, s4, tilt[9]}.
+struct MapParams { double ir[9], fx, fy, u0, v0, k1, k2, p1, p2, k3, k4, k5, k6, s1, s2, s3, s4, tilt[9]; };
+#define DM(a, b) __dmul_rn(a, b)
+#define DA(a, b) __dadd_rn(a, b)
+__global__ void __launch_bounds__(256) k_init_undistort_rectify_map(const MapParams p, int H, int W, float* __restrict__ m1,
+                                                                    float* __restrict__ m2) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)H * W) return;
+    const double i = (double)(int)(idx / W), j = (double)(int)(idx % W);
+    const double _x = DA(DA(DM(i, p.ir[1]), p.ir[2]), DM(j, p.ir[0]));
+    const double _y = DA(DA(DM(i, p.ir[4]), p.ir[5]), DM(j, p.ir[3]));
+    const double _w = DA(DA(DM(i, p.ir[7]), p.ir[8]), DM(j, p.ir[6]));
+    const double w = __ddiv_rn(1.0, _w), x = DM(_x, w), y = DM(_y, w);
+    const double x2 = DM(x, x), y2 = DM(y, y), r2 = DA(x2, y2), _2xy = DM(DM(2.0, x), y);
+    const double num = DA(1.0, DM(DA(DM(DA(DM(p.k3, r2), p.k2), r2), p.k1), r2));
+    const double den = DA(1.0, DM(DA(DM(DA(DM(p.k6, r2), p.k5), r2), p.k4), r2));
+    const double kr = __ddiv_rn(num, den);
+    const double xd = DA(DA(DA(DA(DM(x, kr), DM(p.p1, _2xy)), DM(p.p2, DA(r2, DM(2.0, x2)))), DM(p.s1, r2)), DM(DM(p.s2, r2), r2));
+    const double yd = DA(DA(DA(DA(DM(y, kr), DM(p.p1, DA(r2, DM(2.0, y2)))), DM(p.p2, _2xy)), DM(p.s3, r2)), DM(DM(p.s4, r2), r2));
+    const double t0 = DA(DA(DM(p.tilt[0], xd), DM(p.tilt[1], yd)), p.tilt[2]);
+    const double t1 = DA(DA(DM(p.tilt[3], xd), DM(p.tilt[4], yd)), p.tilt[5]);
+    const double t2 = DA(DA(DM(p.tilt[6], xd), DM(p.tilt[7], yd)), p.tilt[8]);
+    const double inv = (t2 != 0.0) ? __ddiv_rn(1.0, t2) : 1.0;
+    m1[idx] = (float)DA(DM(DM(p.fx, inv), t0), p.u0);
+    m2[idx] = (float)DA(DM(DM(p.fy, inv), t1), p.v0);
+}
+void launch_init_undistort_rectify_map(const double* params34, int H, int W, float* m1, float* m2, cudaStream_t st) {
+    MapParams p;
+    static_assert(sizeof(MapParams) == 34 * sizeof(double), "parameter block");
+    memcpy(&p, params34, sizeof(p));
+    const size_t n = (size_t)H * W;
+    k_init_undistort_rectify_map<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(p, H, W, m1, m2);
 }

@@ -188,6 +188,8 @@ class StereoDepthEstimatorVideo:
         use_maps = core._calibration()
         maps = None
         if use_maps:
+            if core._rect_cache.engine is None:
+                core._rect_cache.engine = core.sgbm.engine
             maps = core._rect_cache.get_maps(p['cam_matrix_L'], p['cam_matrix_R'], p['baseline'], p['image_width'],
                                              p['image_height'], p.get('dist_coeff_L'), p.get('dist_coeff_R'),
                                              p.get('rotation'), p.get('translation'), 1.0)

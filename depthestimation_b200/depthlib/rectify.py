@@ -2,9 +2,9 @@
 
 Per frame (hot path): gray conversion and the two bilinear remaps run on the GPU (C ABI
 ``b200s_bgr2gray`` / ``b200s_remap_u8``; reference: rectify.py:108-119, 185-186).
-Once per calibration (cold): the maps themselves come from host ``cv2.stereoRectify`` +
-``cv2.initUndistortRectifyMap`` exactly as rectify.py:63-73 does (double-precision camera math,
-out of the hot path — SURVEY.md §2 row 2). The size fix-up (rectify.py:92-105) runs on the GPU too (``b200s_resize_linear_u8``).
+Once per calibration (or per call when ``rectify_images`` gets no cache, rectify.py:209-235): ``cv2.stereoRectify`` (3x3
+algebra) on the host, then the per-pixel ``cv2.initUndistortRectifyMap`` of rectify.py:68-73 on the GPU in double
+precision (``b200s_build_maps``). The size fix-up (rectify.py:92-105) runs on the GPU too (``b200s_resize_linear_u8``).
 """
 from __future__ import annotations
 
@@ -41,9 +41,10 @@ class RectificationCache:
     """Keeps the four CV_32FC1 maps of the last calibration (reference: rectify.py:14-87): same key,
     same dict object returned while the calibration is unchanged."""
 
-    def __init__(self):
+    def __init__(self, engine=None):
         self._cache_key: Optional[tuple] = None
         self._maps: Optional[Dict[str, np.ndarray]] = None
+        self.engine = engine     # StereoEngine that generates the maps (None: the calling thread's engine on device 0)
 
     def _make_key(self, cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
                   dist_coeff_L, dist_coeff_R, rotation, translation, alpha) -> tuple:
@@ -58,7 +59,7 @@ class RectificationCache:
         if self._cache_key == key and self._maps is not None:
             return self._maps
         self._maps = _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
-                                 dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
+                                 dist_coeff_L, dist_coeff_R, rotation, translation, alpha, getattr(self, "engine", None))
         self._cache_key = key
         return self._maps
 
@@ -71,9 +72,10 @@ _global_cache = RectificationCache()
 
 
 def _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height, dist_coeff_L, dist_coeff_R,
-                rotation, translation, alpha) -> Dict[str, np.ndarray]:
+                rotation, translation, alpha, engine=None) -> Dict[str, np.ndarray]:
     """cv2.stereoRectify(CALIB_ZERO_DISPARITY) + 2x initUndistortRectifyMap(CV_32FC1); defaults as the
-    reference: zero distortion, R = I, T = [-baseline, 0, 0] (rectify.py:52-73)."""
+    reference: zero distortion, R = I, T = [-baseline, 0, 0] (rectify.py:52-73). stereoRectify is 3x3 algebra, once per
+    calibration, and stays host cv2; the per-pixel part, initUndistortRectifyMap, runs on the GPU (b200s_build_maps)."""
     cv2 = _cv2()
     K_L = np.asarray(cam_matrix_L, dtype=np.float64)
     K_R = np.asarray(cam_matrix_R, dtype=np.float64)
@@ -86,8 +88,9 @@ def _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
          else np.array([-baseline, 0.0, 0.0], dtype=np.float64))
     rect_L, rect_R, proj_L, proj_R, _Q, _roi_L, _roi_R = cv2.stereoRectify(
         K_L, d_L, K_R, d_R, size, R, T, flags=cv2.CALIB_ZERO_DISPARITY, alpha=alpha)
-    map1_L, map2_L = cv2.initUndistortRectifyMap(K_L, d_L, rect_L, proj_L, size, cv2.CV_32FC1)
-    map1_R, map2_R = cv2.initUndistortRectifyMap(K_R, d_R, rect_R, proj_R, size, cv2.CV_32FC1)
+    eng = _engine(engine)
+    map1_L, map2_L = eng.build_maps(K_L, d_L, rect_L, proj_L, size)
+    map1_R, map2_R = eng.build_maps(K_R, d_R, rect_R, proj_R, size)
     return {'map1_L': map1_L, 'map2_L': map2_L, 'map1_R': map1_R, 'map2_R': map2_R}
 
 
@@ -126,11 +129,13 @@ def rectify_images(img_L: np.ndarray, img_R: np.ndarray, cam_matrix_L: np.ndarra
     """Rectify a stereo pair; returns two uint8 gray images of the calibration size (rectify.py:122-237).
     With ``cache`` the maps are reused across frames; without it they are rebuilt per call, as upstream."""
     if cache is not None:
+        if engine is not None and getattr(cache, "engine", None) is None:
+            cache.engine = engine           # the maps are generated on the caller's device
         maps = cache.get_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
                               dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
     else:
         maps = _build_maps(cam_matrix_L, cam_matrix_R, baseline, image_width, image_height,
-                           dist_coeff_L, dist_coeff_R, rotation, translation, alpha)
+                           dist_coeff_L, dist_coeff_R, rotation, translation, alpha, engine)
     size = (image_width, image_height)
     eng = _engine(engine)
     img_L = _ensure_image_size(img_L, size, eng)

@@ -199,6 +199,8 @@ class StereoCore:
         use_maps = self._calibration()
         left, right = left_source, right_source
         if use_maps:
+            if self._rect_cache.engine is None:
+                self._rect_cache.engine = eng
             maps = self._rect_cache.get_maps(p['cam_matrix_L'], p['cam_matrix_R'], p['baseline'], p['image_width'],
                                              p['image_height'], p.get('dist_coeff_L'), p.get('dist_coeff_R'),
                                              p.get('rotation'), p.get('translation'), 1.0)

@@ -184,6 +184,23 @@ class StereoEngine:
         self._check(self._lib.b200s_set_maps(self._h, *[m.ctypes.data for m in ms], H, W), "b200s_set_maps")
         self.maps_shape = (H, W)
 
+    def build_maps(self, K, dist, R, P, size):
+        """== cv2.initUndistortRectifyMap(K, dist, R, P, size, cv2.CV_32FC1) (rectify.py:68-73): (map1, map2) float32."""
+        K = np.ascontiguousarray(K, dtype=np.float64).reshape(3, 3)
+        d = np.zeros(0) if dist is None else np.ascontiguousarray(dist, dtype=np.float64).ravel()
+        Rm = None if R is None else np.ascontiguousarray(R, dtype=np.float64).reshape(3, 3)
+        Pm = None if P is None else np.ascontiguousarray(P, dtype=np.float64)
+        if Pm is not None and Pm.shape == (3, 3):
+            Pm = np.ascontiguousarray(np.hstack([Pm, np.zeros((3, 1))]))
+        if Pm is not None and Pm.shape != (3, 4):
+            raise ValueError("build_maps: P must be 3x3 or 3x4")
+        W, H = int(size[0]), int(size[1])
+        m1, m2 = np.empty((H, W), np.float32), np.empty((H, W), np.float32)
+        self._check(self._lib.b200s_build_maps(
+            self._h, K.ctypes.data, d.ctypes.data if d.size else None, int(d.size), Rm.ctypes.data if Rm is not None else None,
+            Pm.ctypes.data if Pm is not None else None, H, W, m1.ctypes.data, m2.ctypes.data), "b200s_build_maps")
+        return m1, m2
+
     def bgr2gray(self, img):
         img = np.ascontiguousarray(img, dtype=np.uint8)
         if img.ndim != 3 or img.shape[2] != 3:

@@ -109,6 +109,15 @@ int b200s_sync(B200sHandle* h);
 int b200s_set_maps(B200sHandle* h, const float* map1_L, const float* map2_L,
                    const float* map1_R, const float* map2_R, int H, int W);
 
+/* cv2.initUndistortRectifyMap(K, dist, R, P, (W, H), cv2.CV_32FC1) at depthlib/rectify.py:68-73 (cached) and :229-234 (rebuilt
+ * on every call when rectify_images gets no cache): the two float32 maps of ONE camera, computed per pixel in double
+ * precision on the GPU, bit-exact. K: 3x3 camera matrix, dist: 0 / 4 / 5 / 8 / 12 / 14 distortion coefficients (k1 k2 p1 p2
+ * k3 k4 k5 k6 s1 s2 s3 s4 tauX tauY), R: 3x3 rectification rotation (NULL = identity), P: 3x4 new projection matrix
+ * (NULL = K), all row-major doubles; map1 / map2: dense H x W float32 (host). cv2.stereoRectify (3x3 algebra, once per
+ * calibration, :63-66) stays on the host. */
+int b200s_build_maps(B200sHandle* h, const double* K, const double* dist, int ndist, const double* R, const double* P,
+                     int H, int W, float* map1, float* map2);
+
 /* ---- host-buffer entry points (one pair) ------------------------------------------------ */
 
 /* cv2.cvtColor(img, COLOR_BGR2GRAY) at depthlib/rectify.py:116, stereo_core.py:157-159. */

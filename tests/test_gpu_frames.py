@@ -297,3 +297,45 @@ def test_no_silent_host_fallbacks():
     with pytest.warns(RuntimeWarning):
         with pytest.raises(ValueError, match="uint8"):
             _ensure_image_size(np.zeros((8, 8), np.float32), (16, 16))
+
+
+def test_build_maps_matches_oracle_and_cv2(engine):
+    """b200s_build_maps (cv2.initUndistortRectifyMap on the GPU, double precision, no contraction): bit-exact against the
+    numpy restatement for every calibration model, and against cv2 itself up to the documented one-ulp flips of its
+    AVX2 path (at most one value per map pair; none on the synthetic and the rotated / translated rig)."""
+    cv2 = pytest.importorskip("cv2")
+    from oracle import maps as om
+    cases = om.calibration_cases()
+    cal = make_calibration(375, 1242)
+    cases.append(("kitti", cal["cam_matrix_L"], cal["dist_coeff_L"], cal["cam_matrix_R"], cal["dist_coeff_R"], (1242, 375),
+                  np.eye(3), np.array([-0.54, 0.0, 0.0])))
+    for name, KL, dL, KR, dR, size, R, T in cases:
+        for alpha in (0.0, 1.0):
+            rL, rR, pL, pR, *_ = cv2.stereoRectify(KL, dL, KR, dR, size, R, T, flags=cv2.CALIB_ZERO_DISPARITY, alpha=alpha)
+            for K, d, r, p in ((KL, dL, rL, pL), (KR, dR, rR, pR)):
+                got = engine.build_maps(K, d, r, p, size)
+                ref = om.init_undistort_rectify_map(K, d, r, p, size)
+                want = cv2.initUndistortRectifyMap(K, d, r, p, size, cv2.CV_32FC1)
+                assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]), name
+                bad = sum(int((g != w).sum()) for g, w in zip(got, want))
+                assert bad <= (0 if name in ("synthetic", "rotated", "kitti") else 1), (name, alpha, bad)
+    # P = None (new camera matrix = K), R = None, no distortion: the identity map
+    K = cases[0][1]
+    m1, m2 = engine.build_maps(K, None, None, None, (320, 200))
+    w1, w2 = cv2.initUndistortRectifyMap(K, None, None, K, (320, 200), cv2.CV_32FC1)
+    assert np.array_equal(m1, w1) and np.array_equal(m2, w2)
+
+
+def test_rectify_images_uncached_rebuilds_maps_on_gpu(engine):
+    """rectify_images without a cache (depthlib/rectify.py:209-235) rebuilds the maps on every call: stereoRectify on the
+    host, initUndistortRectifyMap and both remaps on the GPU; same rectified images as the cv2 chain."""
+    cv2 = pytest.importorskip("cv2")
+    from oracle import cv2_reference as cr
+    from depthestimation_b200.depthlib.rectify import rectify_images
+    H, W = 120, 300
+    L, R, _ = make_pair(H, W, 32, seed=77)
+    cal = make_calibration(H, W)
+    gl, gr = rectify_images(L, R, cal["cam_matrix_L"], cal["cam_matrix_R"], cal["baseline"], W, H, cal["dist_coeff_L"],
+                            cal["dist_coeff_R"], alpha=1.0, engine=engine)
+    wl, wr = cr.rectify_pair(L, R, cr.build_maps(cal, alpha=1.0))
+    assert np.array_equal(gl, wl) and np.array_equal(gr, wr)

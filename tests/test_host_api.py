@@ -82,10 +82,19 @@ def test_load_stereo_pair_invalid_paths():
             load_stereo_pair("a.png", "b.png")
 
 
+class _HostMapEngine:
+    """Stands in for the GPU map kernel in the CPU suite (the cache logic is what is tested here): the oracle's
+    restatement of initUndistortRectifyMap."""
+    def build_maps(self, K, dist, R, P, size):
+        from oracle import maps as om
+        return om.init_undistort_rectify_map(K, dist, R, P, size)
+
+
 def test_rectification_cache_identity():
+    pytest.importorskip("cv2")
     from depthestimation_b200.depthlib.rectify import RectificationCache
     K = np.array([[500.0, 0, 320], [0, 500.0, 240], [0, 0, 1]])
-    cache = RectificationCache()
+    cache = RectificationCache(engine=_HostMapEngine())
     m1 = cache.get_maps(K, K, 0.1, 640, 480)
     m2 = cache.get_maps(K, K, 0.1, 640, 480)
     assert m1 is m2 and set(m1) == {"map1_L", "map2_L", "map1_R", "map2_R"}

@@ -38,7 +38,7 @@ def run(name, steps, warmup, batch_override=0):
     import torch
     from depthestimation_b200.engine import StereoEngine, make_post_params, make_depth_params
     from depthestimation_b200.synth import make_pair, make_calibration
-    from oracle import cv2_reference as cr   # host-side map generation only (rectify.py:63-73 is host cv2 by design)
+    from depthestimation_b200.depthlib.rectify import RectificationCache
 
     H, W, D, mode, nframes = CONFIGS[name]
     kw = dict(min_disp=0, num_disp=D, block_size=5, disp12_max_diff=1, prefilter_cap=31, uniqueness_ratio=10,
@@ -56,7 +56,8 @@ def run(name, steps, warmup, batch_override=0):
     L = np.stack([pairs[i % len(pairs)][0] for i in range(B)])
     R = np.stack([pairs[i % len(pairs)][1] for i in range(B)])
     cal = make_calibration(H, W)
-    maps = cr.build_maps(cal, alpha=1.0)
+    maps = RectificationCache(engine=eng).get_maps(cal["cam_matrix_L"], cal["cam_matrix_R"], cal["baseline"], W, H,
+                                                   cal["dist_coeff_L"], cal["dist_coeff_R"], None, None, 1.0)
     eng.set_maps(maps["map1_L"], maps["map2_L"], maps["map1_R"], maps["map2_R"])
     pp = make_post_params(False, 100, 1.0, 2.5, True)
     dp = make_depth_params(cal["focal_length"], cal["baseline"], 0.0, eps=0, max_depth=None)
