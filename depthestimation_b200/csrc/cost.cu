@@ -127,7 +127,7 @@ enum { RA_VG = 0, RA_LOG, RA_NHIG, RA_VR, RA_LOR, RA_NHIR, RA_COUNT };
 #define COST_XT 20          // cost columns per strip; measured on B200: 20 beats 16 (by 3 %), 24 and 32
 #endif
 
-// Compile-time geometry of one CTA. NTS = stride of the per-thread shared-memory arrays (power of two >= Dp / 2);
+// Compile-time geometry of one CTA. NTS = stride of the per-thread shared-memory arrays (a multiple of 16 >= Dp / 2);
 // every shared-memory and (when Dp / 2 == NTS) global offset inside the slide loop is then an immediate.
 template <int BS, int NTS>
 struct CostCfg {
@@ -402,7 +402,13 @@ static int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
     const int NT = a.Dp / 2;
     if (NT <= 16) return launch_cost_t<BS, 16>(a, B, nseg, st);
     if (NT <= 32) return launch_cost_t<BS, 32>(a, B, nseg, st);
+    if (NT <= 48) return launch_cost_t<BS, 48>(a, B, nseg, st);
     if (NT <= 64) return launch_cost_t<BS, 64>(a, B, nseg, st);
+    // strides that follow D instead of jumping to 128: the ring of horizontal sums is BS * XT * NTS words, so D = 140
+    // (example_stereo.py) at NTS = 128 left room for four CTAs per SM instead of six
+    if (NT <= 80) return launch_cost_t<BS, 80>(a, B, nseg, st);
+    if (NT <= 96) return launch_cost_t<BS, 96>(a, B, nseg, st);
+    if (NT <= 112) return launch_cost_t<BS, 112>(a, B, nseg, st);
     return launch_cost_t<BS, 128>(a, B, nseg, st);
 }
 

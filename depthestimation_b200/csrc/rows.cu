@@ -14,6 +14,8 @@
 //           one lane per pixel (A.6, or A.7's SIMD rule for sgbm_3way).
 // HBM traffic: C twice + Sv once + the checkpoints = 6.7 B/cell instead of the 14 B/cell of two read-modify-write
 // passes plus a selection pass.
+#include <stdlib.h>
+
 #include "sgm_step.cuh"
 
 #ifndef ROW_K
@@ -576,6 +578,22 @@ int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint
     a.nosat = sum_cannot_saturate(e) ? 1 : 0;
     a.nlines = B * e.H;
     if (e.Dp > 512) return -2;
+    // Few lines in the call (a single pair, a handful of small frames): the GPU is far from full and the time is the
+    // length of one line's serial scan, which a lane group issues at well under one instruction per clock. Twice the
+    // lanes per line with half the registers each halves the instructions on that critical path (and costs ~1.5x the
+    // issue slots per line, which is why full batches keep 16 disparities per lane).
+    static int small_env = -1;
+    if (small_env < 0) { const char* v = getenv("B200S_ROWS_SMALL"); small_env = v ? atoi(v) : 2; }   // 0 never, 1 always, 2 auto
+    if (e.Dp > 64 && e.Dp <= 256 && small_env) {
+        int sms = 0, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const long long warps = (e.Dp <= 128) ? (a.nlines + 1) / 2 : a.nlines;
+        if (small_env == 1 || warps <= 4LL * sms) {
+            if (e.Dp <= 128) launch_rows_t<16, 4>(a, st); else launch_rows_t<32, 4>(a, st);
+            return 0;
+        }
+    }
     if (e.Dp > 64) {             // 16 disparities per lane
         int LW = 2;
         while (LW * 16 < e.Dp) LW *= 2;

@@ -43,6 +43,7 @@ struct VertArgs {
 // that drift against each other and fill each other's barrier / latency gaps); picked by the planner
 #define VERT_THREADS_WIDE 512
 #define VERT_THREADS_NARROW 288
+#define VERT_THREADS_XWIDE 576   // latency plan only: 72 column groups per CTA, so a 16-CTA cluster covers 1152 columns in ONE slot
 #define VERT_KMAX 4
 #define VERT_MAX_DEVICES 64
 #ifndef VERT_UREG
@@ -312,8 +313,12 @@ static cudaLaunchConfig_t vert_cfg(int threads, int CS, int B, size_t smem, cuda
 
 // Pick the cluster size (strips per frame) for one CTA width: frames in flight (co-resident clusters, asked from the
 // driver) per column iteration of a thread, among the sizes whose strip state fits; ties go to the fuller column slots.
+// latency = true: the plan for a few frames per call instead (every cluster resident at once anyway): the fewest
+// column slots per CTA and row, i.e. the frame spread over as many SMs as a cluster allows. A row of a strip costs its
+// CTA ~24 ALU-pipe cycles per column and direction, so one KITTI frame on 9 SMs is bound by those 9 SMs' issue rate
+// (measured: 831 us per frame at one frame per call against 53 us per frame in a full batch).
 template <int LW, int NR, int VT>
-static bool plan_vert(const Eff& e, VertPlan& best) {
+static bool plan_vert(const Eff& e, VertPlan& best, bool latency = false) {
     using VL = VertLayout<LW, NR, VT>;
     constexpr int G = VL::G;
     // function attributes are per DEVICE: opt every device in once (a process may drive several GPUs from several threads)
@@ -352,6 +357,11 @@ static bool plan_vert(const Eff& e, VertPlan& best) {
         if (cudaOccupancyMaxActiveClusters(&ncl, k_vert<LW, NR, true, VT, false>, &cfg) != cudaSuccess) { cudaGetLastError(); continue; }
         if (ncl <= 0) continue;
         double score = (double)ncl / KIT * (clamp ? 0.8 : 1.0) + 1e-3 * (double)e.W1 / ((double)CS * KIT * G);
+        if (latency) {
+            score = 1.0 / ((double)KIT * (clamp ? 1.25 : 1.0)) + 1e-3 / ((double)KIT * G) + 1e-6 * CS;   // serial slots per thread first
+            // one CTA per SM: two narrow CTAs of a cluster sharing an SM would share its issue slots again
+            if (smem < 116 * 1024) smem = 116 * 1024;
+        }
         if (score > best.score) { best.score = score; best.CS = CS; best.NC = NC; best.KIT = KIT; best.smem = smem; best.clusters = ncl; best.threads = VT; best.clamp = clamp; }
     }
     return best.score > 0.0;
@@ -370,7 +380,7 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
                          int* clusters_out) {
     // the plan depends on (device, W1, Dp) only; the last one per device is cached. Several host threads (one handle per
     // thread, possibly on different GPUs) come through here: the cache is guarded and used through a local copy.
-    struct Cache { VertPlan plan; int W1 = -1, Dp = -1; bool ok = false; };
+    struct Cache { VertPlan plan, lat; int W1 = -1, Dp = -1, sms = 0; bool ok = false, lat_ok = false; };
     static Cache cache[VERT_MAX_DEVICES];
     static std::mutex mu;
     int dev = 0;
@@ -388,6 +398,18 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
             const bool okn = (vt_env == 0 || vt_env == VERT_THREADS_NARROW) && plan_vert<LW, NR, VERT_THREADS_NARROW>(e, narrow);
             c.ok = okw || okn;
             if (c.ok) c.plan = (okn && (!okw || narrow.score > wide.score)) ? narrow : wide;
+            VertPlan xwide;
+            const bool lw = (vt_env == 0 || vt_env == VERT_THREADS_WIDE) && plan_vert<LW, NR, VERT_THREADS_WIDE>(e, wide, true);
+            const bool ln = (vt_env == 0 || vt_env == VERT_THREADS_NARROW) && plan_vert<LW, NR, VERT_THREADS_NARROW>(e, narrow, true);
+            const bool lx = (vt_env == 0 || vt_env == VERT_THREADS_XWIDE) && plan_vert<LW, NR, VERT_THREADS_XWIDE>(e, xwide, true);
+            c.lat_ok = lw || ln || lx;
+            if (c.lat_ok) {
+                c.lat.score = -1.0;
+                if (lw && wide.score > c.lat.score) c.lat = wide;
+                if (ln && narrow.score > c.lat.score) c.lat = narrow;
+                if (lx && xwide.score > c.lat.score) c.lat = xwide;
+            }
+            cudaDeviceGetAttribute(&c.sms, cudaDevAttrMultiProcessorCount, dev);
             c.W1 = e.W1; c.Dp = e.Dp;
             if (getenv("B200S_VERBOSE") && c.ok)
                 fprintf(stderr, "[b200s] dev %d k_vert<%d,%d>: W1=%d Dp=%d -> %d threads, cluster %d x %d cols (%d per thread group), %zu B smem%s, %d clusters co-resident\n",
@@ -395,6 +417,14 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
         }
         cached = c.plan;
         cok = c.ok;
+        static int lat_env = -1;
+        if (lat_env < 0) { const char* v = getenv("B200S_VERT_LATENCY"); lat_env = v ? atoi(v) : 1; }
+        // few frames in the call (at most half the SMs busy even with the widest clusters) and a latency plan that
+        // holds every column of its strip in ONE slot per thread: take it. Measured, KITTI pairs per call: 1 -> 1.97 /
+        // 1.79 ms, 4 -> 2.37 / 2.18 ms per call (throughput plan / 16 CTAs x 576 threads); from 8 pairs on the throughput
+        // plan wins, and a latency plan that still needs several slots loses (1920x1080 D=256: 10.5 -> 12.3 ms)
+        if (cok && c.lat_ok && lat_env && B > 0 && 2LL * B * c.lat.CS <= c.sms && c.lat.KIT == 1 && c.plan.KIT > 1)
+            cached = c.lat;
     }
     if (!cok) return 1;                                            // does not fit: caller falls back to k_path
     if (clusters_out) *clusters_out = cached.clusters;
@@ -405,7 +435,8 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     a.KIT = cached.KIT; a.nrec = cached.clamp ? cached.NC + 1 : cached.KIT * (cached.threads / LW) + 1;
     const bool pad = e.D != LW * 2 * NR;
     cudaError_t le = (cached.threads == VERT_THREADS_WIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_WIDE>(cached, a, B, pad, st)
-                                                           : launch_vert_vt<LW, NR, VERT_THREADS_NARROW>(cached, a, B, pad, st);
+                   : (cached.threads == VERT_THREADS_XWIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_XWIDE>(cached, a, B, pad, st)
+                                                            : launch_vert_vt<LW, NR, VERT_THREADS_NARROW>(cached, a, B, pad, st);
     if (le != cudaSuccess) {   // the planner said it fits: a failed launch is an error, not a reason to fall back silently
         fprintf(stderr, "[b200s] k_vert launch failed on device %d: %s\n", dev, cudaGetErrorString(le));
         cudaGetLastError();
