@@ -66,6 +66,11 @@ __device__ __forceinline__ void load_regs_pol(const uint16_t* p, unsigned (&r)[N
 #ifndef ROWS_THREADS
 #define ROWS_THREADS 128
 #endif
+template <int LW, int NR>
+struct RowGeom {
+    static constexpr int NCH = LW * NR / 4;                                   // 16-byte units of one pixel's disparities
+    static constexpr int NCHP = NCH >= 8 ? (NCH + 7) & ~7 : NCH;              // a record is a whole number of 8-unit swizzle blocks
+};
 #ifndef ROWS_MINB
 #define ROWS_MINB 4   // 4 CTAs (16 warps) per SM: 57 KB of shared memory each, <= 128 registers
 #endif
@@ -76,30 +81,41 @@ __device__ __forceinline__ void load_regs_pol(const uint16_t* p, unsigned (&r)[N
 template <int LW, int NR, bool PAD, bool W3, bool NS>
 __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
-    constexpr int RPW = 32 / LW;                    // lines per warp
+    using LG = LaneGroup<LW>;
+    constexpr int RPW = LG::RPW;                    // lines per warp
     constexpr int NCH = LW * NR / 4;                // 16-byte units per pixel record (all disparities of one pixel)
+    constexpr int NCHP = RowGeom<LW, NR>::NCHP;     // units a record occupies (padded to whole swizzle blocks)
     constexpr int NPW = ROW_K * RPW;                // pixels per warp and chunk
-    constexpr int SWZ = NCH >= 8 ? 7 : NCH - 1;     // unit swizzle: record p stores logical unit c at c ^ (p & SWZ)
-    const int LINES = (int)blockDim.x / LW;         // lines per CTA (128 threads for throughput, one warp per CTA when few lines are in flight)
-    extern __shared__ __align__(16) uint4 rsm[];    // [LINES][ROW_K][NR/4][LW] uint4: L(<-), then S, of the current chunk
-    const int gl = threadIdx.x % LW;
-    const int lic = threadIdx.x / LW;               // line in CTA
+    constexpr int SWZ = NCH >= 8 ? 7 : NCH - 1;     // unit swizzle: logical unit c of record p sits at (c & ~SWZ) + ((c ^ p) & SWZ)
+    const int NWARP = (int)blockDim.x / 32;
+    const int LINES = NWARP * RPW;                  // lines per CTA (128 threads for throughput, one warp per CTA when few lines are in flight)
+    extern __shared__ __align__(16) uint4 rsm[];    // [warps][NPW][NCHP] records: L(<-), then S, of the current chunk; then C of the chunk per line
+    const int lane = threadIdx.x & 31;
+    const bool idle = !LG::POW2 && lane >= LG::USED;            // lanes beyond the last whole group of the warp
+    const int gl = LG::POW2 ? (int)threadIdx.x % LW : (idle ? lane - LG::USED : lane % LW);
+    const int lic = LG::POW2 ? (int)threadIdx.x / LW : ((int)threadIdx.x >> 5) * RPW + (idle ? RPW - 1 : lane / LW);   // line in CTA
     const int line_raw = blockIdx.x * LINES + lic;
-    const bool valid = line_raw < a.nlines;
+    const bool valid = line_raw < a.nlines && !idle;
     const int line = valid ? line_raw : a.nlines - 1;   // keep the warp converged: surplus groups shadow the last line
     // every lane of the warp runs the same loops, so shuffles use the full mask with width LW (no
     // divergence check per shuffle)
     const unsigned gmask = 0xffffffffu;
     const int Dp = PAD ? a.Dp : LW * DPL;           // no padded disparities: the pitch is a compile-time constant
-    const bool active = gl * DPL < Dp;
+    const bool active = gl * DPL < Dp && !idle;
     constexpr bool nosat = NS;
     // one RECORD per pixel = all its disparities (NCH units of 8), records of a warp ordered column-major
     // (p = column-in-chunk * RPW + line-in-warp). Lane gl's q-th unit (disparities gl*DPL + 8q ..) is logical unit
     // gl + LW*q, stored at unit ^ (p & SWZ): conflict-free both for the lane groups that write a record during the
     // scans (8 lanes, 8 different units) and for the lanes that each read a whole record during selection.
-    uint4* Lw = rsm + (size_t)(lic / RPW) * NPW * NCH;
+    uint4* Lw = rsm + (size_t)(lic / RPW) * NPW * NCHP;
     const int rw = lic % RPW;
-    uint4* Cb = rsm + (size_t)(LINES + lic) * ROW_K * (NR / 4) * LW;                        // C of the current chunk
+    uint4* Cb = rsm + (size_t)NWARP * NPW * NCHP + (size_t)lic * ROW_K * (NR / 4) * LW;    // C of the current chunk
+    // where this lane's q-th unit (logical unit gl + LW q) sits inside a record of swizzle phase sw
+    auto unit_at = [&](const int q, const int sw) {
+        if (LG::POW2 && NCHP == NCH) return (gl ^ sw) + q * LW;      // LW is a multiple of the swizzle block (or smaller than it)
+        const int c = gl + LW * q;
+        return (c & ~SWZ) + ((c ^ sw) & SWZ);
+    };
 
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
@@ -175,11 +191,13 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
     auto stepb = [&](const int x, const int xs, const unsigned (&Cc)[NR]) {     // one <- step; L and C kept for the -> scan
         sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
         const int pix = (x - xs) * RPW + rw;
-        uint4* rec = Lw + pix * NCH + (gl ^ (pix & SWZ));
+        uint4* rec = Lw + pix * NCHP;
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
-            rec[q * LW] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
-            Cb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(Cc[4 * q], Cc[4 * q + 1], Cc[4 * q + 2], Cc[4 * q + 3]);
+            if (LG::POW2 || !idle) {   // idle lanes shadow the warp's last group: they must not touch its records
+                rec[unit_at(q, pix & SWZ)] = make_uint4(L[4 * q], L[4 * q + 1], L[4 * q + 2], L[4 * q + 3]);
+                Cb[((x - xs) * (NR / 4) + q) * LW + gl] = make_uint4(Cc[4 * q], Cc[4 * q + 1], Cc[4 * q + 2], Cc[4 * q + 3]);
+            }
         }
     };
     auto stepf = [&](const int x, const int xs, unsigned (&Sc)[NR]) {   // one -> step + winner; Sc holds Sv on entry
@@ -191,10 +209,10 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         }
         sgm_step<LW, NR, PAD>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
         const int pix = (x - xs) * RPW + rw;
-        uint4* rec = Lw + pix * NCH + (gl ^ (pix & SWZ));
+        uint4* rec = Lw + pix * NCHP;
 #pragma unroll
         for (int q = 0; q < NR / 4; q++) {
-            const uint4 t = rec[q * LW];
+            const uint4 t = rec[unit_at(q, pix & SWZ)];
             if (nosat) {   // the sum of all paths provably stays below 32768: plain adds on the packed halves
 #if SGM_FMA_ADDS
                 Sc[4 * q] = __vadd2(__vadd2(Sc[4 * q], Lr[4 * q]), t.x); Sc[4 * q + 1] = __vadd2(__vadd2(Sc[4 * q + 1], Lr[4 * q + 1]), t.y);
@@ -219,7 +237,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
             w.y = PAD ? umax2(Sc[4 * q + 1], pm[4 * q + 1]) : Sc[4 * q + 1];
             w.z = PAD ? umax2(Sc[4 * q + 2], pm[4 * q + 2]) : Sc[4 * q + 2];
             w.w = PAD ? umax2(Sc[4 * q + 3], pm[4 * q + 3]) : Sc[4 * q + 3];
-            rec[q * LW] = w;
+            if (LG::POW2 || !idle) rec[unit_at(q, pix & SWZ)] = w;
         }
     };
     // ---- A.6 steps 1-4 for the pixels of chunk [xs, xs + ncols), one lane per pixel ---------------------------------
@@ -235,11 +253,11 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
             const int k = pix / RPW, r = pix % RPW;
             const int pline = wline0 + r;
             if (k >= ncols || pline >= a.nlines) continue;
-            uint4* pb = Lw + pix * NCH;
+            uint4* pb = Lw + pix * NCHP;
             const int sw = pix & SWZ;
             auto unit_of = [&](const int j) {                 // record unit that holds disparities 8j .. 8j+7
                 const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;
-                return c ^ sw;
+                return (c & ~SWZ) + ((c ^ sw) & SWZ);
             };
             auto unit_ct = [&](const int j) -> uint4 {        // the same for a compile-time j: immediate offsets
                 const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;
@@ -387,7 +405,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
     };
     auto start_from_ck = [&](const int xe) {
         if (xe < a.W1) {
-            const unsigned mn = group_min2<LW>(local_min2<NR>(L), gmask);
+            const unsigned mn = group_min2<LW>(local_min2<NR>(L), gmask, gl);
             m = min(mn & 0xffffu, mn >> 16);
         } else {
             sgm_reset<NR>(L, m);
@@ -395,12 +413,20 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
     };
     auto prefetch_chunk = [&](const int xs) {    // bring C and Sv of chunk [xs, xs+K) towards L2
 #if ROWS_PF2
-        if (active && xs + gl < a.W1 && gl < ROW_K) {
-            if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * Dp - gl * DPL);
-            if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * Dp - gl * DPL);
-            if (Dp > 64) {
-                if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + gl) * Dp - gl * DPL + 64);
-                if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + gl) * Dp - gl * DPL + 64);
+#pragma unroll
+        for (int c0 = 0; c0 < ROW_K; c0 += LW) {
+            const int c = c0 + gl;
+            if (active && xs + c < a.W1 && c < ROW_K) {
+                if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + c) * Dp - gl * DPL);
+                if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + c) * Dp - gl * DPL);
+                if (Dp > 64) {
+                    if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + c) * Dp - gl * DPL + 64);
+                    if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + c) * Dp - gl * DPL + 64);
+                }
+                if (Dp > 128) {
+                    if (ROWS_PF2 & 1) prefetch_l2(Crow + (size_t)(xs + c) * Dp - gl * DPL + 128);
+                    if (ROWS_PF2 & 2) prefetch_l2(Srow + (size_t)(xs + c) * Dp - gl * DPL + 128);
+                }
             }
         }
 #endif
@@ -501,9 +527,9 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
 }
 
 template <int LW, int NR>
-static size_t rows_smem() {   // L / S records + C of the chunk
-    constexpr int LINES = ROWS_THREADS / LW;
-    return (size_t)2 * LINES * ROW_K * (NR / 4) * LW * sizeof(uint4);
+static size_t rows_smem() {   // L / S records + C of the chunk, for ROWS_THREADS threads
+    constexpr int NW = ROWS_THREADS / 32, RPW = LaneGroup<LW>::RPW;
+    return ((size_t)NW * ROW_K * RPW * RowGeom<LW, NR>::NCHP + (size_t)NW * RPW * ROW_K * (NR / 4) * LW) * sizeof(uint4);
 }
 
 template <int LW, int NR, bool PAD, bool W3, bool NS>
@@ -514,7 +540,7 @@ static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t 
     cudaFuncSetAttribute(k_rows<LW, NR, PAD, W3, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     // a single frame (or a few small ones) leaves most SMs without a CTA at 128 threads: spread the lines one warp per CTA
     if (grid < 2 * sms) {
-        constexpr int L1 = 32 / LW;
+        constexpr int L1 = LaneGroup<LW>::RPW;
         k_rows<LW, NR, PAD, W3, NS><<<(a.nlines + L1 - 1) / L1, 32, smem / (ROWS_THREADS / 32), st>>>(a);
     } else {
         k_rows<LW, NR, PAD, W3, NS><<<grid, ROWS_THREADS, smem, st>>>(a);
@@ -523,7 +549,7 @@ static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t 
 
 template <int LW, int NR>
 static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
-    constexpr int LINES = ROWS_THREADS / LW;
+    constexpr int LINES = ROWS_THREADS / 32 * LaneGroup<LW>::RPW;
     const bool w3 = (a.mode == B200S_MODE_SGBM_3WAY) && (8 * (a.D / 8) > 0);
     const size_t smem = rows_smem<LW, NR>();
     const int grid = (a.nlines + LINES - 1) / LINES;
@@ -541,7 +567,7 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
 
 template <int LW, int NR>
 static int rows_capacity_t() {
-    constexpr int LINES = ROWS_THREADS / LW;
+    constexpr int LINES = ROWS_THREADS / 32 * LaneGroup<LW>::RPW;
     const size_t smem = rows_smem<LW, NR>();
     cudaFuncSetAttribute(k_rows<LW, NR, true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int nb = 0, dev = 0, sms = 0;
@@ -554,9 +580,16 @@ static int rows_capacity_t() {
 // image rows the row kernel keeps in flight at once (one wave); a batch of B frames is B*H rows
 int rows_capacity_lines(const Eff& e) {
     if (e.Dp > 64) {
-        int LW = 8;
-        while (LW * 16 < e.Dp) LW *= 2;
-        return LW == 8 ? rows_capacity_t<8, 8>() : (LW == 16 ? rows_capacity_t<16, 8>() : rows_capacity_t<32, 8>());
+        switch ((e.Dp + 15) / 16) {
+            case 5: return rows_capacity_t<5, 8>();
+            case 6: return rows_capacity_t<6, 8>();
+            case 7: return rows_capacity_t<7, 8>();
+            case 8: return rows_capacity_t<8, 8>();
+            case 9: return rows_capacity_t<9, 8>();
+            case 10: return rows_capacity_t<10, 8>();
+            case 11: case 12: case 13: case 14: case 15: case 16: return rows_capacity_t<16, 8>();
+            default: return rows_capacity_t<32, 8>();
+        }
     }
     int LW = 2;
     while (LW * 8 < e.Dp) LW *= 2;
@@ -594,12 +627,15 @@ int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint
             return 0;
         }
     }
-    if (e.Dp > 64) {             // 16 disparities per lane
-        int LW = 2;
-        while (LW * 16 < e.Dp) LW *= 2;
-        switch (LW) {
-            case 2: case 4: case 8: launch_rows_t<8, 8>(a, st); break;
-            case 16: launch_rows_t<16, 8>(a, st); break;
+    if (e.Dp > 64) {             // 16 disparities per lane; the lane count follows D (a warp carries 32 / LW lines)
+        switch ((e.Dp + 15) / 16) {
+            case 5: launch_rows_t<5, 8>(a, st); break;     // D  65 ..  80: 6 lines per warp
+            case 6: launch_rows_t<6, 8>(a, st); break;     // D  81 ..  96: 5
+            case 7: launch_rows_t<7, 8>(a, st); break;     // D  97 .. 112: 4
+            case 8: launch_rows_t<8, 8>(a, st); break;     // D 113 .. 128: 4
+            case 9: launch_rows_t<9, 8>(a, st); break;     // D 129 .. 144: 3 (example_stereo.py: D = 140)
+            case 10: launch_rows_t<10, 8>(a, st); break;   // D 145 .. 160: 3
+            case 11: case 12: case 13: case 14: case 15: case 16: launch_rows_t<16, 8>(a, st); break;   // 2 lines per warp either way
             default: launch_rows_t<32, 8>(a, st); break;
         }
     } else {                     // 8 disparities per lane

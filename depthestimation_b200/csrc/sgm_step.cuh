@@ -36,17 +36,47 @@ __device__ __forceinline__ void store_regs(uint16_t* p, const unsigned (&r)[NR])
     for (int q = 0; q < NR / 4; q++) *(uint4*)(p + 8 * q) = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
 }
 
+// ---- lane groups ----------------------------------------------------------------------------------------------------------
+// LW lanes hold the disparities of one pixel. LW need not be a power of two: a warp then carries RPW = 32 / LW whole groups
+// in its first RPW * LW lanes (the rest idle), e.g. 3 groups of 9 lanes for D = 140 instead of 2 groups of 16 with 7 lanes
+// idle each. Neighbour exchange uses absolute lane indices (the group-edge lanes are patched by the caller anyway); the
+// group minimum of a non-power-of-two group is a shuffle-down tree with out-of-group sources ignored, then a broadcast.
+template <int LW> struct LaneGroup {
+    static constexpr bool POW2 = (LW & (LW - 1)) == 0;
+    static constexpr int RPW = 32 / LW;                       // groups per warp
+    static constexpr int USED = RPW * LW;                     // lanes of a warp that belong to a group
+    static constexpr int P2 = LW <= 1 ? 1 : LW <= 2 ? 2 : LW <= 4 ? 4 : LW <= 8 ? 8 : LW <= 16 ? 16 : 32;   // next power of two
+};
 template <int LW>
 __device__ __forceinline__ unsigned group_mask() {
     if (LW == 32) return 0xffffffffu;
     return ((1u << LW) - 1u) << ((threadIdx.x & 31) / LW * LW);
 }
+// value of the previous / next lane (garbage at the group edges: callers replace it there)
+template <int LW>
+__device__ __forceinline__ unsigned grp_prev(unsigned v, unsigned gmask) {
+    if (LaneGroup<LW>::POW2) return __shfl_up_sync(gmask, v, 1, LW);
+    return __shfl_sync(0xffffffffu, v, (int)(threadIdx.x & 31) - 1);
+}
+template <int LW>
+__device__ __forceinline__ unsigned grp_next(unsigned v, unsigned gmask) {
+    if (LaneGroup<LW>::POW2) return __shfl_down_sync(gmask, v, 1, LW);
+    return __shfl_sync(0xffffffffu, v, (int)(threadIdx.x & 31) + 1);
+}
 
 template <int LW>
-__device__ __forceinline__ unsigned group_min2(unsigned v, unsigned gmask) {
+__device__ __forceinline__ unsigned group_min2(unsigned v, unsigned gmask, const int gl = 0) {
+    if (LaneGroup<LW>::POW2) {
 #pragma unroll
-    for (int o = LW / 2; o > 0; o >>= 1) v = umin2(v, __shfl_xor_sync(gmask, v, o, LW));
-    return v;
+        for (int o = LW / 2; o > 0; o >>= 1) v = umin2(v, __shfl_xor_sync(gmask, v, o, LW));
+        return v;
+    }
+#pragma unroll
+    for (int o = LaneGroup<LW>::P2 / 2; o > 0; o >>= 1) {
+        const unsigned t = __shfl_down_sync(0xffffffffu, v, o);
+        if (gl + o < LW) v = umin2(v, t);
+    }
+    return __shfl_sync(0xffffffffu, v, (int)(threadIdx.x & 31) - gl);   // group lane 0 holds the minimum
 }
 
 template <int NR>
@@ -75,8 +105,8 @@ template <int LW, int NR, bool PAD = true>
 __device__ __forceinline__ unsigned sgm_step_core(unsigned (&L)[NR], const unsigned m, const unsigned (&Cq)[NR],
                                          const unsigned (&pm)[NR], const unsigned gmask, const int gl,
                                          const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
-    unsigned up = __shfl_up_sync(gmask, L[NR - 1], 1, LW);
-    unsigned dn = __shfl_down_sync(gmask, L[0], 1, LW);
+    unsigned up = grp_prev<LW>(L[NR - 1], gmask);
+    unsigned dn = grp_next<LW>(L[0], gmask);
     if (gl == 0) up = 0x7fff7fffu;
     if (gl == LW - 1) dn = 0x7fff7fffu;
     const unsigned mm = pk2(m);
@@ -102,7 +132,7 @@ __device__ __forceinline__ unsigned sgm_step_core(unsigned (&L)[NR], const unsig
     }
     if (PAD && quirk) {
         // d0 is a multiple of 8, so it sits in register 0 or (NR == 8) register 4 of lane d0 / (2 NR)
-        const unsigned upn = __shfl_up_sync(gmask, Ln[NR - 1], 1, LW);
+        const unsigned upn = grp_prev<LW>(Ln[NR - 1], gmask);
         const int ql = d0 / (2 * NR), jq = (d0 % (2 * NR)) / 2;
         if (gl == ql) {
             if (jq == 0) {
@@ -130,7 +160,7 @@ template <int LW, int NR, bool PAD = true>
 __device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const unsigned (&Cq)[NR],
                                          const unsigned (&pm)[NR], const unsigned gmask, const int gl,
                                          const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
-    const unsigned mn = group_min2<LW>(sgm_step_core<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirk, d0), gmask);
+    const unsigned mn = group_min2<LW>(sgm_step_core<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirk, d0), gmask, gl);
     m = min(mn & 0xffffu, mn >> 16);
 }
 

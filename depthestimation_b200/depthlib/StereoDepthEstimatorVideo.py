@@ -49,6 +49,7 @@ class _FrameWorker:
         self.want_depth = bool(dp.enabled)
         self._free = []          # page-locked (L, R, out) triples of the current chunk geometry
         self._geom = None
+        self._sized = None
         self._cap = max(1, int(cap))   # frames per buffer: the full chunk, also for the shorter first and last chunks
         self._lock = threading.Lock()
         self._pool = ThreadPoolExecutor(max(1, int(copy_threads)))
@@ -75,6 +76,16 @@ class _FrameWorker:
             raise ValueError("sharded video path: every frame of a stream must be uint8 and of one size")
         bufs, geom = self._buffers(B, shape)
         bL, bR, out = bufs
+        if self._sized != geom:
+            # size the engine's device scratch for a FULL chunk once: the first chunks of a stream are shorter (ramp),
+            # and growing the scratch later frees and reallocates gigabytes in the middle of the stream
+            self._sized = geom
+            if B < geom[0]:
+                bL[B:] = 0; bR[B:] = 0
+                self.eng.pipeline_batch_wait(self.eng.pipeline_frames_submit(
+                    bL, bR, self.pp, self.dp, size=self.size, area=self.area, use_maps=self.use_maps,
+                    want_disp=not self.want_depth, want_depth=self.want_depth,
+                    out_disp=None if self.want_depth else out, out_depth=out if self.want_depth else None))
 
         def put(k):
             np.copyto(bL[k], Ls[k]); np.copyto(bR[k], Rs[k])
@@ -212,6 +223,15 @@ class StereoDepthEstimatorVideo:
         chunk = self.chunk
         if chunk is None:
             chunk = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
+            # a source of known length (a list of frames, a short clip): at least two chunks per GPU, so that every GPU
+            # gets work and its copies overlap its kernels
+            n = None
+            try:
+                n = min(len(self.left_source), len(self.right_source))
+            except TypeError:
+                pass
+            if n:
+                chunk = max(1, min(chunk, -(-n // (2 * len(self.devices)))))
 
         # workers (engine handle with its device scratch, uploaded maps, page-locked chunk buffers) survive between
         # calls of this generator as long as the configuration is the same

@@ -4,7 +4,7 @@ node in ONE process (frames sharded chunk-per-GPU by sharding.ThreadedSharder, h
 
   video720  configs[3]: 240 stereo frames 1280x720 (3-channel, as a capture delivers them), D = 128, default sgbm_3way,
             calibrated: rectify -> match -> post -> depth, one depth map per frame yielded in order
-  uhd4k     configs[4]: a batch of 64 pairs 3840x2160, D = 256, sgbm_3way, the same full pipeline, 8 pairs per GPU call
+  uhd4k     configs[4]: a batch of 64 pairs 3840x2160, D = 256, sgbm_3way, the same full pipeline
 
     python tools/multigpu_jobs.py [--gpus 1,2,4,8] [--only video720,uhd4k]
 
@@ -23,7 +23,7 @@ import numpy as np
 ROOT = Path(__file__).resolve().parents[1]
 sys.path.insert(0, str(ROOT))
 
-JOBS = {"video720": (720, 1280, 128, 240, 3, None), "uhd4k": (2160, 3840, 256, 64, 1, 8)}
+JOBS = {"video720": (720, 1280, 128, 240, 3, None), "uhd4k": (2160, 3840, 256, 64, 1, None)}
 
 
 def main():
