@@ -406,6 +406,7 @@ static int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
     if (NT <= 64) return launch_cost_t<BS, 64>(a, B, nseg, st);
     // strides that follow D instead of jumping to 128: the ring of horizontal sums is BS * XT * NTS words, so D = 140
     // (example_stereo.py) at NTS = 128 left room for four CTAs per SM instead of six
+    if (NT <= 72) return launch_cost_t<BS, 72>(a, B, nseg, st);   // D = 129 .. 144 exactly: compile-time global offsets too
     if (NT <= 80) return launch_cost_t<BS, 80>(a, B, nseg, st);
     if (NT <= 96) return launch_cost_t<BS, 96>(a, B, nseg, st);
     if (NT <= 112) return launch_cost_t<BS, 112>(a, B, nseg, st);

@@ -16,7 +16,7 @@
 //                     the predecessor is then outside the cost domain, which is exactly the
 //                     reference's border condition (L = 0, m = 0)
 // S is accumulated with a saturating add at 32767 (VIADDMNMX.U16x2).
-#include "common.cuh"
+#include "sgm_step.cuh"
 
 struct PathArgs {
     const uint16_t* C;
@@ -29,16 +29,23 @@ struct PathArgs {
     StripePlan sp;
 };
 
-template <int LW>
+// LW lanes x 2 NR disparities per lane; a warp carries 32 / LW lines (LW need not be a power of two, sgm_step.cuh).
+template <int LW, int NR>
 __global__ void __launch_bounds__(128) k_path(const PathArgs a) {
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int gl = threadIdx.x % LW;            // lane within the line group
-    const int line = tid / LW;
+    using LG = LaneGroup<LW>;
+    constexpr int DPL = 2 * NR;
+    const int lane = threadIdx.x & 31;
+    const bool idle = !LG::POW2 && lane >= LG::USED;
+    const int gl = LG::POW2 ? (int)threadIdx.x % LW : (idle ? lane - LG::USED : lane % LW);   // lane within the line group
+    const int wline = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * LG::RPW;        // first line of this warp
     const int b = blockIdx.z;
     const bool horizontal = (a.py == 0);
     const int nlines = horizontal ? a.H : a.W1 * a.sp.n;
-    if (line >= nlines) return;
-    const unsigned gmask = (LW == 32) ? 0xffffffffu : (((1u << LW) - 1u) << ((threadIdx.x % 32) / LW * LW));
+    if (wline >= nlines) return;                                                              // whole warps only: shuffles below
+    const int line_raw = wline + (LG::POW2 ? lane / LW : (idle ? LG::RPW - 1 : lane / LW));
+    const bool live = line_raw < nlines && !idle;
+    const int line = live ? line_raw : nlines - 1;                                            // surplus groups shadow the last line
+    const unsigned gmask = 0xffffffffu;
 
     // ---- line geometry --------------------------------------------------------------------
     int x, y, nsteps, ya = 0, racc = 0, stripe = 0;
@@ -53,113 +60,100 @@ __global__ void __launch_bounds__(128) k_path(const PathArgs a) {
         nsteps = yb - ya;
         y = (a.py < 0) ? ya : yb - 1;
     }
+    // every lane of the warp runs the longest line of the warp (stripes differ in length): shuffles stay converged
+    int wsteps = nsteps;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wsteps = max(wsteps, __shfl_xor_sync(0xffffffffu, wsteps, o));
     const int sx = -a.px, sy = -a.py;
 
-    const bool active = (gl * 8 < a.Dp);
-    unsigned pm[4];
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-        int d = gl * 8 + 2 * j;
-        pm[j] = (d >= a.D ? 0x7fffu : 0u) | (d + 1 >= a.D ? 0x7fff0000u : 0u);
-    }
-    const unsigned P1P1 = pk2((unsigned)a.P1);
-    const int qlane = a.D / 8;  // lane holding the partial tail d0..D-1 (only used when quirk)
+    const bool active = (gl * DPL < a.Dp) && live;
+    unsigned pm[NR];
+    make_padmask<NR>(pm, gl, a.D);
+    const unsigned P1P1 = pk2((unsigned)a.P1), P2mP1 = (unsigned)(a.P2 - a.P1);
+    const int d0 = 8 * (a.D / 8);
 
-    unsigned L[4] = {0x7fff7fffu, 0x7fff7fffu, 0x7fff7fffu, 0x7fff7fffu};
+    unsigned L[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) L[j] = 0x7fff7fffu;
     unsigned m = 0;
     const size_t frameC = (size_t)b * a.H * a.W1 * a.Dp;
+    auto c_ptr = [&](const int xx, const int yy) -> const uint16_t* {
+        if (a.Calt != nullptr && stripe > 0 && (yy - ya) < a.sp.alt_rows)
+            return a.Calt + (((size_t)(b * B200S_MAX_STRIPES + stripe) * a.sp.alt_rows + (yy - ya)) * a.W1 + xx) * a.Dp + gl * DPL;
+        return a.C + frameC + ((size_t)yy * a.W1 + xx) * a.Dp + gl * DPL;
+    };
+    // C of the next step is requested before the current step is computed (one step of look-ahead in registers)
+    unsigned Cq[NR], Cn[NR];
+#pragma unroll
+    for (int j = 0; j < NR; j++) { Cq[j] = 0u; Cn[j] = 0u; }
+    if (active && nsteps > 0) load_regs_nc<NR>(c_ptr(x, y), Cn);
 
-    for (int t = 0; t < nsteps; t++) {
+    for (int t = 0; t < wsteps; t++) {
+        const bool in_line = t < nsteps;
         bool reset = (t == 0);
         if (!horizontal) reset = reset || (a.px < 0 && x == 0) || (a.px > 0 && x == a.W1 - 1);
         // ---- loads -----------------------------------------------------------------------
-        uint4 cq = make_uint4(0, 0, 0, 0), sq = make_uint4(0, 0, 0, 0);
+        unsigned Sq[NR];
+#pragma unroll
+        for (int j = 0; j < NR; j++) { Cq[j] = Cn[j]; Sq[j] = 0u; }
         const bool acc = horizontal || (y >= racc);
-        size_t off = frameC + ((size_t)y * a.W1 + x) * a.Dp + gl * 8;
-        if (active) {
-            const uint16_t* cp = a.C + off;
-            if (a.Calt != nullptr && stripe > 0 && (y - ya) < a.sp.alt_rows)
-                cp = a.Calt + (((size_t)(b * B200S_MAX_STRIPES + stripe) * a.sp.alt_rows + (y - ya)) * a.W1 + x) * a.Dp +
-                     gl * 8;
-            cq = __ldg((const uint4*)cp);
-            if (acc && !a.first) sq = *(const uint4*)(a.S + off);
-        }
-        if (reset) {
-            L[0] = L[1] = L[2] = L[3] = 0u;
-            m = 0;
-        }
-        // ---- neighbours d-1 / d+1 across lanes ----------------------------------------------
-        unsigned up = __shfl_up_sync(gmask, L[3], 1, LW);
-        unsigned dn = __shfl_down_sync(gmask, L[0], 1, LW);
-        if (gl == 0) up = 0x7fff7fffu;
-        if (gl == LW - 1) dn = 0x7fff7fffu;
-        const unsigned mm = pk2(m);
-        const unsigned dmp = pk2(m + (unsigned)(a.P2 - a.P1));
-        const unsigned Cq[4] = {cq.x, cq.y, cq.z, cq.w};
-        unsigned Ln[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            unsigned bq = shift_pair(j == 0 ? up : L[j - 1], L[j]);       // (L[d-1], L[d])
-            unsigned cn = shift_pair(L[j], j == 3 ? dn : L[j + 1]);       // (L[d+1], L[d+2])
-            unsigned tt = umin3_2(bq, cn, dmp);
-            tt = uaddmin2(tt, P1P1, L[j]);
-            Ln[j] = umax2(Cq[j] + tt - mm, pm[j]);
-        }
-        if (a.quirk) {
-            unsigned upn = __shfl_up_sync(gmask, Ln[3], 1, LW);
-            if (gl == qlane) {
-                unsigned bq = shift_pair(a.quirk == 1 ? upn : 0x7fff7fffu, L[0]);
-                unsigned cn = shift_pair(L[0], L[1]);
-                unsigned tt = umin3_2(bq, cn, dmp);
-                tt = uaddmin2(tt, P1P1, L[0]);
-                Ln[0] = umax2(Cq[0] + tt - mm, pm[0]);
-            }
-        }
-        if (!active) Ln[0] = Ln[1] = Ln[2] = Ln[3] = 0x7fff7fffu;
-        // ---- m = min over d ------------------------------------------------------------------
-        unsigned mn = umin2(umin3_2(Ln[0], Ln[1], Ln[2]), Ln[3]);
-#pragma unroll
-        for (int o = LW / 2; o > 0; o >>= 1) mn = umin2(mn, __shfl_xor_sync(gmask, mn, o, LW));
-        m = min(mn & 0xffffu, mn >> 16);
-#pragma unroll
-        for (int j = 0; j < 4; j++) L[j] = Ln[j];
-        // ---- S ---------------------------------------------------------------------------------
-        if (active && acc) {
-            uint4 so;
-            if (a.first) {
-                so = make_uint4(Ln[0], Ln[1], Ln[2], Ln[3]);
-            } else {
-                so.x = uaddmin2(sq.x, Ln[0], 0x7fff7fffu);
-                so.y = uaddmin2(sq.y, Ln[1], 0x7fff7fffu);
-                so.z = uaddmin2(sq.z, Ln[2], 0x7fff7fffu);
-                so.w = uaddmin2(sq.w, Ln[3], 0x7fff7fffu);
-            }
-            *(uint4*)(a.S + off) = so;
-        }
-        // ---- advance ---------------------------------------------------------------------------
+        const size_t off = frameC + ((size_t)y * a.W1 + x) * a.Dp + gl * DPL;
+        int xn = x, yn = y;
         if (horizontal) {
-            x += sx;
+            xn += sx;
         } else {
-            y += sy;
-            x += sx;
-            if (x >= a.W1) x -= a.W1;
-            if (x < 0) x += a.W1;
+            yn += sy;
+            xn += sx;
+            if (xn >= a.W1) xn -= a.W1;
+            if (xn < 0) xn += a.W1;
         }
+        if (active && in_line) {
+            if (t + 1 < nsteps) load_regs_nc<NR>(c_ptr(xn, yn), Cn);
+            if (acc && !a.first) load_regs<NR>(a.S + off, Sq);
+        }
+        if (reset) sgm_reset<NR>(L, m);
+        sgm_step<LW, NR, true>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, a.quirk, d0);
+        // ---- S ---------------------------------------------------------------------------------
+        if (active && in_line && acc) {
+            unsigned So[NR];
+#pragma unroll
+            for (int j = 0; j < NR; j++) So[j] = a.first ? L[j] : uaddmin2(Sq[j], L[j], 0x7fff7fffu);
+            store_regs<NR>(a.S + off, So);
+        }
+        x = xn; y = yn;
     }
 }
 
-static void launch_one(const PathArgs& a, int B, cudaStream_t st) {
-    int LW = 2;
-    while (LW * 8 < a.Dp) LW *= 2;
-    const int nlines = (a.py == 0) ? a.H : a.W1 * a.sp.n;
+template <int LW, int NR>
+static void launch_path_t(const PathArgs& a, int B, int nlines, cudaStream_t st) {
     const int threads = 128;
-    dim3 grid((unsigned)(((size_t)nlines * LW + threads - 1) / threads), 1, B);
-    switch (LW) {
-        case 2: k_path<2><<<grid, threads, 0, st>>>(a); break;
-        case 4: k_path<4><<<grid, threads, 0, st>>>(a); break;
-        case 8: k_path<8><<<grid, threads, 0, st>>>(a); break;
-        case 16: k_path<16><<<grid, threads, 0, st>>>(a); break;
-        default: k_path<32><<<grid, threads, 0, st>>>(a); break;
+    const int per_cta = (threads / 32) * LaneGroup<LW>::RPW;
+    dim3 grid((unsigned)((nlines + per_cta - 1) / per_cta), 1, B);
+    k_path<LW, NR><<<grid, threads, 0, st>>>(a);
+}
+
+static void launch_one(const PathArgs& a, int B, cudaStream_t st) {
+    const int nlines = (a.py == 0) ? a.H : a.W1 * a.sp.n;
+    if (a.Dp > 64) {                       // 16 disparities per lane, the lane count follows D
+        switch ((a.Dp + 15) / 16) {
+            case 5: launch_path_t<5, 8>(a, B, nlines, st); break;
+            case 6: launch_path_t<6, 8>(a, B, nlines, st); break;
+            case 7: launch_path_t<7, 8>(a, B, nlines, st); break;
+            case 8: launch_path_t<8, 8>(a, B, nlines, st); break;
+            case 9: launch_path_t<9, 8>(a, B, nlines, st); break;
+            case 10: launch_path_t<10, 8>(a, B, nlines, st); break;
+            default: launch_path_t<16, 8>(a, B, nlines, st); break;
+        }
+        return;
+    }
+    switch ((a.Dp + 7) / 8) {              // 8 disparities per lane
+        case 1: case 2: launch_path_t<2, 4>(a, B, nlines, st); break;
+        case 3: launch_path_t<3, 4>(a, B, nlines, st); break;
+        case 4: launch_path_t<4, 4>(a, B, nlines, st); break;
+        case 5: launch_path_t<5, 4>(a, B, nlines, st); break;
+        case 6: launch_path_t<6, 4>(a, B, nlines, st); break;
+        case 7: launch_path_t<7, 4>(a, B, nlines, st); break;
+        default: launch_path_t<8, 4>(a, B, nlines, st); break;
     }
 }
 
