@@ -92,7 +92,7 @@ struct VertLayout {
     static constexpr int NFLD = VERT_UREG ? 4 : 5;
     static constexpr int OFF_A = 0, OFF_B = 2 * FLD, OFF_U = 4 * FLD, OFF_M = NFLD * FLD;
     static constexpr int REC = NFLD * FLD + 32;      // bytes per record
-    static constexpr int G = VT / LW;                // column groups per CTA
+    static constexpr int G = VT / 32 * LaneGroup<LW>::RPW;   // column groups per CTA (whole lane groups per warp, sgm_step.cuh)
 };
 
 // CL = true: the strip state is sized NC + 1 records instead of KIT * G + 1 and the surplus groups of the last column
@@ -106,7 +106,11 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
     cg::cluster_group cluster = cg::this_cluster();
     const int r = (int)cluster.block_rank();
     const int b = blockIdx.x / a.CS;
-    const int gl = threadIdx.x % LW, g = threadIdx.x / LW;
+    using LG = LaneGroup<LW>;
+    const int lane = threadIdx.x & 31;
+    const bool idle = !LG::POW2 && lane >= LG::USED;            // lanes beyond the warp's last whole group: no loads, no stores
+    const int gl = LG::POW2 ? (int)threadIdx.x % LW : (idle ? lane - LG::USED : lane % LW);
+    const int g = LG::POW2 ? (int)threadIdx.x / LW : ((int)threadIdx.x >> 5) * LG::RPW + (idle ? LG::RPW - 1 : lane / LW);
     const unsigned gmask = 0xffffffffu;
     const int x0 = r * a.NC;
     const int NCr = min(a.NC, a.W1 - x0);     // >= 1 by construction of CS / NC
@@ -135,7 +139,7 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
         if (has_right && a.H > 1) { mbar_expect_tx(barB, HALO_BYTES); if (a.H > 2) mbar_expect_tx(barB + 8, HALO_BYTES); }
     }
 
-    const bool active = PAD ? (gl * DPL < a.Dp) : true;
+    const bool active = (PAD ? (gl * DPL < a.Dp) : true) && !idle;
     unsigned pm[NR];
     make_padmask<NR>(pm, gl, a.D);
     const unsigned P1P1 = pk2((unsigned)a.P1), P2mP1 = (unsigned)(a.P2 - a.P1);
@@ -177,7 +181,7 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
         for (int k = 0; k < VERT_KMAX; k++) {
             if (k < KIT) {
                 const int i = k * G + g;
-                const bool valid = i < NCr;
+                const bool valid = i < NCr && !idle;
                 const int ro = CL ? min(k * G, lastrec) * REC : k * G * REC;   // CL: surplus groups shadow record NCr-1
                 unsigned char* const rb = tb + ro;
                 unsigned char* const rm = tm + ro;
@@ -190,11 +194,11 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
                     if (__any_sync(0xffffffffu, eL)) {
                         while (!mbar_try_wait(barA + 8 * P, ph)) {}
                         // re-arm the slot for row t+1 of the neighbour (row H-1 is never sent)
-                        if (eL && gl == 0 && t + 1 < a.H - 1) mbar_expect_tx(barA + 8 * P, HALO_BYTES);
+                        if (eL && gl == 0 && !idle && t + 1 < a.H - 1) mbar_expect_tx(barA + 8 * P, HALO_BYTES);
                     }
                     if (__any_sync(0xffffffffu, eR)) {
                         while (!mbar_try_wait(barB + 8 * P, ph)) {}
-                        if (eR && gl == 0 && t + 1 < a.H - 1) mbar_expect_tx(barB + 8 * P, HALO_BYTES);
+                        if (eR && gl == 0 && !idle && t + 1 < a.H - 1) mbar_expect_tx(barB + 8 * P, HALO_BYTES);
                     }
                 }
 #pragma unroll
@@ -432,7 +436,7 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     VertArgs a;
     a.C = C; a.S = S; a.H = e.H; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e;
     a.NC = cached.NC; a.CS = cached.CS; a.dy = dy; a.accumulate = accumulate; a.nosat = (sum_cannot_saturate(e) && e.D == LW * 2 * NR) ? 1 : 0;   // padded halves (0x7fff) must keep saturating
-    a.KIT = cached.KIT; a.nrec = cached.clamp ? cached.NC + 1 : cached.KIT * (cached.threads / LW) + 1;
+    a.KIT = cached.KIT; a.nrec = cached.clamp ? cached.NC + 1 : cached.KIT * (cached.threads / 32 * LaneGroup<LW>::RPW) + 1;   // G column groups per CTA
     const bool pad = e.D != LW * 2 * NR;
     cudaError_t le = (cached.threads == VERT_THREADS_WIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_WIDE>(cached, a, B, pad, st)
                    : (cached.threads == VERT_THREADS_XWIDE) ? launch_vert_vt<LW, NR, VERT_THREADS_XWIDE>(cached, a, B, pad, st)
@@ -455,12 +459,15 @@ int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int 
     if (disabled) return 1;
     if (e.Dp % 8 != 0 || e.Dp > 512) return 1;
     if ((size_t)e.H * e.W1 * e.Dp >= (1ull << 31)) return 1;   // 32-bit element offsets inside a frame
-    if (e.Dp > 64) {               // 16 disparities per lane
-        int LW = 8;
-        while (LW * 16 < e.Dp) LW *= 2;
-        switch (LW) {
+    if (e.Dp > 64) {               // 16 disparities per lane, the lane count follows D (sgm_step.cuh, LaneGroup)
+        switch ((e.Dp + 15) / 16) {
+            case 5: return launch_vert_t<5, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
+            case 6: return launch_vert_t<6, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
+            case 7: return launch_vert_t<7, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
             case 8: return launch_vert_t<8, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
-            case 16: return launch_vert_t<16, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
+            case 9: return launch_vert_t<9, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
+            case 10: return launch_vert_t<10, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
+            case 11: case 12: case 13: case 14: case 15: case 16: return launch_vert_t<16, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
             default: return launch_vert_t<32, 8>(e, B, C, S, dy, accumulate, st, clusters_out);
         }
     }

@@ -145,6 +145,22 @@ def test_baseline_config_shapes_vs_oracle(engine):
         _check(engine, L, R, stages=False, min_disp=0, num_disp=D, block_size=5, sgbm_mode="sgbm_3way")
 
 
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("D", [70, 89, 100, 140, 150])
+def test_lane_groups_follow_d(engine, mode, D):
+    """Disparity counts whose lane count is not a power of two (5, 6, 7, 9, 10 lanes of 16 disparities: a warp then
+    carries 6, 5, 4, 3, 3 lines instead of rounding up to 8 or 16 lanes): D = 140 is what example_stereo.py produces, 89
+    what the video path's re-scaling quirk yields. All four modes, every kernel family (cluster
+    kernel, generic line scan, row kernel), fused and debug flow with stage taps, against the oracle."""
+    L, R, _ = make_pair(40, D + 90, D, seed=4000 + D)
+    _check(engine, L, R, min_disp=0, num_disp=D, block_size=5, sgbm_mode=mode)
+    from depthestimation_b200 import _lib
+    engine.configure(min_disp=0, num_disp=D, block_size=5, sgbm_mode=mode)
+    engine.compute(L, R)
+    if mode in ("sgbm", "hh"):
+        assert engine.last_flow & _lib.FLOW_VERT_DOWN, "the cluster kernel must take these shapes, not the fallback"
+
+
 def _flows_agree(engine, H, W, D, mode, seed):
     """Size-independent property for shapes the scalar oracle cannot do in seconds: the product flow (cluster kernel +
     fused row kernel, S never materialised) and the debug flow (one generic kernel per direction + a selection kernel
