@@ -66,17 +66,18 @@ __device__ __forceinline__ unsigned grp_next(unsigned v, unsigned gmask) {
 
 template <int LW>
 __device__ __forceinline__ unsigned group_min2(unsigned v, unsigned gmask, const int gl = 0) {
-    if (LaneGroup<LW>::POW2) {
+    if constexpr (LaneGroup<LW>::POW2) {
 #pragma unroll
         for (int o = LW / 2; o > 0; o >>= 1) v = umin2(v, __shfl_xor_sync(gmask, v, o, LW));
         return v;
-    }
+    } else {
 #pragma unroll
-    for (int o = LaneGroup<LW>::P2 / 2; o > 0; o >>= 1) {
-        const unsigned t = __shfl_down_sync(0xffffffffu, v, o);
-        if (gl + o < LW) v = umin2(v, t);
+        for (int o = LaneGroup<LW>::P2 / 2; o > 0; o >>= 1) {
+            const unsigned t = __shfl_down_sync(0xffffffffu, v, o);
+            if (gl + o < LW) v = umin2(v, t);
+        }
+        return __shfl_sync(0xffffffffu, v, (int)(threadIdx.x & 31) - gl);   // group lane 0 holds the minimum
     }
-    return __shfl_sync(0xffffffffu, v, (int)(threadIdx.x & 31) - gl);   // group lane 0 holds the minimum
 }
 
 template <int NR>

@@ -67,7 +67,37 @@ __global__ void __launch_bounds__(256) k_ccl_tile(const int16_t* __restrict__ im
         const int len = (above ? __ffs(above) - 1 : 32) - lane;
         piece[k] = ((lane == 0 || !jl) && val[ly][lx] != newVal) ? len : 0;
     }
-    __syncthreads();
+    // Fast paths for the two common tiles of a disparity map: every pixel equal to newVal (nothing to label), and
+    // every pixel joined to its left and upper neighbour inside the tile (ONE component: a smooth surface). Both skip
+    // the union-find phases; the result is what they would produce (root = the tile's first pixel).
+    {
+        bool all_new = true, all_joined = (x0 + TW <= W && y0 + TH <= H);
+#pragma unroll
+        for (int k = 0; k < TH * TW / 256; k++) {
+            const int p = threadIdx.x + 256 * k;
+            const int lx = p % TW, ly = p / TW;
+            const int v = val[ly][lx];
+            all_new = all_new && (v == newVal);
+            all_joined = all_joined && (lx == 0 || joined(v, val[ly][lx - 1], newVal, maxDiff)) &&
+                         (ly == 0 || joined(v, val[ly - 1][lx], newVal, maxDiff)) && v != newVal;
+        }
+        // (the barrier reductions return a truth value, not a bitwise result: one per question)
+        const bool one = __syncthreads_and(all_joined ? 1 : 0) != 0;
+        const bool none = __syncthreads_and(all_new ? 1 : 0) != 0;
+        if (one || none) {
+#pragma unroll
+            for (int k = 0; k < TH * TW / 256; k++) {
+                const int p = threadIdx.x + 256 * k;
+                const int lx = p % TW, ly = p / TW, x = x0 + lx, y = y0 + ly;
+                if (x < W && y < H) {
+                    const size_t gi = frame + (size_t)y * W + x;
+                    lab[gi] = one ? (int)(frame + (size_t)y0 * W + x0) : -1;
+                    sizes[gi] = (one && p == 0) ? TH * TW : 0;
+                }
+            }
+            return;
+        }
+    }
     // vertical links; skipped when the left neighbour pair already carries the same link
     for (int p = threadIdx.x; p < TH * TW; p += 256) {
         int lx = p % TW, ly = p / TW;

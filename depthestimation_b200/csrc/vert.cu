@@ -45,6 +45,10 @@ struct VertArgs {
 #define VERT_THREADS_NARROW 288
 #define VERT_THREADS_XWIDE 576   // latency plan only: 72 column groups per CTA, so a 16-CTA cluster covers 1152 columns in ONE slot
 #define VERT_KMAX 4
+#ifndef VERT_PAIRSYNC
+#define VERT_PAIRSYNC 1   // 1: rows are ordered warp to neighbouring warp through progress counters; 0: one CTA barrier per row
+#endif
+#define VERT_TAIL_BYTES (4 * sizeof(unsigned long long) + 32 * sizeof(unsigned))   // 4 halo mbarriers + per-warp row counters
 #define VERT_MAX_DEVICES 64
 #ifndef VERT_UREG
 #define VERT_UREG 1   // 1: keep the vertical path's L in registers instead of shared memory
@@ -118,6 +122,16 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
 
     extern __shared__ __align__(16) unsigned char vsm[];
     unsigned long long* bars = (unsigned long long*)(vsm + (size_t)a.nrec * REC);   // [4]: halo A slot 0/1, halo B slot 0/1
+    // rows finished by every warp of the CTA. A column only exchanges L with the columns beside it, which belong to
+    // the same warp or to the warp before / after it (cyclically: a thread's next column slot continues at group 0),
+    // so a warp may start row t + 1 as soon as it and its two neighbours have finished row t: reads of row t - 1 data
+    // are over (the slot it overwrites) and row t data is there. Warps drift by a row against each other instead of
+    // all meeting at a CTA barrier per row (measured: 13 % of the stall samples were barrier waits, and the warps then
+    // hit the ALU pipe all at once).
+    unsigned* const done = (unsigned*)(bars + 4);
+    const int wid = (int)threadIdx.x >> 5, NWARP = VT / 32;
+    const unsigned done_l = smem_u32(done + (wid + NWARP - 1) % NWARP), done_r = smem_u32(done + (wid + 1) % NWARP), done_me = smem_u32(done + wid);
+    if (threadIdx.x < 32) done[threadIdx.x] = 0u;
     for (int i = threadIdx.x; i < a.nrec * (REC / 16); i += VT) ((uint4*)vsm)[i] = make_uint4(0u, 0u, 0u, 0u);
     unsigned char* const tb = vsm + g * REC + gl * 16;   // this thread's chunk 0 of field 0 of record g
     unsigned char* const tm = vsm + g * REC + OFF_M;     // minima of record g
@@ -291,7 +305,34 @@ __global__ void __launch_bounds__(VT, (VT <= 320 ? 2 : 1)) k_vert(const VertArgs
                 }
             }
         }
+#if VERT_PAIRSYNC == 2
+        // progress counters in shared memory polled by lane 0 (measured: 4x SLOWER, 7.8 -> 31.5 ms per 150 frames: the
+        // polling warps take the issue slots and the shared-memory port of the working ones)
+        __syncwarp();
+        if (lane == 0) {
+            const unsigned row1 = (unsigned)t + 1u;
+            unsigned v;
+            asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(done_me), "r"(row1) : "memory");
+            do { asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(done_l) : "memory"); } while (v < row1);
+            do { asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(done_r) : "memory"); } while (v < row1);
+        }
+        __syncwarp();
+#elif VERT_PAIRSYNC == 1
+        // row t complete in this warp: meet the two neighbouring warps on hardware barriers (one per pair of adjacent
+        // warps, ids 0..15: only for an even number of at most 16 warps, where the ring of pairs can be walked in two
+        // rounds without a cycle); otherwise the whole CTA
+        if constexpr (VT / 32 <= 16 && (VT / 32) % 2 == 0) {
+            constexpr int NW_ = VT / 32;
+            const int lo = (wid + NW_ - 1) % NW_;                       // pair (wid-1, wid) has id wid-1, pair (wid, wid+1) id wid
+            const int first = (wid & 1) ? lo : wid, second = (wid & 1) ? wid : lo;
+            asm volatile("bar.sync %0, 64;" ::"r"(first) : "memory");
+            asm volatile("bar.sync %0, 64;" ::"r"(second) : "memory");
+        } else {
+            __syncthreads();
+        }
+#else
         __syncthreads();   // row t complete in this CTA: ping-pong fields may flip (halos are ordered by the mbarriers)
+#endif
     };
     for (int t = 0; t < a.H; t += 2) {
         row(std::integral_constant<int, 0>{}, t);
@@ -348,10 +389,10 @@ static bool plan_vert(const Eff& e, VertPlan& best, bool latency = false) {
         if ((CS - 1) * NC >= e.W1) continue;                       // last strip would be empty
         int KIT = (NC + G - 1) / G;
         if (KIT > VERT_KMAX) continue;
-        size_t smem = (size_t)(KIT * G + 1) * VL::REC + 4 * sizeof(unsigned long long);   // a record per group and slot + the right halo
+        size_t smem = (size_t)(KIT * G + 1) * VL::REC + VERT_TAIL_BYTES;   // a record per group and slot + the right halo
         int clamp = 0;
         if (smem > 225 * 1024) {                                   // own columns + the right halo only (k_vert<.., CL = true>)
-            smem = (size_t)(NC + 1) * VL::REC + 4 * sizeof(unsigned long long);
+            smem = (size_t)(NC + 1) * VL::REC + VERT_TAIL_BYTES;
             clamp = 1;
         }
         if (smem > 225 * 1024) continue;

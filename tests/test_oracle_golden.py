@@ -42,3 +42,29 @@ def test_oracle_post_and_depth_match_reference(name, golden):
     assert np.array_equal(np.isinf(depth), np.isinf(ref))
     fin = np.isfinite(ref)
     assert np.allclose(depth[fin], ref[fin], rtol=1e-6, atol=0)
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_cv2_reference_pipeline_matches_reference(name, golden):
+    """The assembled cv2 pipeline that `bench.py --impl reference` and its cpu_baseline leg time
+    (oracle/cv2_reference.py::Cv2StereoPipeline) against what the reference's own StereoCore.estimate_depth produced for
+    the same inputs (tests/golden, recorded by tools/make_golden.py): rectified pair -> post-processed disparity bit for
+    bit, depth within 1e-6 relative. Pins the reference arm itself, not just its pieces."""
+    from oracle import cv2_reference as cr
+    if not cr.HAVE_CV2:
+        pytest.skip("cv2 not importable")
+    g = golden(name)
+    kw = golden_sgbm_kwargs(g)
+    pipe = cr.Cv2StereoPipeline(kw, calib=None, downscale=float(g["downscale"]), fast_mode=bool(int(g["fast"])),
+                                focal_length=float(g["focal_length"]), baseline=float(g["baseline"]),
+                                doffs=float(g["doffs"]), max_depth=golden_max_depth(g))
+    if "map1_L" in g:      # calibrated cases: the maps the reference built, raw frames in
+        pipe.maps = {k: g[k] for k in ("map1_L", "map2_L", "map1_R", "map2_R")}
+        disp, depth = pipe(g["left"], g["right"])
+    else:
+        disp, depth = pipe(g["left_rect"], g["right_rect"])
+    assert np.array_equal(disp, g["disp"]), f"{(disp != g['disp']).sum()} px differ"
+    ref = g["depth"]
+    assert np.array_equal(np.isinf(depth), np.isinf(ref))
+    fin = np.isfinite(ref)
+    assert np.allclose(depth[fin], ref[fin], rtol=1e-6, atol=0)
