@@ -236,7 +236,7 @@ int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch) {
     if (granule > cap) granule = 0;
     if (granule <= 0) { *batch = cap; return B200S_OK; }
     int b = granule;
-    while (b + granule <= cap) b += granule;   // largest multiple of the cluster granule within three row-kernel waves
+    while (b + granule <= cap) b += granule;   // largest multiple of the cluster granule within six row-kernel waves
     *batch = b;
     return B200S_OK;
 }

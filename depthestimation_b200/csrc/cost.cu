@@ -19,6 +19,7 @@
 // ------------------------------------------------------------------------------------------------
 // Four pixels per thread: the Sobel response and the raw sample are needed at x-1 .. x+4 (six columns, eight source
 // columns x-2 .. x+5 per row), each evaluated once instead of three times.
+#if COST_PART <= 0
 #define PF_ROWS 8   // rows per CTA (one row per CTA made a batch ~170 000 tiny CTAs: CTA launch rate bound)
 __global__ void __launch_bounds__(128) k_prefilter(const uint8_t* __restrict__ L, const uint8_t* __restrict__ R,
                                                    int H, int W, int ftzero, uint2* __restrict__ recL,
@@ -91,6 +92,8 @@ void launch_prefilter(const Eff& e, const uint8_t* L, const uint8_t* R, int B, u
     dim3 grid((e.W + 511) / 512, (e.H + PF_ROWS - 1) / PF_ROWS, 2 * B);
     k_prefilter<<<grid, 128, 0, st>>>(L, R, e.H, e.W, e.ftzero, recL, recR);
 }
+
+#endif  // COST_PART <= 0 (prefilter)
 
 // ------------------------------------------------------------------------------------------------
 // block cost
@@ -397,8 +400,13 @@ static int launch_cost_t(const CostArgs& a, int B, int nseg, cudaStream_t st) {
     return 0;
 }
 
+// Build partitioning (Makefile): the kernel instantiations of one block size each compile in their own translation
+// unit (-DCOST_PART=<block size>), the host side in part 0; without COST_PART everything is in this one file.
+#ifndef COST_PART
+#define COST_PART -1
+#endif
 template <int BS>
-static int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
+int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
     const int NT = a.Dp / 2;
     if (NT <= 16) return launch_cost_t<BS, 16>(a, B, nseg, st);
     if (NT <= 32) return launch_cost_t<BS, 32>(a, B, nseg, st);
@@ -413,6 +421,17 @@ static int launch_cost_bs(const CostArgs& a, int B, int nseg, cudaStream_t st) {
     return launch_cost_t<BS, 128>(a, B, nseg, st);
 }
 
+#if COST_PART > 0
+template int launch_cost_bs<COST_PART>(const CostArgs&, int, int, cudaStream_t);
+#else
+#if COST_PART == 0
+extern template int launch_cost_bs<1>(const CostArgs&, int, int, cudaStream_t);
+extern template int launch_cost_bs<3>(const CostArgs&, int, int, cudaStream_t);
+extern template int launch_cost_bs<5>(const CostArgs&, int, int, cudaStream_t);
+extern template int launch_cost_bs<7>(const CostArgs&, int, int, cudaStream_t);
+extern template int launch_cost_bs<9>(const CostArgs&, int, int, cudaStream_t);
+extern template int launch_cost_bs<11>(const CostArgs&, int, int, cudaStream_t);
+#endif
 int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uint2* recR, int B, uint16_t* C,
                 uint16_t* Calt, cudaStream_t st) {
     CostArgs a;
@@ -440,3 +459,4 @@ int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uin
         default: return -3;
     }
 }
+#endif  // COST_PART <= 0

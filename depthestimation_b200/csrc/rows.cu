@@ -548,7 +548,7 @@ static void launch_rows_k(const RowArgs& a, int grid, size_t smem, cudaStream_t 
 }
 
 template <int LW, int NR>
-static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
+void launch_rows_t(const RowArgs& a, cudaStream_t st) {
     constexpr int LINES = ROWS_THREADS / 32 * LaneGroup<LW>::RPW;
     const bool w3 = (a.mode == B200S_MODE_SGBM_3WAY) && (8 * (a.D / 8) > 0);
     const size_t smem = rows_smem<LW, NR>();
@@ -566,7 +566,7 @@ static void launch_rows_t(const RowArgs& a, cudaStream_t st) {
 }
 
 template <int LW, int NR>
-static int rows_capacity_t() {
+int rows_capacity_t() {
     constexpr int LINES = ROWS_THREADS / 32 * LaneGroup<LW>::RPW;
     const size_t smem = rows_smem<LW, NR>();
     cudaFuncSetAttribute(k_rows<LW, NR, true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -577,6 +577,103 @@ static int rows_capacity_t() {
     return nb * sms * LINES;
 }
 
+// Build partitioning (Makefile): the lane-group instantiations are spread over six translation units
+// (-DROWS_PART=1..6), the host side is part 0; without ROWS_PART everything is in this one file.
+#ifndef ROWS_PART
+#define ROWS_PART -1
+#endif
+#if ROWS_PART == 1
+template void launch_rows_t<2, 4>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<2, 4>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<2, 4>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<2, 4>();
+#endif
+#if ROWS_PART == 2
+template void launch_rows_t<4, 4>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<4, 4>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<4, 4>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<4, 4>();
+#endif
+#if ROWS_PART == 3
+template void launch_rows_t<8, 4>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<8, 4>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<8, 4>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<8, 4>();
+#endif
+#if ROWS_PART == 4
+template void launch_rows_t<16, 4>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<16, 4>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<16, 4>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<16, 4>();
+#endif
+#if ROWS_PART == 5
+template void launch_rows_t<32, 4>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<32, 4>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<32, 4>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<32, 4>();
+#endif
+#if ROWS_PART == 6
+template void launch_rows_t<5, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<5, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<5, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<5, 8>();
+#endif
+#if ROWS_PART == 1
+template void launch_rows_t<6, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<6, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<6, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<6, 8>();
+#endif
+#if ROWS_PART == 2
+template void launch_rows_t<7, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<7, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<7, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<7, 8>();
+#endif
+#if ROWS_PART == 3
+template void launch_rows_t<8, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<8, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<8, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<8, 8>();
+#endif
+#if ROWS_PART == 4
+template void launch_rows_t<9, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<9, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<9, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<9, 8>();
+#endif
+#if ROWS_PART == 5
+template void launch_rows_t<10, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<10, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<10, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<10, 8>();
+#endif
+#if ROWS_PART == 6
+template void launch_rows_t<16, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<16, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<16, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<16, 8>();
+#endif
+#if ROWS_PART == 1
+template void launch_rows_t<32, 8>(const RowArgs&, cudaStream_t);
+template int rows_capacity_t<32, 8>();
+#elif ROWS_PART == 0
+extern template void launch_rows_t<32, 8>(const RowArgs&, cudaStream_t);
+extern template int rows_capacity_t<32, 8>();
+#endif
+#if ROWS_PART <= 0
 // image rows the row kernel keeps in flight at once (one wave); a batch of B frames is B*H rows
 int rows_capacity_lines(const Eff& e) {
     if (e.Dp > 64) {
@@ -649,3 +746,4 @@ int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint
     }
     return 0;
 }
+#endif  // ROWS_PART <= 0

@@ -421,8 +421,8 @@ static cudaError_t launch_vert_vt(const VertPlan& pl, const VertArgs& a, int B, 
 }
 
 template <int LW, int NR>
-static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, int accumulate, cudaStream_t st,
-                         int* clusters_out) {
+int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, int accumulate, cudaStream_t st,
+                  int* clusters_out) {
     // the plan depends on (device, W1, Dp) only; the last one per device is cached. Several host threads (one handle per
     // thread, possibly on different GPUs) come through here: the cache is guarded and used through a local copy.
     struct Cache { VertPlan plan, lat; int W1 = -1, Dp = -1, sms = 0; bool ok = false, lat_ok = false; };
@@ -490,6 +490,68 @@ static int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, in
     return 0;
 }
 
+// Build partitioning (Makefile): the lane-group instantiations are spread over six translation units
+// (-DVERT_PART=1..6), the host side is part 0; without VERT_PART everything is in this one file.
+#ifndef VERT_PART
+#define VERT_PART -1
+#endif
+#define VERT_SIG const Eff&, int, const uint16_t*, uint16_t*, int, int, cudaStream_t, int*
+#if VERT_PART == 1
+template int launch_vert_t<2, 4>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<2, 4>(VERT_SIG);
+#endif
+#if VERT_PART == 2
+template int launch_vert_t<4, 4>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<4, 4>(VERT_SIG);
+#endif
+#if VERT_PART == 3
+template int launch_vert_t<8, 4>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<8, 4>(VERT_SIG);
+#endif
+#if VERT_PART == 4
+template int launch_vert_t<5, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<5, 8>(VERT_SIG);
+#endif
+#if VERT_PART == 5
+template int launch_vert_t<6, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<6, 8>(VERT_SIG);
+#endif
+#if VERT_PART == 6
+template int launch_vert_t<7, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<7, 8>(VERT_SIG);
+#endif
+#if VERT_PART == 1
+template int launch_vert_t<8, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<8, 8>(VERT_SIG);
+#endif
+#if VERT_PART == 2
+template int launch_vert_t<9, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<9, 8>(VERT_SIG);
+#endif
+#if VERT_PART == 3
+template int launch_vert_t<10, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<10, 8>(VERT_SIG);
+#endif
+#if VERT_PART == 4
+template int launch_vert_t<16, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<16, 8>(VERT_SIG);
+#endif
+#if VERT_PART == 5
+template int launch_vert_t<32, 8>(VERT_SIG);
+#elif VERT_PART == 0
+extern template int launch_vert_t<32, 8>(VERT_SIG);
+#endif
+#if VERT_PART <= 0
 // returns 0 when launched, 1 when the configuration does not fit this kernel (use the generic kernel), -1 when the
 // launch itself failed (a CUDA error the caller must report).
 // B == 0 only plans; *clusters_out = frames this kernel processes concurrently (preferred batch granule).
@@ -520,3 +582,4 @@ int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int 
         default: return launch_vert_t<8, 4>(e, B, C, S, dy, accumulate, st, clusters_out);
     }
 }
+#endif  // VERT_PART <= 0

@@ -258,7 +258,7 @@ int b200s_geometry(const B200sHandle* h, int W, int* W1, int* minX1, int* Dp, in
 int b200s_debug_stage(B200sHandle* h, int which, int b, int16_t* out);
 /* Batch size (frames per *_batch* call) that fills the GPU without a partial last wave for HxW images
  * under the current parameters: a multiple of the number of frames the cluster kernel keeps
- * co-resident, capped by one wave of the row kernel. A throughput hint, any B works. */
+ * co-resident, within six waves of the row kernel and 70 % of the free device memory. A throughput hint, any B works. */
 int b200s_preferred_batch(B200sHandle* h, int H, int W, int* batch);
 /* on != 0: run the matcher with the generic one-direction-per-launch kernels that materialise the
  * full aggregate S (needed for the S tap above; slower, same results). Default off: horizontal
