@@ -31,7 +31,14 @@ struct RowArgs {
     int H, W, W1, D, Dp, P1, P2, minD, minX1, maxX1, INV, ue, d12e, mode, nck, nlines, nosat;
 };
 
+#ifndef ROWS_PF_L1
+#define ROWS_PF_L1 0
+#endif
+#if ROWS_PF_L1
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+#else
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#endif
 #ifndef ROW_PD
 #define ROW_PD 12  // pass-1 L2 prefetch distance in columns (measured: 3 -> 72.8, 6 -> 67.9, 12 -> 66.2, 18 -> 66.6, 24 -> 67.1 us per frame)
 #endif
