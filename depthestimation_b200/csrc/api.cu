@@ -70,6 +70,8 @@ struct B200sHandle {
         int rc = 0;
     } slot[NSLOT];
     cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaStream_t s_aux = nullptr;                       // second kernel queue of small calls (row kernel pass 1 beside the vertical kernels)
+    cudaEvent_t ev_cost = nullptr, ev_p1 = nullptr;
     unsigned next_ticket = 0;
     // submit and wait may come from two host threads (a producer that uploads and enqueues, a consumer that waits and
     // drains): the slot bookkeeping is guarded, the blocking event wait itself runs outside the lock
@@ -158,6 +160,9 @@ int b200s_create(int device, const B200sParams* p, B200sHandle** out) {
     cudaEventCreate(&h->ev1);
     cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&h->s_aux, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&h->ev_cost, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_p1, cudaEventDisableTiming);
     for (B200sHandle::Slot& sl : h->slot) {
         cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&sl.compute_done, cudaEventDisableTiming);
@@ -188,6 +193,9 @@ int b200s_destroy(B200sHandle* h) {
         if (sl.compute_done) cudaEventDestroy(sl.compute_done);
         if (sl.out_done) cudaEventDestroy(sl.out_done);
     }
+    if (h->s_aux) { cudaStreamSynchronize(h->s_aux); cudaStreamDestroy(h->s_aux); }
+    if (h->ev_cost) cudaEventDestroy(h->ev_cost);
+    if (h->ev_p1) cudaEventDestroy(h->ev_p1);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -344,14 +352,30 @@ static int dev_sgbm(B200sHandle* h, const uint8_t* dL, const uint8_t* dR, int B,
         launch_wta(e, B, h->S.as<uint16_t>(), h->raw.as<int16_t>(), h->stream);
         h->launches++;
     } else {
+        CUDA_TRY(h, h->ck.ensure(rows_ck_bytes(e, B)));
+        CUDA_TRY(h, h->keys.ensure(npx * sizeof(unsigned)));
+        // Few lines per call: the row kernel's first pass (C -> checkpoints of the right-to-left scan) needs nothing from
+        // the vertical kernels, so it runs beside them on a second stream; its second pass follows both.
+        // (sgbm / hh only: their vertical cluster kernel is long enough to hide it. Measured, one KITTI pair: sgbm 1.81 ->
+        // 1.67 ms; sgbm_3way, whose vertical pass is 0.1 ms, 1.43 -> 1.48 ms with the split, so it keeps one launch)
+        const bool split = rows_small_call(e, B) && h->s_aux && h->ev_cost && h->ev_p1 &&
+                           (e.mode == B200S_MODE_SGBM || e.mode == B200S_MODE_HH);
+        if (split) {
+            CUDA_TRY(h, cudaEventRecord(h->ev_cost, h->stream));
+            CUDA_TRY(h, cudaStreamWaitEvent(h->s_aux, h->ev_cost, 0));
+            rc = launch_rows(e, B, h->C.as<uint16_t>(), h->S.as<uint16_t>(), h->ck.as<uint16_t>(), h->keys.as<unsigned>(),
+                             h->raw.as<int16_t>(), h->s_aux, 1);
+            if (rc) { h->set_error(B200S_E_INVALID, "row kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
+            CUDA_TRY(h, cudaEventRecord(h->ev_p1, h->s_aux));
+            h->launches++;
+        }
         rc = launch_paths(e, sp, B, h->C.as<uint16_t>(), h->Calt.as<uint16_t>(), h->S.as<uint16_t>(), h->stream, &h->launches, 1, &h->last_flow);
         if (rc == -4) { h->set_error(B200S_E_CUDA, "vertical cluster kernel: planned but the launch failed on device %d (see stderr)", h->device); return B200S_E_CUDA; }
         if (rc) { h->set_error(B200S_E_INVALID, "path kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
         mark(h, B200S_STAGE_PATHS);
-        CUDA_TRY(h, h->ck.ensure(rows_ck_bytes(e, B)));
-        CUDA_TRY(h, h->keys.ensure(npx * sizeof(unsigned)));
+        if (split) CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->ev_p1, 0));
         rc = launch_rows(e, B, h->C.as<uint16_t>(), h->S.as<uint16_t>(), h->ck.as<uint16_t>(), h->keys.as<unsigned>(),
-                         h->raw.as<int16_t>(), h->stream);
+                         h->raw.as<int16_t>(), h->stream, split ? 2 : 0);
         if (rc) { h->set_error(B200S_E_INVALID, "row kernel: unsupported configuration (%d)", rc); return B200S_E_INVALID; }
         h->launches++;
         h->last_flow |= B200S_FLOW_ROWS_FUSED;

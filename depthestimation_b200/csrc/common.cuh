@@ -109,8 +109,11 @@ int launch_vert_family(const Eff& e, int B, const uint16_t* C, uint16_t* S, int 
 // fused horizontal paths + winner selection (rows.cu): C', Sv -> raw disparity
 size_t rows_ck_bytes(const Eff& e, int B);
 int rows_capacity_lines(const Eff& e);
+// phase 0: both passes in one launch; 1: pass 1 only (C -> checkpoints); 2: pass 2 only
 int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,
-                cudaStream_t st);
+                cudaStream_t st, int phase);
+// few lines per call (a single pair): the call is bound by one line's serial chain, not by throughput
+int rows_small_call(const Eff& e, int B);
 void launch_wta(const Eff& e, int B, const uint16_t* S, int16_t* raw, cudaStream_t st);
 void launch_median3_s16(const int16_t* src, int16_t* dst, int B, int H, int W, cudaStream_t st);
 // speckle filter (B.3) in place; labels/sizes are int32 scratch of B*H*W each

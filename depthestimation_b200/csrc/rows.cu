@@ -29,6 +29,7 @@ struct RowArgs {
     unsigned* keys;    // right-view candidates [B*H][W]
     int16_t* raw;      // [B*H][W]
     int H, W, W1, D, Dp, P1, P2, minD, minX1, maxX1, INV, ue, d12e, mode, nck, nlines, nosat;
+    int phase;         // 0: both passes; 1: pass 1 only (C -> checkpoints, needs no Sv); 2: pass 2 only (checkpoints are there)
 };
 
 #ifndef ROWS_PF_L1
@@ -137,7 +138,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
     unsigned* keys = a.keys + (size_t)line * a.W;
     int16_t* out = a.raw + (size_t)line * a.W;
 
-    if (valid)
+    if (valid && a.phase != 1)
         for (int x = gl; x < a.W; x += LW) { keys[x] = 0xffffffffu; out[x] = (int16_t)a.INV; }
     __syncwarp();
 
@@ -157,8 +158,10 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
     auto ldC = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Crow + (size_t)x * Dp, dst, pol_first); };
     auto ldS = [&](const int x, unsigned (&dst)[NR]) { if (active) load_regs_pol<NR>(Srow + (size_t)x * Dp, dst, pol_first); };
     // ---- pass 1: <- over the row down to column r0, checkpoint L at every chunk start -------------------
+    // (a.phase, uniform: with few lines per call the two passes are two launches, and pass 1, which needs only C,
+    // runs beside the vertical kernels on a second stream)
     sgm_reset<NR>(L, m);
-    {
+    if (a.phase != 2) {
         // W1 - r0 is a multiple of ROW_K: the pass runs whole groups of ROW_K columns, each ending on a checkpoint
         // column, so neither the ring position nor the checkpoint test depends on x
         auto step1 = [&](const unsigned (&Cc)[NR]) { sgm_step<LW, NR, PAD>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0); };
@@ -190,6 +193,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
             if (active && valid) store_regs<NR>(pck, L);
         }
     }
+    if (a.phase == 1) return;
     __syncwarp();
     // ---- pass 2: chunk by chunk, left to right ------------------------------------------------------
     unsigned Lr[NR];   // L(->)
@@ -705,9 +709,23 @@ size_t rows_ck_bytes(const Eff& e, int B) {
     return (size_t)B * e.H * nck * e.Dp * sizeof(uint16_t);
 }
 
+int rows_small_call(const Eff& e, int B) {
+    static int small_env = -1;
+    if (small_env < 0) { const char* v = getenv("B200S_ROWS_SMALL"); small_env = v ? atoi(v) : 2; }   // 0 never, 1 always, 2 auto
+    if (!small_env) return 0;
+    if (small_env == 1) return 1;
+    int sms = 0, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long nlines = (long long)B * e.H;
+    const long long warps = (e.Dp <= 128) ? (nlines + 1) / 2 : nlines;
+    return warps <= 4LL * sms;
+}
+
 int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,
-                cudaStream_t st) {
+                cudaStream_t st, int phase) {
     RowArgs a;
+    a.phase = phase;
     a.C = C; a.Sv = Sv; a.ck = ck; a.keys = keys; a.raw = raw;
     a.H = e.H; a.W = e.W; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e; a.minD = e.minD;
     a.minX1 = e.minX1; a.maxX1 = e.maxX1; a.INV = e.INV; a.ue = e.ue; a.d12e = e.d12e; a.mode = e.mode;
@@ -719,17 +737,9 @@ int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint
     // length of one line's serial scan, which a lane group issues at well under one instruction per clock. Twice the
     // lanes per line with half the registers each halves the instructions on that critical path (and costs ~1.5x the
     // issue slots per line, which is why full batches keep 16 disparities per lane).
-    static int small_env = -1;
-    if (small_env < 0) { const char* v = getenv("B200S_ROWS_SMALL"); small_env = v ? atoi(v) : 2; }   // 0 never, 1 always, 2 auto
-    if (e.Dp > 64 && e.Dp <= 256 && small_env) {
-        int sms = 0, dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        const long long warps = (e.Dp <= 128) ? (a.nlines + 1) / 2 : a.nlines;
-        if (small_env == 1 || warps <= 4LL * sms) {
-            if (e.Dp <= 128) launch_rows_t<16, 4>(a, st); else launch_rows_t<32, 4>(a, st);
-            return 0;
-        }
+    if (e.Dp > 64 && e.Dp <= 256 && rows_small_call(e, B)) {
+        if (e.Dp <= 128) launch_rows_t<16, 4>(a, st); else launch_rows_t<32, 4>(a, st);
+        return 0;
     }
     if (e.Dp > 64) {             // 16 disparities per lane; the lane count follows D (a warp carries 32 / LW lines)
         switch ((e.Dp + 15) / 16) {

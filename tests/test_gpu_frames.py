@@ -339,3 +339,25 @@ def test_rectify_images_uncached_rebuilds_maps_on_gpu(engine):
                             cal["dist_coeff_R"], alpha=1.0, engine=engine)
     wl, wr = cr.rectify_pair(L, R, cr.build_maps(cal, alpha=1.0))
     assert np.array_equal(gl, wl) and np.array_equal(gr, wr)
+
+
+def test_video_generator_in_memory_sources():
+    """Two lists of frames as sources (no capture object): same depth maps, in order, as the frame-by-frame core; the
+    chunk size is derived from the known length (at least two chunks per GPU)."""
+    from depthestimation_b200.depthlib import StereoCore, StereoDepthEstimatorVideo
+    H, W, D = 48, 176, 32
+    pairs = [make_pair(H, W, D, seed=3500 + k)[:2] for k in range(11)]
+    lefts = [np.stack([l] * 3, -1) for l, _ in pairs]
+    rights = [np.stack([r] * 3, -1) for _, r in pairs]
+    cfg = dict(num_disp=D, sgbm_mode="hh4", focal_length=0.8 * W, baseline=0.54)
+    core = StereoCore()
+    core.configure_sgbm(**cfg)
+    expect = [core.estimate_depth(l, r)[1] for l, r in zip(lefts, rights)]
+    vid = StereoDepthEstimatorVideo(lefts, rights, target_fps=0, devices=[0])
+    vid.configure_sgbm(**cfg)
+    for _ in range(2):                       # second pass reuses the cached worker (engine, page-locked buffers)
+        got = list(vid.estimate_depth())
+        assert len(got) == len(expect)
+        for a, b in zip(got, expect):
+            assert np.array_equal(a, b)
+    assert len(vid._worker_pool[0]) == 1
