@@ -443,7 +443,11 @@ int launch_cost(const Eff& e, const StripePlan& sp, const uint2* recL, const uin
     // rows per segment: every segment re-computes SH2 rows above and below it, so long segments are cheaper per row
     // (measured, KITTI batch: 32 -> 54.5, 64 -> 51.7, 128 -> 50.3 us per frame) as long as the grid still fills the GPU
     a.RS = 64;
-    if ((long long)((e.W1 + COST_XT - 1) / COST_XT) * ((e.H + 127) / 128) * B >= 32LL * 148) a.RS = 128;
+    const long long strips = (long long)((e.W1 + COST_XT - 1) / COST_XT) * B;
+    if (strips * ((e.H + 127) / 128) >= 32LL * 148) a.RS = 128;
+    // a single pair (or a few small frames): shorter segments, so that there are several CTAs per SM to overlap
+    // (one KITTI pair: 336 CTAs of 2 warps on 148 SMs at 64 rows per segment)
+    else if (strips * ((e.H + 63) / 64) < 8LL * 148) a.RS = (strips * ((e.H + 31) / 32) < 8LL * 148) ? 16 : 32;
     if (rs_env > 0) a.RS = rs_env;
     a.nreg = (e.H + a.RS - 1) / a.RS;
     a.sp = sp;
