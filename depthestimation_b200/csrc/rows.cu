@@ -87,8 +87,13 @@ struct RowGeom {
 // W3 = true: sgbm_3way's selection rule (the binary's 8-wide SIMD minimum + scalar tail, A.7); false: A.6.
 // NS: the sum of all paths cannot reach 32768, plain adds instead of saturating ones.
 template <int LW, int NR, bool PAD, bool W3, bool NS>
-__global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs a) {
+__global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS_MINB) k_rows(const RowArgs a) {
     constexpr int DPL = 2 * NR;
+    // The small-call instantiations (8 disparities per lane on 16 / 32 lanes: few lines in flight, each line's serial
+    // chain IS the run time) load a whole phase ahead: while a chunk's <- re-scan runs, its six Sv columns are in
+    // flight, while its -> scan runs, the six C columns of the next chunk are (two sets of ROW_K x NR registers; ncu of
+    // one pair per call had 39 % of the stall samples on the first use of a column that was requested two steps before).
+    constexpr bool DEEP = (NR == 4 && LW >= 16);
     using LG = LaneGroup<LW>;
     constexpr int RPW = LG::RPW;                    // lines per warp
     constexpr int NCH = LW * NR / 4;                // 16-byte units per pixel record (all disparities of one pixel)
@@ -168,10 +173,34 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         int x = a.W1 - 1;
         const uint16_t* pC = Crow + (size_t)x * Dp;                                   // C of column x
         uint16_t* pck = ck + (size_t)((x - (ROW_K - 1) - r0) / ROW_K + 1) * Dp;       // checkpoint of the group that starts at x
-        if (x >= r0 && active) {
+        if (!DEEP && x >= r0 && active) {
             load_regs_pol<NR>(pC, X0, pol_first);
             load_regs_pol<NR>(pC - Dp, X1, pol_first);
         }
+        if constexpr (DEEP) {
+            unsigned G0[ROW_K][NR], G1[ROW_K][NR];                                    // this group's columns / the next group's
+#pragma unroll
+            for (int i = 0; i < ROW_K; i++)
+#pragma unroll
+                for (int j = 0; j < NR; j++) { G0[i][j] = 0u; G1[i][j] = 0u; }
+            if (x >= r0 && active) {
+#pragma unroll
+                for (int i = 0; i < ROW_K; i++) load_regs_pol<NR>(pC - (size_t)i * Dp, G0[i], pol_first);
+            }
+            for (; x >= r0; x -= ROW_K, pC -= (size_t)ROW_K * Dp, pck -= Dp) {
+                if (active && x - ROW_K >= r0) {
+#pragma unroll
+                    for (int i = 0; i < ROW_K; i++) load_regs_pol<NR>(pC - (size_t)(ROW_K + i) * Dp, G1[i], pol_first);
+                }
+#pragma unroll
+                for (int i = 0; i < ROW_K; i++) step1(G0[i]);
+                if (active && valid) store_regs<NR>(pck, L);
+#pragma unroll
+                for (int i = 0; i < ROW_K; i++)
+#pragma unroll
+                    for (int j = 0; j < NR; j++) G0[i][j] = G1[i][j];
+            }
+        } else
         for (; x >= r0; x -= ROW_K, pC -= (size_t)ROW_K * Dp, pck -= Dp) {
             const bool more = x - ROW_K >= r0;                                        // another group follows
 #pragma unroll
@@ -454,8 +483,10 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         __syncwarp();
         if (r0 < a.W1) {   // set up chunk 1: its checkpoint and its first two <- columns
             fetch_ck(r0 + ROW_K);
-            ldC(r0 + ROW_K - 1, X0);
-            ldC(r0 + ROW_K - 2, X1);
+            if (!DEEP) {
+                ldC(r0 + ROW_K - 1, X0);
+                ldC(r0 + ROW_K - 2, X1);
+            }
         }
         for (int x = 0; x < r0; x++) {
             ldS(x, X2);
@@ -464,6 +495,36 @@ __global__ void __launch_bounds__(ROWS_THREADS, ROWS_MINB) k_rows(const RowArgs 
         select_chunk(0, r0);
         __syncwarp();
     }
+    if constexpr (DEEP) {
+        unsigned XC[ROW_K][NR], XS[ROW_K][NR];
+#pragma unroll
+        for (int i = 0; i < ROW_K; i++)
+#pragma unroll
+            for (int j = 0; j < NR; j++) { XC[i][j] = 0u; XS[i][j] = 0u; }
+        if (r0 < a.W1) {
+#pragma unroll
+            for (int i = 0; i < ROW_K; i++) ldC(r0 + ROW_K - 1 - i, XC[i]);       // <- order of the first full chunk
+        }
+        for (int xs = r0; xs < a.W1; xs += ROW_K) {
+            const int xe = xs + ROW_K;
+            start_from_ck(xe);
+            prefetch_chunk(xe + (ROWS_PFC - 1) * ROW_K);
+#pragma unroll
+            for (int i = 0; i < ROW_K; i++) ldS(xs + i, XS[i]);                   // this chunk's Sv, needed after the re-scan
+#pragma unroll
+            for (int i = 0; i < ROW_K; i++) stepb(xe - 1 - i, xs, XC[i]);
+            __syncwarp();
+            if (xe < a.W1) {
+                fetch_ck(xe + ROW_K);
+#pragma unroll
+                for (int i = 0; i < ROW_K; i++) ldC(xe + ROW_K - 1 - i, XC[i]);   // the next chunk's C, needed after the -> scan
+            }
+#pragma unroll
+            for (int i = 0; i < ROW_K; i++) stepf(xs + i, xs, XS[i]);
+            select_chunk(xs, ROW_K);
+            __syncwarp();
+        }
+    } else
     for (int xs = r0; xs < a.W1; xs += ROW_K) {
         // full chunk [xs, xe): X0 = C(xe-1), X1 = C(xe-2) and L = checkpoint(xe) were requested a phase ago
         const int xe = xs + ROW_K;
