@@ -780,7 +780,10 @@ int rows_small_call(const Eff& e, int B) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const long long nlines = (long long)B * e.H;
     const long long warps = (e.Dp <= 128) ? (nlines + 1) / 2 : nlines;
-    return warps <= 4LL * sms;
+    // measured (KITTI pairs per call, small / regular variant, pairs/s): sgbm 4: 2330 / 1841, 8: 3690 / 3078, 12: 4630 / 4104,
+    // 16: 3904 / 3880; sgbm_3way 4: 2428 / 2076, 8: 3577 / 3234, 12: 3446 / 4064
+    const bool vertical_cluster = (e.mode == B200S_MODE_SGBM || e.mode == B200S_MODE_HH);   // pass 1 then hides beside it
+    return warps <= (vertical_cluster ? 16LL : 11LL) * sms;
 }
 
 int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,
