@@ -33,8 +33,27 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", default="1,2,4,8")
     ap.add_argument("--only", default="")
+    ap.add_argument("--isolate", type=int, default=1, help="1: every (job, N) in a process of its own (no engines, page-locked "
+                    "buffers or host threads left over from the previous configuration)")
     a = ap.parse_args()
     ndev = torch.cuda.device_count()
+    if a.isolate:
+        import subprocess
+        for name in [n for n in a.only.split(",") if n] or list(JOBS):
+            base = None
+            for n in [int(g) for g in a.gpus.split(",")]:
+                if n > ndev:
+                    continue
+                out = subprocess.run([sys.executable, __file__, "--isolate", "0", "--only", name, "--gpus", str(n)],
+                                     capture_output=True, text=True).stdout.strip().splitlines()
+                if not out:
+                    continue
+                d = json.loads(out[-1])
+                base = base or d["seconds"]
+                d["speedup_vs_1gpu"] = round(base / d["seconds"], 2)
+                d.pop("first_frame_equals_1gpu", None)
+                print(json.dumps(d), flush=True)
+        return
     for name in [n for n in a.only.split(",") if n] or list(JOBS):
         H, W, D, nframes, cn, chunk = JOBS[name]
         distinct = []
