@@ -22,6 +22,7 @@
 
 #include <mutex>
 #include <type_traits>
+#include <vector>
 
 #include "sgm_step.cuh"
 
@@ -363,7 +364,7 @@ static cudaLaunchConfig_t vert_cfg(int threads, int CS, int B, size_t smem, cuda
 // CTA ~24 ALU-pipe cycles per column and direction, so one KITTI frame on 9 SMs is bound by those 9 SMs' issue rate
 // (measured: 831 us per frame at one frame per call against 53 us per frame in a full batch).
 template <int LW, int NR, int VT>
-static bool plan_vert(const Eff& e, VertPlan& best, bool latency = false) {
+static bool plan_vert(const Eff& e, VertPlan& best, bool latency = false, std::vector<VertPlan>* all = nullptr) {
     using VL = VertLayout<LW, NR, VT>;
     constexpr int G = VL::G;
     // function attributes are per DEVICE: opt every device in once (a process may drive several GPUs from several threads)
@@ -407,6 +408,7 @@ static bool plan_vert(const Eff& e, VertPlan& best, bool latency = false) {
             // one CTA per SM: two narrow CTAs of a cluster sharing an SM would share its issue slots again
             if (smem < 116 * 1024) smem = 116 * 1024;
         }
+        if (all) { VertPlan p; p.score = score; p.CS = CS; p.NC = NC; p.KIT = KIT; p.smem = smem; p.clusters = ncl; p.threads = VT; p.clamp = clamp; all->push_back(p); }
         if (score > best.score) { best.score = score; best.CS = CS; best.NC = NC; best.KIT = KIT; best.smem = smem; best.clusters = ncl; best.threads = VT; best.clamp = clamp; }
     }
     return best.score > 0.0;
@@ -425,7 +427,7 @@ int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, i
                   int* clusters_out) {
     // the plan depends on (device, W1, Dp) only; the last one per device is cached. Several host threads (one handle per
     // thread, possibly on different GPUs) come through here: the cache is guarded and used through a local copy.
-    struct Cache { VertPlan plan, lat; int W1 = -1, Dp = -1, sms = 0; bool ok = false, lat_ok = false; };
+    struct Cache { VertPlan plan, lat; std::vector<VertPlan> all; int W1 = -1, Dp = -1, sms = 0; bool ok = false, lat_ok = false; };
     static Cache cache[VERT_MAX_DEVICES];
     static std::mutex mu;
     int dev = 0;
@@ -439,8 +441,9 @@ int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, i
             static int vt_env = -1;
             if (vt_env < 0) { const char* v = getenv("B200S_VERT_VT"); vt_env = v ? atoi(v) : 0; }
             VertPlan wide, narrow;
-            const bool okw = (vt_env == 0 || vt_env == VERT_THREADS_WIDE) && plan_vert<LW, NR, VERT_THREADS_WIDE>(e, wide);
-            const bool okn = (vt_env == 0 || vt_env == VERT_THREADS_NARROW) && plan_vert<LW, NR, VERT_THREADS_NARROW>(e, narrow);
+            c.all.clear();
+            const bool okw = (vt_env == 0 || vt_env == VERT_THREADS_WIDE) && plan_vert<LW, NR, VERT_THREADS_WIDE>(e, wide, false, &c.all);
+            const bool okn = (vt_env == 0 || vt_env == VERT_THREADS_NARROW) && plan_vert<LW, NR, VERT_THREADS_NARROW>(e, narrow, false, &c.all);
             c.ok = okw || okn;
             if (c.ok) c.plan = (okn && (!okw || narrow.score > wide.score)) ? narrow : wide;
             VertPlan xwide;
@@ -462,6 +465,15 @@ int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, i
         }
         cached = c.plan;
         cok = c.ok;
+        // The throughput plan maximises frames in flight per column slot, which is right when the call fills whole waves of
+        // clusters. A call whose frame count is not a multiple of the co-resident cluster count pays a whole extra wave
+        // for the remainder (16 KITTI pairs on 15 co-resident clusters: two waves): take the plan with the fewest
+        // (waves x column slots per thread) for THIS frame count, the throughput score breaking ties.
+        if (cok && B > 0 && B % c.plan.clusters != 0) {
+            auto cost = [&](const VertPlan& p) { return (double)((B + p.clusters - 1) / p.clusters) * p.KIT * (p.clamp ? 1.25 : 1.0); };
+            for (const VertPlan& p : c.all)
+                if (cost(p) < cost(cached) - 1e-9 || (cost(p) < cost(cached) + 1e-9 && p.score > cached.score)) cached = p;
+        }
         static int lat_env = -1;
         if (lat_env < 0) { const char* v = getenv("B200S_VERT_LATENCY"); lat_env = v ? atoi(v) : 1; }
         // few frames in the call (at most half the SMs busy even with the widest clusters) and a latency plan that

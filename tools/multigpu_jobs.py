@@ -33,8 +33,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", default="1,2,4,8")
     ap.add_argument("--only", default="")
-    ap.add_argument("--isolate", type=int, default=1, help="1: every (job, N) in a process of its own (no engines, page-locked "
-                    "buffers or host threads left over from the previous configuration)")
+    ap.add_argument("--isolate", type=int, default=0, help="1: every (job, N) in a process of its own (no engines, page-locked "
+                    "buffers or host threads left over from the previous configuration; costs a start-up per configuration: "
+                    "minutes of an 8-GPU box)")
     a = ap.parse_args()
     ndev = torch.cuda.device_count()
     if a.isolate:
@@ -91,12 +92,17 @@ def main():
             if base is None:
                 base, ref = t, first
             same = bool(np.array_equal(first, ref))
+            for ws in getattr(vid, "_worker_pool", {}).values():     # give the device scratch and page-locked buffers back
+                for w in ws:
+                    w.eng.close()
             print(json.dumps({"job": name, "shape": f"{W}x{H}", "D": D, "mode": "sgbm_3way", "frames": nframes, "channels": cn,
                               "n_gpus": n, "seconds": round(t, 4), "frames_per_s": round(nframes / t, 1),
                               "speedup_vs_1gpu": round(base / t, 2), "first_frame_equals_1gpu": same,
                               "api": "StereoDepthEstimatorVideo(devices=[0..N-1]) generator, in-memory frame sources, depth plane only"}),
                   flush=True)
             del vid
+            import gc
+            gc.collect()
 
 
 if __name__ == "__main__":
