@@ -302,7 +302,7 @@ def test_no_silent_host_fallbacks():
 def test_build_maps_matches_oracle_and_cv2(engine):
     """b200s_build_maps (cv2.initUndistortRectifyMap on the GPU, double precision, no contraction): bit-exact against the
     numpy restatement for every calibration model, and against cv2 itself up to the documented one-ulp flips of its
-    AVX2 path (at most one value per map pair; none on the synthetic and the rotated / translated rig)."""
+    SIMD column accumulation (at most one value per map pair; none on the synthetic and the rotated / translated rig)."""
     cv2 = pytest.importorskip("cv2")
     from oracle import maps as om
     cases = om.calibration_cases()

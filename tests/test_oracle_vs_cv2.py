@@ -135,8 +135,8 @@ def test_resize_linear_matches_cv2():
 def test_maps_oracle_matches_cv2():
     """oracle/maps.py (numpy restatement of cv2.initUndistortRectifyMap, depthlib/rectify.py:68-73) against the live
     binary: five calibrations (synthetic, rotated / translated rig, 8-, 12- and 14-coefficient models), alpha 0 and 1.
-    cv2's AVX2 path walks the columns four at a time with fused multiply-adds; the restatement evaluates every pixel
-    directly without contraction. Over 157 M map values of the builder's survey 9 differed, each by one float32 ulp:
+    cv2's dispatched SIMD path accumulates the column coordinate several columns at a time (eight on an AVX-512 host); the
+    restatement evaluates every pixel directly. Over 157 M map values of the builder's survey 9 differed, each by one float32 ulp:
     the bar here is at most one value per map pair, by at most one ulp, and none on the two standard cases."""
     import cv2
     from oracle import maps as om
