@@ -168,6 +168,51 @@ def test_threaded_sharder_order_and_failover():
         list(ThreadedSharder([0, 1], all_fail, chunk=2).run(iter(frames)))
 
 
+def test_threaded_sharder_async_workers_ramp_and_failover():
+    """The submit / wait worker protocol the video generator uses (several chunks in flight per GPU, chunks handed over as
+    lists of frames, ramped-up first chunks, depth-only results): frame order, chunk sizes, in-flight bound, and a worker
+    that dies with chunks in flight hands all of them to the survivors."""
+    import threading
+    import time as _time
+    from depthestimation_b200.sharding import ThreadedSharder
+    frames = [(np.full((2, 3), i, np.uint8), np.full((2, 3), 200 - i, np.uint8)) for i in range(61)]
+    lock = threading.Lock()
+    sizes, peak = [], {}
+
+    class Worker:
+        max_inflight = 3
+
+        def __init__(self, dev, fail_after=None):
+            self.dev, self.fly, self.n, self.fail_after = dev, 0, 0, fail_after
+
+        def submit(self, Ls, Rs):
+            assert isinstance(Ls, list) and len(Ls) == len(Rs)
+            with lock:
+                sizes.append(len(Ls))
+                self.fly += 1
+                self.n += 1
+                peak[self.dev] = max(peak.get(self.dev, 0), self.fly)
+            if self.fail_after is not None and self.n > self.fail_after:
+                raise RuntimeError("injected failure with chunks in flight")
+            return np.stack(Rs).astype(np.float32)
+
+        def wait(self, token):
+            _time.sleep(0.002)
+            with lock:
+                self.fly -= 1
+            return None, token            # depth only
+
+    out = list(ThreadedSharder([0, 1], lambda d: Worker(d), chunk=8, ramp=True).run(iter(frames)))
+    assert [float(depth[0, 0]) for _, depth in out] == [200.0 - i for i in range(61)] and all(d is None for d, _ in out)
+    assert sizes[:4] == [2, 2, 4, 4] and sum(sizes) == 61 and max(sizes) == 8      # quarter, half, then full chunks
+    assert max(peak.values()) <= 3
+    sizes.clear()
+    out = list(ThreadedSharder([0, 1, 2], lambda d: Worker(d, fail_after=2 if d == 1 else None), chunk=4).run(iter(frames)))
+    assert [float(depth[0, 0]) for _, depth in out] == [200.0 - i for i in range(61)]
+    with pytest.raises(RuntimeError, match="all GPU workers failed"):
+        list(ThreadedSharder([0], lambda d: Worker(d, fail_after=0), chunk=4).run(iter(frames)))
+
+
 def _gloo_worker(rank, world, port, n, q):
     import os
     import torch.distributed as dist
