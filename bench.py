@@ -285,13 +285,18 @@ def video_api_leg(local, rank, world, barrier, dist, torch):
         return n
 
     run()                                         # warm-up: allocations, maps, page-locked buffers
-    barrier()
-    t0 = time.perf_counter()
-    n = run()
-    te = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
-    if dist is not None:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    assert n == VFRAMES
+    run()                                         # (a fresh box's first pass also pays for page faults and clock ramps)
+    reps = []
+    for _ in range(3):                            # the job lasts ~0.12 s: median of three, each the max over ranks
+        barrier()
+        t0 = time.perf_counter()
+        n = run()
+        te = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        assert n == VFRAMES
+        reps.append(float(te.item()))
+    te = torch.tensor([sorted(reps)[1]], dtype=torch.float64)
     # the 240-frame job of config #4 lasts ~0.1 s (three chunks): filling the first chunk and draining the last are
     # a fifth of it. The same generator on a stream four times as long, for the steady-state rate:
     vid.left_source, vid.right_source = lefts * 4, rights * 4
@@ -335,6 +340,7 @@ def video_api_leg(local, rank, world, barrier, dist, torch):
     if dist is not None:
         dist.all_reduce(tc, op=dist.ReduceOp.MAX)
     return {"value": world * VFRAMES / float(te.item()), "unit": UNIT, "frames_per_rank": VFRAMES,
+            "job_seconds_3_runs": [round(r, 4) for r in reps],
             "value_960_frames": world * n4 / float(t4.item()),
             "cabi_async_same_shape_fps": world * nch * Bc / float(tc.item()), "cabi_chunk": Bc,
             "workload": f"video_{VW}x{VH}_D{VD}_sgbm_3way_bgr_frames_rectify+match+post+depth",
