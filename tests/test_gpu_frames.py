@@ -361,3 +361,27 @@ def test_video_generator_in_memory_sources():
         for a, b in zip(got, expect):
             assert np.array_equal(a, b)
     assert len(vid._worker_pool[0]) == 1
+
+
+def test_pipeline_frames_rejects_bad_requests(engine):
+    """Argument errors of the frame pipeline come back as B200S_E_INVALID -> ValueError with the reason, before any work."""
+    from depthestimation_b200.engine import make_depth_params, make_post_params
+    engine.configure(num_disp=32, sgbm_mode="sgbm")
+    pp, dp = make_post_params(False, 100, 1.0, 2.5, True), make_depth_params(100.0, 0.5)
+    L = np.zeros((2, 40, 96), np.uint8)
+    with pytest.raises(ValueError, match="only shrinks"):
+        engine.pipeline_frames(L, L, pp, dp, area=(200, 80))                 # INTER_AREA upscaling
+    with pytest.raises(ValueError, match="no output requested"):
+        engine.pipeline_frames(L, L, pp, dp, want_disp=False, want_disp16=False, want_depth=False)
+    with pytest.raises(ValueError, match="no output requested"):
+        engine.pipeline_frames(L, L, pp, make_depth_params(None, None), want_disp=False, want_depth=True)   # depth disabled
+    with pytest.raises(ValueError, match="num_disp"):
+        engine.pipeline_frames(np.zeros((1, 40, 24), np.uint8), np.zeros((1, 40, 24), np.uint8), pp, dp)
+    with pytest.raises(ValueError):
+        engine.pipeline_frames(np.zeros((1, 40, 96, 2), np.uint8), np.zeros((1, 40, 96, 2), np.uint8), pp, dp)   # 2 channels
+    with pytest.raises(ValueError, match="does not match the rectification maps"):
+        engine.set_maps(*[np.zeros((30, 64), np.float32)] * 4)
+        engine.pipeline_frames(L, L, pp, dp, use_maps=True)
+    # and the handle still works afterwards
+    d, _, z = engine.pipeline_frames(L, L, pp, dp)
+    assert d.shape == (2, 40, 64) and z.shape == d.shape
