@@ -174,3 +174,5 @@ class ThreadedSharder:
         finally:
             for _ in threads:
                 work.put(None)
+            for t in threads:        # the workers drain what they have in flight: nobody may reuse their engines before that
+                t.join(timeout=60.0)
