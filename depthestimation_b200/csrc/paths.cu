@@ -26,11 +26,13 @@ struct PathArgs {
     int px, py;   // predecessor offset (A.5)
     int first;    // 1: S = L (S not read)
     int quirk;    // sgbm_3way D%8 tail artefact: 0 none, 1 vertical path, 2 px=+1 path (A.7)
+    int plain;    // product flow (S is consumed by the row kernel): the unpadded instantiation may be used when D == Dp
     StripePlan sp;
 };
 
 // LW lanes x 2 NR disparities per lane; a warp carries 32 / LW lines (LW need not be a power of two, sgm_step.cuh).
-template <int LW, int NR>
+// PAD = false: no padded disparities at all (D == Dp == LW * 2 * NR) and S goes to the row kernel: no clamp per step
+template <int LW, int NR, bool PAD>
 __global__ void __launch_bounds__(128) k_path(const PathArgs a) {
     using LG = LaneGroup<LW>;
     constexpr int DPL = 2 * NR;
@@ -112,7 +114,7 @@ __global__ void __launch_bounds__(128) k_path(const PathArgs a) {
             if (acc && !a.first) load_regs<NR>(a.S + off, Sq);
         }
         if (reset) sgm_reset<NR>(L, m);
-        sgm_step<LW, NR, true>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, a.quirk, d0);
+        sgm_step<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, a.quirk, d0);
         // ---- S ---------------------------------------------------------------------------------
         if (active && in_line && acc) {
             unsigned So[NR];
@@ -129,7 +131,8 @@ static void launch_path_t(const PathArgs& a, int B, int nlines, cudaStream_t st)
     const int threads = 128;
     const int per_cta = (threads / 32) * LaneGroup<LW>::RPW;
     dim3 grid((unsigned)((nlines + per_cta - 1) / per_cta), 1, B);
-    k_path<LW, NR><<<grid, threads, 0, st>>>(a);
+    if (a.plain && a.D == LW * 2 * NR) k_path<LW, NR, false><<<grid, threads, 0, st>>>(a);
+    else k_path<LW, NR, true><<<grid, threads, 0, st>>>(a);
 }
 
 static void launch_one(const PathArgs& a, int B, cudaStream_t st) {
@@ -164,6 +167,7 @@ int launch_paths(const Eff& e, const StripePlan& sp, int B, const uint16_t* C, c
     a.C = C; a.Calt = nullptr; a.S = S;
     a.H = e.H; a.W1 = e.W1; a.D = e.D; a.Dp = e.Dp; a.P1 = e.P1e; a.P2 = e.P2e;
     a.quirk = 0;
+    a.plain = vertical_only ? 1 : 0;   // the debug flow's selection kernel reads S as is: it keeps the clamped steps
     StripePlan whole;
     whole.n = 1; whole.a[0] = 0; whole.r0[0] = 0; whole.r1[0] = e.H; whole.alt_rows = 0;
     for (int i = 1; i < B200S_MAX_STRIPES; i++) whole.a[i] = whole.r0[i] = whole.r1[i] = 0;
