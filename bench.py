@@ -59,6 +59,19 @@ def make_maps():
     return maps, cal
 
 
+def make_reference_maps():
+    """The reference arm's maps: the reference's own cv2 calls (rectify.py:63-73), else the oracle's restatement of them.
+    Nothing of the product library is on this arm's path, so it also runs on a box without a GPU."""
+    from depthestimation_b200.synth import make_calibration
+    from oracle import cv2_reference as cr
+    cal = make_calibration(H, W)
+    if cr.HAVE_CV2:
+        return cr.build_maps(cal, alpha=1.0), cal
+    # no cv2 (and so no stereoRectify) on this host: identity maps time the same remap work
+    xs, ys = np.meshgrid(np.arange(W, dtype=np.float32), np.arange(H, dtype=np.float32))
+    return dict(map1_L=xs, map2_L=ys, map1_R=xs.copy(), map2_R=ys.copy()), cal
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (profiling guide recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -175,7 +188,7 @@ def run_reference(args):
     if rank != 0:
         return 0
     L, R = make_inputs(N_DISTINCT)
-    maps, cal = make_maps()
+    maps, cal = make_reference_maps()
     ref = CpuReference(maps, cal)
     per_step = ref.cores  # one frame per host thread and step: a bounded sample of the workload
     for _ in range(min(args.warmup, 1)):

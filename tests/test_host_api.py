@@ -242,3 +242,21 @@ def test_gloo_world2_gather_in_frame_order():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert res == [float(i) for i in range(n)]
+
+
+def test_bench_reference_arm_runs_without_a_gpu():
+    """`bench.py --impl reference` (the driver's reference arm) is the reference's own CPU path: it must not touch the
+    product library (it runs here, where no GPU exists) and its one JSON line carries the contract's keys."""
+    import json
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["metric"] == "stereo_pairs_per_second" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert line["gpu_launches"] == 0 and line["config"]["workload"].startswith("kitti_1242x375_D128")
