@@ -55,6 +55,12 @@ class _FrameWorker:
         self._pool = ThreadPoolExecutor(max(1, int(copy_threads)))
         self._feeder = ThreadPoolExecutor(1)
 
+    def close(self):
+        self._feeder.shutdown(wait=True)
+        self._pool.shutdown(wait=True)
+        self._free = []
+        self.eng.close()
+
     def _buffers(self, B, shape):
         from ..engine import pinned_empty
         with self._lock:
@@ -139,6 +145,14 @@ class StereoDepthEstimatorVideo:
     def configure_sgbm(self, **kwargs):
         self.core.configure_sgbm(**kwargs)
 
+    def close_workers(self):
+        """Give back what the sharded generator keeps between calls (per GPU: an engine handle with its device scratch and
+        the page-locked chunk buffers). Called when the configuration changes; safe to call at any time between runs."""
+        for ws in getattr(self, "_worker_pool", {}).values():
+            for w in ws:
+                w.close()
+        self._worker_key, self._worker_pool = None, {}
+
     # -- frame sources ----------------------------------------------------------------------------
     def _frames(self, downscale_factor=None):
         f = self.downscale_factor if downscale_factor is None else downscale_factor
@@ -220,24 +234,28 @@ class StereoDepthEstimatorVideo:
             warnings.warn("Input image size %sx%s does not match calibration %sx%s; resizing for rectification." %
                           (aw, ah, size[0], size[1]), RuntimeWarning, stacklevel=2)
         W, H = size if size is not None else (aw, ah)
-        chunk = self.chunk
-        if chunk is None:
-            chunk = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
-            # a source of known length (a list of frames, a short clip): at least two chunks per GPU, so that every GPU
-            # gets work and its copies overlap its kernels
-            n = None
-            try:
-                n = min(len(self.left_source), len(self.right_source))
-            except TypeError:
-                pass
-            if n:
-                chunk = max(1, min(chunk, -(-n // (2 * len(self.devices)))))
-
+        n = None
+        try:
+            n = min(len(self.left_source), len(self.right_source))
+        except TypeError:
+            pass
         # workers (engine handle with its device scratch, uploaded maps, page-locked chunk buffers) survive between
-        # calls of this generator as long as the configuration is the same
-        key = (tuple(sorted((k, str(v)) for k, v in kw.items())), id(maps), size, area, bytes(pp), bytes(dp), chunk)
+        # calls of this generator as long as the configuration is the same. The chunk length is part of what survives:
+        # the engine's preferred batch depends on the free device memory, which the workers' own scratch changes, so it
+        # is asked for once per configuration and not on every call
+        key = (tuple(sorted((k, str(v)) for k, v in kw.items())), id(maps), size, area, bytes(pp), bytes(dp),
+               self.chunk, int(self.max_chunk), n, tuple(self.devices), (sh, sw))
         if getattr(self, "_worker_key", None) != key:
-            self._worker_key, self._worker_pool = key, {}
+            self.close_workers()
+            chunk = self.chunk
+            if chunk is None:
+                chunk = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
+                # a source of known length (a list of frames, a short clip): at least two chunks per GPU, so that every
+                # GPU gets work and its copies overlap its kernels
+                if n:
+                    chunk = max(1, min(chunk, -(-n // (2 * len(self.devices)))))
+            self._worker_key, self._worker_pool, self._worker_chunk = key, {}, int(chunk)
+        chunk = self._worker_chunk
         pool, used, lock = self._worker_pool, [], threading.Lock()
 
         def make_worker(dev):

@@ -361,6 +361,17 @@ def test_video_generator_in_memory_sources():
         for a, b in zip(got, expect):
             assert np.array_equal(a, b)
     assert len(vid._worker_pool[0]) == 1
+    # the chunk length is fixed per configuration: the engine's preferred batch follows the free device memory (which the
+    # worker's own scratch changes), and a different answer on a later call must not throw the worker away
+    w0, chunk0 = vid._worker_pool[0][0], vid._worker_chunk
+    with patch.object(type(vid.core.sgbm.engine), "preferred_batch", lambda self, H, W: 1):
+        assert len(list(vid.estimate_depth())) == len(expect)
+    assert vid._worker_pool[0][0] is w0 and vid._worker_chunk == chunk0
+    vid.configure_sgbm(num_disp=D // 2)     # a new configuration does: the old worker's engine and buffers are given back
+    assert len(list(vid.estimate_depth())) == len(expect)
+    assert vid._worker_pool[0][0] is not w0 and not w0.eng._h
+    vid.close_workers()
+    assert vid._worker_pool == {}
 
 
 def test_pipeline_frames_rejects_bad_requests(engine):

@@ -92,9 +92,7 @@ def main():
             if base is None:
                 base, ref = t, first
             same = bool(np.array_equal(first, ref))
-            for ws in getattr(vid, "_worker_pool", {}).values():     # give the device scratch and page-locked buffers back
-                for w in ws:
-                    w.eng.close()
+            vid.close_workers()     # give the device scratch and page-locked buffers back
             print(json.dumps({"job": name, "shape": f"{W}x{H}", "D": D, "mode": "sgbm_3way", "frames": nframes, "channels": cn,
                               "n_gpus": n, "seconds": round(t, 4), "frames_per_s": round(nframes / t, 1),
                               "speedup_vs_1gpu": round(base / t, 2), "first_frame_equals_1gpu": same,
