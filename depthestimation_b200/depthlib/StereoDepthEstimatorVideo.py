@@ -86,6 +86,11 @@ class _FrameWorker:
             # size the engine's device scratch for a FULL chunk once: the first chunks of a stream are shorter (ramp),
             # and growing the scratch later frees and reallocates gigabytes in the middle of the stream
             self._sized = geom
+            # ... and page-lock the other chunk buffers a stream will have in flight now, not in the middle of a later run
+            spare = [self._buffers(B, shape)[0] for _ in range(self.max_inflight - 1)]
+            with self._lock:
+                if geom == self._geom:
+                    self._free.extend(spare)
             if B < geom[0]:
                 bL[B:] = 0; bR[B:] = 0
                 self.eng.pipeline_batch_wait(self.eng.pipeline_frames_submit(
@@ -250,12 +255,18 @@ class StereoDepthEstimatorVideo:
             chunk = self.chunk
             if chunk is None:
                 chunk = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
-                # a source of known length (a list of frames, a short clip): at least two chunks per GPU, so that every
-                # GPU gets work and its copies overlap its kernels
+                # a source of known length (a list of frames, a short clip): equal chunks, the same number for every GPU
+                # (chunk i goes to GPU i mod G) and at least two each, so that its copies overlap its kernels
                 if n:
-                    chunk = max(1, min(chunk, -(-n // (2 * len(self.devices)))))
+                    G = len(self.devices)
+                    nchunks = max(2 * G, -(-n // chunk))
+                    nchunks = -(-nchunks // G) * G
+                    chunk = max(1, -(-n // nchunks))
             self._worker_key, self._worker_pool, self._worker_chunk = key, {}, int(chunk)
         chunk = self._worker_chunk
+        # shorter first chunks start the GPUs before a full chunk has been captured; frames that are all there already
+        # (several GPUs, known length) are split evenly instead
+        ramp = n is None or len(self.devices) == 1
         pool, used, lock = self._worker_pool, [], threading.Lock()
 
         def make_worker(dev):
@@ -273,7 +284,7 @@ class StereoDepthEstimatorVideo:
 
         t0 = time.time()
         try:
-            for _disp, depth_m in ThreadedSharder(self.devices, make_worker, chunk, max_inflight=4, ramp=True).run(pairs()):
+            for _disp, depth_m in ThreadedSharder(self.devices, make_worker, chunk, max_inflight=4, ramp=ramp).run(pairs()):
                 yield depth_m
                 self._show(depth_m)
                 t0 = self._pace(t0)

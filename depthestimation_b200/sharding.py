@@ -46,7 +46,7 @@ def gather_in_order(local: Dict[int, object], n_frames: int, group=None, dst: in
 
 
 class ThreadedSharder:
-    """Chunks of frames -> GPUs round-robin, ordered results back.
+    """Chunks of frames -> GPUs round-robin (chunk i to GPU i mod G), ordered results back.
 
     ``make_worker(device)`` is called once per device inside that device's worker thread (so each thread owns its
     handle, like one cv2.StereoSGBM per thread in the reference) and returns either
@@ -55,8 +55,8 @@ class ThreadedSharder:
       optional ``max_inflight`` (default 3): the worker then keeps that many chunks in flight on its GPU, so uploads,
       kernels and downloads of consecutive chunks overlap (b200s_pipeline_frames_submit / b200s_pipeline_batch_wait).
       ``submit`` receives the chunk as two lists of frames (no host-side stacking on the dispatcher thread).
-    A failing worker re-queues its chunks for the others; when every worker has failed the error is raised to the
-    caller.
+    A failing worker hands its chunks (in flight and waiting) to whichever of the others is free first, and later
+    chunks that would have been its turn go the same way; when every worker has failed the error is raised to the caller.
     """
 
     def __init__(self, devices: Sequence[int], make_worker: Callable[[int], Callable], chunk: int = 8,
@@ -71,36 +71,52 @@ class ThreadedSharder:
 
     def run(self, pairs: Iterable[Tuple[np.ndarray, np.ndarray]]) -> Iterator[Tuple[np.ndarray, Optional[np.ndarray]]]:
         G = len(self.devices)
-        work: "queue.Queue" = queue.Queue()
+        cv = threading.Condition()                 # guards everything below
+        mine: List[List[tuple]] = [[] for _ in range(G)]   # chunk i waits in the list of worker i mod G (round-robin) ...
+        orphans: List[tuple] = []                  # ... and the chunks of a failed worker here, where any worker takes them
+        dead = [False] * G
+        stop = [False]
         done: Dict[int, object] = {}
-        cv = threading.Condition()
-        alive = [G]
         errors: List[BaseException] = []
 
-        def fail(exc, items):
+        def fail(w, exc, items):
             with cv:
-                errors.append(exc); alive[0] -= 1
-                if alive[0] > 0:
-                    for it_ in items:
-                        work.put(it_)            # another GPU picks the chunks up
+                errors.append(exc)
+                dead[w] = True
+                orphans.extend(items)
+                orphans.extend(mine[w])
+                mine[w].clear()
+                orphans.sort(key=lambda it_: it_[0])
                 cv.notify_all()
 
-        def worker(dev):
+        def take(w, block):
+            """Next chunk for worker w (orphans first: they are the oldest), None when there is none (yet)."""
+            with cv:
+                while True:
+                    if orphans:
+                        return orphans.pop(0)
+                    if mine[w]:
+                        return mine[w].pop(0)
+                    if stop[0] or not block:
+                        return None
+                    cv.wait(timeout=0.5)
+
+        def worker(w, dev):
             try:
                 fn = self.make_worker(dev)
             except BaseException as exc:  # noqa: BLE001
-                fail(exc, [])
+                fail(w, exc, [])
                 return
             if not hasattr(fn, "submit"):        # blocking worker: one chunk at a time
                 while True:
-                    item = work.get()
+                    item = take(w, True)
                     if item is None:
                         break
                     cid, Ls, Rs = item
                     try:
                         res = fn(np.ascontiguousarray(np.stack(Ls)), np.ascontiguousarray(np.stack(Rs)))
                     except BaseException as exc:  # noqa: BLE001
-                        fail(exc, [item])
+                        fail(w, exc, [item])
                         return
                     with cv:
                         done[cid] = res
@@ -108,34 +124,27 @@ class ThreadedSharder:
                 return
             cap = max(1, int(getattr(fn, "max_inflight", 3)))
             flying = []                          # [(item, token)] oldest first
-            stop = False
             while True:
                 try:
-                    while not stop and len(flying) < cap:
-                        try:
-                            item = work.get(block=not flying)
-                        except queue.Empty:
-                            break
+                    while len(flying) < cap:
+                        item = take(w, not flying)
                         if item is None:
-                            stop = True
                             break
                         flying.append((item, None))
                         flying[-1] = (item, fn.submit(item[1], item[2]))
                     if not flying:
-                        if stop:
-                            break
-                        continue
+                        break                    # take() blocked until the stop flag: nothing left to do
                     item, tok = flying[0]
                     res = fn.wait(tok)
                     flying.pop(0)
                 except BaseException as exc:  # noqa: BLE001
-                    fail(exc, [it_ for it_, _ in flying])
+                    fail(w, exc, [it_ for it_, _ in flying])
                     return
                 with cv:
                     done[item[0]] = res
                     cv.notify_all()
 
-        threads = [threading.Thread(target=worker, args=(d,), daemon=True) for d in self.devices]
+        threads = [threading.Thread(target=worker, args=(w, d), daemon=True) for w, d in enumerate(self.devices)]
         for t in threads:
             t.start()
         submitted = emitted = 0
@@ -155,7 +164,13 @@ class ThreadedSharder:
                     if not Ls:
                         exhausted = True
                         break
-                    work.put((submitted, Ls, Rs))
+                    with cv:
+                        w = submitted % G
+                        if dead[w]:              # its turn goes to whoever is free first
+                            orphans.append((submitted, Ls, Rs))
+                        else:
+                            mine[w].append((submitted, Ls, Rs))
+                        cv.notify_all()
                     submitted += 1
                     if len(Ls) < want:
                         exhausted = True
@@ -163,7 +178,7 @@ class ThreadedSharder:
                     break
                 with cv:
                     while emitted not in done:
-                        if alive[0] <= 0:
+                        if all(dead):
                             raise RuntimeError(f"all GPU workers failed: {errors[-1]!r}") from errors[-1]
                         cv.wait(timeout=0.5)
                     disp, depth = done.pop(emitted)
@@ -172,7 +187,8 @@ class ThreadedSharder:
                 for k in range(n):
                     yield (disp[k] if disp is not None else None), (depth[k] if depth is not None else None)
         finally:
-            for _ in threads:
-                work.put(None)
+            with cv:
+                stop[0] = True
+                cv.notify_all()
             for t in threads:        # the workers drain what they have in flight: nobody may reuse their engines before that
                 t.join(timeout=60.0)

@@ -177,7 +177,7 @@ def test_threaded_sharder_async_workers_ramp_and_failover():
     from depthestimation_b200.sharding import ThreadedSharder
     frames = [(np.full((2, 3), i, np.uint8), np.full((2, 3), 200 - i, np.uint8)) for i in range(61)]
     lock = threading.Lock()
-    sizes, peak = [], {}
+    sizes, peak, per_dev = [], {}, {}
 
     class Worker:
         max_inflight = 3
@@ -189,6 +189,7 @@ def test_threaded_sharder_async_workers_ramp_and_failover():
             assert isinstance(Ls, list) and len(Ls) == len(Rs)
             with lock:
                 sizes.append(len(Ls))
+                per_dev.setdefault(self.dev, []).append(len(Ls))
                 self.fly += 1
                 self.n += 1
                 peak[self.dev] = max(peak.get(self.dev, 0), self.fly)
@@ -204,7 +205,9 @@ def test_threaded_sharder_async_workers_ramp_and_failover():
 
     out = list(ThreadedSharder([0, 1], lambda d: Worker(d), chunk=8, ramp=True).run(iter(frames)))
     assert [float(depth[0, 0]) for _, depth in out] == [200.0 - i for i in range(61)] and all(d is None for d, _ in out)
-    assert sizes[:4] == [2, 2, 4, 4] and sum(sizes) == 61 and max(sizes) == 8      # quarter, half, then full chunks
+    assert sorted(sizes)[:5] == [1, 2, 2, 4, 4] and sum(sizes) == 61 and max(sizes) == 8      # quarter, half, then full chunks
+    # chunk i goes to worker i mod G: each of the two sees a quarter, a half, then full chunks, and the same number of chunks
+    assert per_dev[0][:3] == [2, 4, 8] and per_dev[1][:3] == [2, 4, 8] and abs(len(per_dev[0]) - len(per_dev[1])) <= 1
     assert max(peak.values()) <= 3
     sizes.clear()
     out = list(ThreadedSharder([0, 1, 2], lambda d: Worker(d, fail_after=2 if d == 1 else None), chunk=4).run(iter(frames)))

@@ -36,6 +36,7 @@ def fault_probe():
 
 
 ACC = {}
+EVENTS = []
 
 
 def _instrument():
@@ -82,6 +83,20 @@ def _instrument():
             ACC["workers_created"] = ACC.get("workers_created", 0) + 1
         return init(self, *a, **k)
     mod._FrameWorker.__init__ = counted_init
+    feed0, wait0 = mod._FrameWorker._feed, mod._FrameWorker.wait
+    def ev_feed(self, Ls, Rs):
+        t0 = time.perf_counter()
+        r = feed0(self, Ls, Rs)
+        with lock:
+            EVENTS.append(("feed", id(self), len(Ls), t0, time.perf_counter()))
+        return r
+    def ev_wait(self, tok):
+        t0 = time.perf_counter()
+        r = wait0(self, tok)
+        with lock:
+            EVENTS.append(("wait", id(self), r[1].shape[0] if r[1] is not None else r[0].shape[0], t0, time.perf_counter()))
+        return r
+    mod._FrameWorker._feed, mod._FrameWorker.wait = ev_feed, ev_wait
     wrap(mod._FrameWorker, "_buffers", "buffers")
     wrap(mod._FrameWorker, "_feed", "feed_total")
     wrap(mod._FrameWorker, "wait", "wait_total")
@@ -106,14 +121,17 @@ def job(nworkers, H=720, W=1280, D=128, n=240, cn=3, devices=None):
     phases = []
     for _ in range(5):
         ACC.clear()
+        EVENTS.clear()
         t0 = time.perf_counter()
         c = sum(1 for _ in vid.estimate_depth())
         ts.append(time.perf_counter() - t0)
         phases.append({k: round(v, 3) for k, v in sorted(ACC.items())})
+        ids = {}
+        timeline = [(k, ids.setdefault(w, len(ids)), b, round(1e3 * (a - t0), 1), round(1e3 * (e - t0), 1)) for k, w, b, a, e in sorted(EVENTS, key=lambda x: x[3])]
     assert c == n
     vid.close_workers()
     return {"shape": f"{W}x{H}", "frames": n, "workers": nworkers, "devices": devices or [0] * nworkers,
-            "seconds": [round(t, 4) for t in ts], "phases_last": phases[-1]}
+            "seconds": [round(t, 4) for t in ts], "phases_last": phases[-1], "timeline_last_ms": timeline}
 
 
 if __name__ == "__main__":
@@ -121,6 +139,7 @@ if __name__ == "__main__":
     import torch
     _instrument()
     nd = torch.cuda.device_count()
-    print(json.dumps(job(1, 2160, 3840, 256, 64, 1)), flush=True)
+    print(json.dumps(job(1)), flush=True)
     if nd > 1:
+        print(json.dumps(job(nd, devices=list(range(nd)))), flush=True)
         print(json.dumps(job(nd, 2160, 3840, 256, 64, 1, devices=list(range(nd)))), flush=True)

@@ -9,7 +9,7 @@ node in ONE process (frames sharded chunk-per-GPU by sharding.ThreadedSharder, h
     python tools/multigpu_jobs.py [--gpus 1,2,4,8] [--only video720,uhd4k]
 
 One JSON line per (job, N): wall-clock seconds of the whole job from host frames to host depth maps (strong scaling: the
-job is fixed), frames/s, and the speed-up over N = 1. The first run of every configuration is a warm-up (allocations)."""
+job is fixed), frames/s, and the speed-up over N = 1. Three warm-up runs per configuration (allocations), then the median of five."""
 from __future__ import annotations
 
 import argparse
@@ -81,9 +81,10 @@ def main():
                         first = depth_m.copy()
                     cnt += 1
                 return cnt, first
-            run()
+            for _ in range(3):       # which worker gets which chunks differs from run to run: let every worker see a full chunk
+                run()
             times = []
-            for _ in range(3):
+            for _ in range(5):
                 t0 = time.perf_counter()
                 cnt, first = run()
                 times.append(time.perf_counter() - t0)
