@@ -245,25 +245,25 @@ class StereoDepthEstimatorVideo:
         except TypeError:
             pass
         # workers (engine handle with its device scratch, uploaded maps, page-locked chunk buffers) survive between
-        # calls of this generator as long as the configuration is the same. The chunk length is part of what survives:
-        # the engine's preferred batch depends on the free device memory, which the workers' own scratch changes, so it
-        # is asked for once per configuration and not on every call
+        # calls of this generator as long as the configuration is the same. The chunk CAPACITY (what their buffers and
+        # scratch are sized for) is part of what survives: the engine's preferred batch depends on the free device memory,
+        # which the workers' own scratch changes, so it is asked for once per configuration and not on every call
         key = (tuple(sorted((k, str(v)) for k, v in kw.items())), id(maps), size, area, bytes(pp), bytes(dp),
-               self.chunk, int(self.max_chunk), n, tuple(self.devices), (sh, sw))
+               self.chunk, int(self.max_chunk), tuple(self.devices), (sh, sw))
         if getattr(self, "_worker_key", None) != key:
             self.close_workers()
-            chunk = self.chunk
-            if chunk is None:
-                chunk = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
-                # a source of known length (a list of frames, a short clip): equal chunks, the same number for every GPU
-                # (chunk i goes to GPU i mod G) and at least two each, so that its copies overlap its kernels
-                if n:
-                    G = len(self.devices)
-                    nchunks = max(2 * G, -(-n // chunk))
-                    nchunks = -(-nchunks // G) * G
-                    chunk = max(1, -(-n // nchunks))
-            self._worker_key, self._worker_pool, self._worker_chunk = key, {}, int(chunk)
-        chunk = self._worker_chunk
+            cap = self.chunk
+            if cap is None:
+                cap = max(1, min(core.sgbm.engine.preferred_batch(H, W), int(self.max_chunk)))
+            self._worker_key, self._worker_pool, self._worker_cap = key, {}, int(cap)
+        cap = chunk = self._worker_cap
+        if self.chunk is None and n:
+            # a source of known length (a list of frames, a short clip): equal chunks, the same number for every GPU
+            # (chunk i goes to GPU i mod G) and at least two each, so that its copies overlap its kernels
+            G = len(self.devices)
+            nchunks = max(2 * G, -(-n // cap))
+            nchunks = -(-nchunks // G) * G
+            chunk = max(1, -(-n // nchunks))
         # shorter first chunks start the GPUs before a full chunk has been captured; frames that are all there already
         # (several GPUs, known length) are split evenly instead
         ramp = n is None or len(self.devices) == 1
@@ -273,7 +273,7 @@ class StereoDepthEstimatorVideo:
             with lock:
                 w = pool.get(dev, []).pop() if pool.get(dev) else None
             if w is None:
-                w = _FrameWorker(dev, kw, maps, pp, dp, use_maps, size, area, cap=chunk)
+                w = _FrameWorker(dev, kw, maps, pp, dp, use_maps, size, area, cap=cap)
             with lock:
                 used.append((dev, w))
             return w

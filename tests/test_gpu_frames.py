@@ -363,10 +363,13 @@ def test_video_generator_in_memory_sources():
     assert len(vid._worker_pool[0]) == 1
     # the chunk length is fixed per configuration: the engine's preferred batch follows the free device memory (which the
     # worker's own scratch changes), and a different answer on a later call must not throw the worker away
-    w0, chunk0 = vid._worker_pool[0][0], vid._worker_chunk
+    w0, chunk0 = vid._worker_pool[0][0], vid._worker_cap
     with patch.object(type(vid.core.sgbm.engine), "preferred_batch", lambda self, H, W: 1):
         assert len(list(vid.estimate_depth())) == len(expect)
-    assert vid._worker_pool[0][0] is w0 and vid._worker_chunk == chunk0
+    assert vid._worker_pool[0][0] is w0 and vid._worker_cap == chunk0
+    vid.left_source, vid.right_source = lefts[:2], rights[:2]      # nor does a source of another length
+    assert len(list(vid.estimate_depth())) == 2 and vid._worker_pool[0][0] is w0
+    vid.left_source, vid.right_source = lefts, rights
     vid.configure_sgbm(num_disp=D // 2)     # a new configuration does: the old worker's engine and buffers are given back
     assert len(list(vid.estimate_depth())) == len(expect)
     assert vid._worker_pool[0][0] is not w0 and not w0.eng._h
