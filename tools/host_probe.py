@@ -1,7 +1,13 @@
 #!/usr/bin/env python
-"""Host-side probe for the in-process multi-GPU jobs: (1) what first-touch page faults of freshly allocated result arrays cost
-on this host, alone and from 8 threads at once; (2) the 240-frame 720p job of tools/multigpu_jobs.py with 1, 2, 4 and 8
-workers that all sit on GPU 0 (the GPU work serialises, so what grows with the worker count is host overhead)."""
+"""Host-side probe of the in-process multi-GPU video driver (StereoDepthEstimatorVideo(devices=[...])):
+
+(1) what first-touch page faults of freshly allocated result arrays cost on this host, alone and from 8 threads at once;
+(2) the 240-frame 720p job of tools/multigpu_jobs.py on one GPU and, on a multi-GPU node, that job and the 64-pair 4K job on
+    all GPUs, five runs each, with the wall time per phase of a worker (chunk buffers, copies into / out of page-locked
+    memory, the submit call, the wait for the GPU), the count of page-locked allocations and workers built per run, and a
+    per-chunk timeline (feed / wait, worker, frames, start and end in ms) of the last run.
+
+    python tools/host_probe.py > gpurun_out/host_probe.txt"""
 import json
 import os
 import sys
