@@ -342,28 +342,34 @@ __global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS
                 }
                 const unsigned mm = umin2(umin2(l0, l1), umin2(l2, l3));
                 minS = (int)min(mm & 0xffffu, mm >> 16);
-                // per SIMD lane: 1 + the last block whose value equals minS (0: none). v - minS has no borrow (minS is the
-                // minimum of these blocks), min(., 1) is 0 where equal, and (j+1) - (j+1) * that is j+1 or 0 per half.
-                const unsigned pkm = pk2((unsigned)minS);
-                unsigned j0 = 0u, j1 = 0u, j2 = 0u, j3 = 0u;
+                // Which SIMD lanes reach minS (almost always one), and in each of them the LAST block that does: one
+                // 16-bit load and a compare per block of that lane only, instead of five packed operations on each of the
+                // four registers of every block.
+                unsigned cand = 0u;
+                {
+                    const unsigned lq[4] = {l0, l1, l2, l3};
 #pragma unroll
-                for (int j = 0; j < NCH; j++) {
-                    if (j < NB) {
-                        const uint4 v = unit_ct(j);
-                        const unsigned pj = pk2((unsigned)(j + 1));
-                        j0 = umax2(j0, pj - umin2(v.x - pkm, 0x00010001u) * (unsigned)(j + 1));
-                        j1 = umax2(j1, pj - umin2(v.y - pkm, 0x00010001u) * (unsigned)(j + 1));
-                        j2 = umax2(j2, pj - umin2(v.z - pkm, 0x00010001u) * (unsigned)(j + 1));
-                        j3 = umax2(j3, pj - umin2(v.w - pkm, 0x00010001u) * (unsigned)(j + 1));
+                    for (int q = 0; q < 4; q++) {
+                        cand |= (unsigned)((int)(lq[q] & 0xffffu) == minS) << (2 * q);
+                        cand |= (unsigned)((int)(lq[q] >> 16) == minS) << (2 * q + 1);
                     }
                 }
+                if (NB == 0) cand = 0u;                       // no whole block: only the scalar tail below
                 best = 0x7fffffff;
-                const unsigned jl[4] = {j0, j1, j2, j3};
+                const unsigned short* phs = (const unsigned short*)pb;
+                while (cand) {
+                    const int l = __ffs((int)cand) - 1;
+                    cand &= cand - 1u;
+                    const unsigned short* pl = phs + l;
+                    int jl = 0;
 #pragma unroll
-                for (int q = 3; q >= 0; q--) {                // descending, so the lowest d is the last assignment that sticks via min
-                    const int hi = (int)(jl[q] >> 16), lo = (int)(jl[q] & 0xffffu);
-                    if (hi) best = min(best, 8 * (hi - 1) + 2 * q + 1);
-                    if (lo) best = min(best, 8 * (lo - 1) + 2 * q);
+                    for (int j = 0; j < NCH; j++) {
+                        if (j < NB) {
+                            const int c = (NR == 8) ? (j >> 1) + LW * (j & 1) : j;
+                            if ((int)pl[8 * ((c & ~SWZ) + ((c & SWZ) ^ sw))] == minS) jl = j;
+                        }
+                    }
+                    best = min(best, 8 * jl + l);
                 }
                 if (a.D > 8 * NB) {                           // scalar tail: at most 7 disparities, all in unit NB
                     const uint4 v = pb[unit_of(NB)];
