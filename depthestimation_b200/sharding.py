@@ -188,7 +188,10 @@ class ThreadedSharder:
                     yield (disp[k] if disp is not None else None), (depth[k] if depth is not None else None)
         finally:
             with cv:
-                stop[0] = True
+                stop[0] = True               # (a consumer that walks away early: what is still queued is dropped)
+                orphans.clear()
+                for q in mine:
+                    q.clear()
                 cv.notify_all()
             for t in threads:        # the workers drain what they have in flight: nobody may reuse their engines before that
                 t.join(timeout=60.0)

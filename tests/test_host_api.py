@@ -263,3 +263,24 @@ def test_bench_reference_arm_runs_without_a_gpu():
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert line["gpu_launches"] == 0 and line["config"]["workload"].startswith("kitti_1242x375_D128")
+
+
+def test_threaded_sharder_consumer_stops_early():
+    """A consumer that abandons the generator: the workers finish what they have in flight, queued chunks are dropped, the
+    threads end."""
+    import threading
+    from depthestimation_b200.sharding import ThreadedSharder
+    frames = [(np.full((2, 3), i % 200, np.uint8), np.full((2, 3), i % 200, np.uint8)) for i in range(400)]
+    calls = []
+
+    def make_worker(dev):
+        def fn(L, R):
+            calls.append(L.shape[0])
+            return L.astype(np.float32), R.astype(np.float32)
+        return fn
+    before = threading.active_count()
+    gen = ThreadedSharder([0, 1], make_worker, chunk=4, max_inflight=4).run(iter(frames))
+    first = [next(gen) for _ in range(3)]
+    gen.close()
+    assert [float(d[0, 0]) for d, _ in first] == [0.0, 1.0, 2.0]
+    assert sum(calls) <= 4 * 4 * 2 + 8 and threading.active_count() <= before      # nothing beyond the queued window ran
