@@ -451,8 +451,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS
     };
     auto start_from_ck = [&](const int xe) {
         if (xe < a.W1) {
-            const unsigned mn = group_min2<LW>(local_min2<NR>(L), gmask, gl);
-            m = min(mn & 0xffffu, mn >> 16);
+            m = group_min<LW>(local_min2<NR>(L), gmask, gl);
         } else {
             sgm_reset<NR>(L, m);
         }

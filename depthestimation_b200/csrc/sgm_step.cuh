@@ -12,6 +12,9 @@
 #ifndef SGM_FMA_ADDS
 #define SGM_FMA_ADDS 1
 #endif
+#ifndef SGM_WARP_REDUX
+#define SGM_WARP_REDUX 1   // 0: shuffle tree also for whole-warp groups (for comparison)
+#endif
 
 // ---- 16-byte global loads / stores of a lane's NR packed registers --------------------------------
 template <int NR>
@@ -77,6 +80,19 @@ __device__ __forceinline__ unsigned group_min2(unsigned v, unsigned gmask, const
             if (gl + o < LW) v = umin2(v, t);
         }
         return __shfl_sync(0xffffffffu, v, (int)(threadIdx.x & 31) - gl);   // group lane 0 holds the minimum
+    }
+}
+
+// minimum over both halves of v over the lane group, as a scalar. A group that is the whole warp uses the hardware warp
+// reduction (CREDUX.MIN: ~40 cycles on the dependent path against ~170 for five shuffle + min levels, tools/ubench/redux.cu;
+// with a sub-warp member mask the same intrinsic serialises over the groups and is slower than the shuffle tree).
+template <int LW>
+__device__ __forceinline__ unsigned group_min(unsigned v, unsigned gmask, const int gl = 0) {
+    if constexpr (LW == 32 && SGM_WARP_REDUX) {
+        return __reduce_min_sync(0xffffffffu, min(v & 0xffffu, v >> 16));
+    } else {
+        const unsigned mn = group_min2<LW>(v, gmask, gl);
+        return min(mn & 0xffffu, mn >> 16);
     }
 }
 
@@ -161,8 +177,7 @@ template <int LW, int NR, bool PAD = true>
 __device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const unsigned (&Cq)[NR],
                                          const unsigned (&pm)[NR], const unsigned gmask, const int gl,
                                          const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
-    const unsigned mn = group_min2<LW>(sgm_step_core<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirk, d0), gmask, gl);
-    m = min(mn & 0xffffu, mn >> 16);
+    m = group_min<LW>(sgm_step_core<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirk, d0), gmask, gl);
 }
 
 template <int NR>
