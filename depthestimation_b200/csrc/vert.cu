@@ -434,6 +434,7 @@ int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, i
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= VERT_MAX_DEVICES) { cudaGetLastError(); return 1; }
     VertPlan cached;
     bool cok;
+    int sms = 0;
     {
         std::lock_guard<std::mutex> lk(mu);
         Cache& c = cache[dev];
@@ -482,8 +483,19 @@ int launch_vert_t(const Eff& e, int B, const uint16_t* C, uint16_t* S, int dy, i
         // plan wins, and a latency plan that still needs several slots loses (1920x1080 D=256: 10.5 -> 12.3 ms)
         if (cok && c.lat_ok && lat_env && B > 0 && 2LL * B * c.lat.CS <= c.sms && c.lat.KIT == 1 && c.plan.KIT > 1)
             cached = c.lat;
+        sms = c.sms;
     }
     if (!cok) return 1;                                            // does not fit: caller falls back to k_path
+    // The clamped-record plan (wide frames at D > 128: every column of a strip in shared memory, several per thread) on a
+    // call that keeps under a third of the SMs busy: the generic line kernel, one launch per direction with the lines
+    // spread over every SM, is faster there. Measured per pair, 1920x1080 D = 256 hh: 1 pair 9.14 -> 5.66 ms, 2 pairs
+    // 4.63 -> 3.69, 4 pairs 2.34 -> 2.42 (cluster kernel kept). Unclamped plans stay: 1920x1080 D = 128 sgbm, one pair,
+    // 2.07 (cluster) against 2.57 ms; KITTI 0.66 against 0.87.
+    // (B200S_VERT_SMALL_GENERIC=0, read on every call so that a test can switch it, keeps the cluster kernel.)
+    if (B > 0 && cached.clamp && 3LL * B * cached.CS <= sms) {
+        const char* v = getenv("B200S_VERT_SMALL_GENERIC");
+        if (!v || v[0] != '0') return 1;
+    }
     if (clusters_out) *clusters_out = cached.clusters;
     if (B <= 0) return 0;                                          // plan query only
     VertArgs a;

@@ -182,8 +182,18 @@ def _flows_agree(engine, H, W, D, mode, seed):
     assert valid.min() >= 0 and valid.max() <= (D - 1) * 16
 
 
-def test_full_size_1080p_hh_d256(engine):
-    _flows_agree(engine, 1080, 1920, 256, "hh", 1003)          # BASELINE config #3
+def test_full_size_1080p_hh_d256(engine, monkeypatch):
+    """BASELINE config #3, one pair. A single pair on this shape's clamped-record cluster plan goes to the generic line
+    kernel (vert.cu: under a third of the SMs busy); with the rule switched off the cluster kernel itself runs: both
+    must agree with the debug flow."""
+    from depthestimation_b200 import _lib
+    _flows_agree(engine, 1080, 1920, 256, "hh", 1003)
+    engine.compute(*make_pair(1080, 1920, 256, seed=1003)[:2])
+    assert engine.last_flow & _lib.FLOW_PATH_VERTICAL and not engine.last_flow & _lib.FLOW_VERT_DOWN
+    monkeypatch.setenv("B200S_VERT_SMALL_GENERIC", "0")
+    _flows_agree(engine, 1080, 1920, 256, "hh", 1003)
+    engine.compute(*make_pair(1080, 1920, 256, seed=1003)[:2])
+    assert engine.last_flow & _lib.FLOW_VERT_DOWN and engine.last_flow & _lib.FLOW_VERT_UP
 
 
 def test_full_size_4k_d256(engine):
@@ -214,9 +224,14 @@ def _full_size_vs_cv2(engine, H, W, D, mode, seed, **extra):
     assert np.array_equal(np.isfinite(depth), fin) and np.allclose(depth[fin], wz[fin], rtol=1e-4, atol=0)
 
 
-def test_full_size_1080p_hh_d256_vs_cv2(engine):
-    """BASELINE config #3: 1920x1080, D = 256, 8-path (hh) + LR check + speckle filter."""
+@pytest.mark.parametrize("small_generic", ["1", "0"])
+def test_full_size_1080p_hh_d256_vs_cv2(engine, monkeypatch, small_generic):
+    """BASELINE config #3: 1920x1080, D = 256, 8-path (hh) + LR check + speckle filter; through the generic line kernel
+    (what a single pair of this shape takes) and through the clamped-record cluster kernel (what a batch takes)."""
+    monkeypatch.setenv("B200S_VERT_SMALL_GENERIC", small_generic)
     _full_size_vs_cv2(engine, 1080, 1920, 256, "hh", 1003, disp12_max_diff=1, speckle_window_size=100, speckle_range=2)
+    from depthestimation_b200 import _lib
+    assert bool(engine.last_flow & _lib.FLOW_VERT_DOWN) == (small_generic == "0")
 
 
 @pytest.mark.parametrize("mode", ["sgbm_3way", "sgbm"])
@@ -242,6 +257,8 @@ for mode in ("sgbm", "hh"):
         got = e.compute(L, R)
         ref = oracle.sgbm_compute(L, R, oracle.make_params(**kw))
         bad += int((got != ref).sum())
+        if not e.last_flow & 1 or e.last_flow & 4:        # B200S_FLOW_VERT_DOWN / B200S_FLOW_PATH_VERTICAL
+            bad += 1000000
 e.close()
 print("MISMATCH", bad)
 """
@@ -257,7 +274,8 @@ def test_vertical_kernel_clamped_records():
     import sys
     from pathlib import Path
     root = str(Path(__file__).resolve().parents[1])
-    env = dict(os.environ, B200S_VERT_CS="1", B200S_VERBOSE="1")
+    # (B200S_VERT_SMALL_GENERIC=0: a single small pair on a clamped plan would otherwise go to the generic line kernel)
+    env = dict(os.environ, B200S_VERT_CS="1", B200S_VERBOSE="1", B200S_VERT_SMALL_GENERIC="0")
     r = subprocess.run([sys.executable, "-c", _CLAMP_SCRIPT.format(root=root)], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "clamped records" in r.stderr, "the clamped instantiation was not selected:\n" + r.stderr[-1000:]

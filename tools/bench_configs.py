@@ -30,6 +30,7 @@ CONFIGS = {
     "uhd4k": (2160, 3840, 256, "sgbm_3way", 64),     # configs[4]
     "kitti_3way": (375, 1242, 128, "sgbm_3way", 0),  # the reference's default mode on the KITTI shape
     "kitti_hh": (375, 1242, 128, "hh", 0),
+    "hd1080_sgbm": (1080, 1920, 128, "sgbm", 0),     # a wide frame at D = 128: two column slots per thread in the vertical cluster kernel
 }
 BYTES_PER_CELL = {"sgbm": 10, "sgbm_3way": 10, "hh": 16, "hh4": 16}
 
