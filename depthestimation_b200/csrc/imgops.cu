@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256) k_d16_to_f32_crop(const int16_t* __restri
     int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= Wc) return;
     size_t row = (size_t)blockIdx.z * H + blockIdx.y;
-    out[row * Wc + x] = __fdiv_rn((float)d16[row * W + x0 + x], 16.0f);
+    out[row * Wc + x] = __fmul_rn((float)d16[row * W + x0 + x], 0.0625f);   // == / 16.0f exactly (power of two)
 }
 void launch_disp16_to_f32_crop(const int16_t* d16, int B, int H, int W, int x0, float* out, cudaStream_t st) {
     dim3 grid((W - x0 + 255) / 256, H, B);
@@ -197,7 +197,7 @@ void launch_f32_to_s16x16(const float* d, size_t n, int16_t* out, cudaStream_t s
 __global__ void __launch_bounds__(256) k_s16_to_f32_div16(const int16_t* __restrict__ d, size_t n, float* __restrict__ out) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = __fdiv_rn((float)d[i], 16.0f);
+    out[i] = __fmul_rn((float)d[i], 0.0625f);   // == / 16.0f exactly (a power of two: no rounding, no underflow for int16 inputs)
 }
 void launch_s16_to_f32_div16(const int16_t* d, size_t n, float* out, cudaStream_t st) {
     k_s16_to_f32_div16<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d, n, out);
@@ -216,7 +216,7 @@ __device__ __forceinline__ int reflect101(int p, int n) {
 #define OT_H 16
 template <typename TIn> __device__ __forceinline__ float outl_val(TIn v);
 template <> __device__ __forceinline__ float outl_val<float>(float v) { return v; }
-template <> __device__ __forceinline__ float outl_val<int16_t>(int16_t v) { return __fdiv_rn((float)v, 16.0f); }
+template <> __device__ __forceinline__ float outl_val<int16_t>(int16_t v) { return __fmul_rn((float)v, 0.0625f); }   // == v / 16.0f exactly
 
 template <typename TIn>
 __global__ void __launch_bounds__(256) k_outliers(const TIn* __restrict__ d, float* __restrict__ out, int H, int W, float thr) {
