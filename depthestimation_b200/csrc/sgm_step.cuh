@@ -86,10 +86,19 @@ __device__ __forceinline__ unsigned group_min2(unsigned v, unsigned gmask, const
 // minimum over both halves of v over the lane group, as a scalar. A group that is the whole warp uses the hardware warp
 // reduction (CREDUX.MIN: ~40 cycles on the dependent path against ~170 for five shuffle + min levels, tools/ubench/redux.cu;
 // with a sub-warp member mask the same intrinsic serialises over the groups and is slower than the shuffle tree).
-template <int LW>
+// WR (the caller guarantees that all 32 lanes of the warp are converged here): two groups of 16 take two FULL-warp
+// reductions, each group masking the other's lanes out with 0xffffffff, and every lane keeps its own group's result:
+// two pipelined CREDUX against four shuffle + min levels on the critical path of a single line's scan.
+template <int LW, bool WR = false>
 __device__ __forceinline__ unsigned group_min(unsigned v, unsigned gmask, const int gl = 0) {
     if constexpr (LW == 32 && SGM_WARP_REDUX) {
         return __reduce_min_sync(0xffffffffu, min(v & 0xffffu, v >> 16));
+    } else if constexpr (LW == 16 && WR && SGM_WARP_REDUX) {
+        const unsigned s = min(v & 0xffffu, v >> 16);
+        const bool up = (threadIdx.x & 16u) != 0u;
+        const unsigned lo = __reduce_min_sync(0xffffffffu, up ? 0xffffffffu : s);
+        const unsigned hi = __reduce_min_sync(0xffffffffu, up ? s : 0xffffffffu);
+        return up ? hi : lo;
     } else {
         const unsigned mn = group_min2<LW>(v, gmask, gl);
         return min(mn & 0xffffu, mn >> 16);
@@ -173,11 +182,11 @@ __device__ __forceinline__ unsigned sgm_step_core(unsigned (&L)[NR], const unsig
 
 
 // full step: the minimum over d of the new column is reduced across the lane group here
-template <int LW, int NR, bool PAD = true>
+template <int LW, int NR, bool PAD = true, bool WR = false>
 __device__ __forceinline__ void sgm_step(unsigned (&L)[NR], unsigned& m, const unsigned (&Cq)[NR],
                                          const unsigned (&pm)[NR], const unsigned gmask, const int gl,
                                          const unsigned P1P1, const unsigned P2mP1, const int quirk, const int d0) {
-    m = group_min<LW>(sgm_step_core<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirk, d0), gmask, gl);
+    m = group_min<LW, WR>(sgm_step_core<LW, NR, PAD>(L, m, Cq, pm, gmask, gl, P1P1, P2mP1, quirk, d0), gmask, gl);
 }
 
 template <int NR>
