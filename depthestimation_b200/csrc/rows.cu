@@ -788,7 +788,10 @@ int rows_small_call(const Eff& e, int B) {
     // measured (KITTI pairs per call, small / regular variant, pairs/s): sgbm 4: 2330 / 1841, 8: 3690 / 3078, 12: 4630 / 4104,
     // 16: 3904 / 3880; sgbm_3way 4: 2428 / 2076, 8: 3577 / 3234, 12: 3446 / 4064
     const bool vertical_cluster = (e.mode == B200S_MODE_SGBM || e.mode == B200S_MODE_HH);   // pass 1 then hides beside it
-    return warps <= (vertical_cluster ? 16LL : 11LL) * sms;
+    // with the two-reduction group minimum (sgm_step.cuh) the small variant of sgbm keeps up with the regular one at every
+    // call size and wins up to ~50 KITTI pairs (pairs/s, small / regular: 20: 4650 / 4600, 32: 4760 / 4220, 48: 4990 /
+    // 4780, 75: 5167 / 5171, 150: 5220 / 5226): taken up to 64 warps per SM at D <= 128
+    return warps <= (vertical_cluster ? (e.Dp <= 128 ? 64LL : 16LL) : 11LL) * sms;
 }
 
 int launch_rows(const Eff& e, int B, const uint16_t* C, const uint16_t* Sv, uint16_t* ck, unsigned* keys, int16_t* raw,
