@@ -94,6 +94,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS
     // flight, while its -> scan runs, the six C columns of the next chunk are (two sets of ROW_K x NR registers; ncu of
     // one pair per call had 39 % of the stall samples on the first use of a column that was requested two steps before).
     constexpr bool DEEP = (NR == 4 && LW >= 16);
+    constexpr bool WR = (LW == 16);   // every lane of the warp runs the same loops (below): two 16-lane groups reduce with two full-warp CREDUX
     using LG = LaneGroup<LW>;
     constexpr int RPW = LG::RPW;                    // lines per warp
     constexpr int NCH = LW * NR / 4;                // 16-byte units per pixel record (all disparities of one pixel)
@@ -169,7 +170,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS
     if (a.phase != 2) {
         // W1 - r0 is a multiple of ROW_K: the pass runs whole groups of ROW_K columns, each ending on a checkpoint
         // column, so neither the ring position nor the checkpoint test depends on x
-        auto step1 = [&](const unsigned (&Cc)[NR]) { sgm_step<LW, NR, PAD, DEEP>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0); };
+        auto step1 = [&](const unsigned (&Cc)[NR]) { sgm_step<LW, NR, PAD, WR>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0); };
         int x = a.W1 - 1;
         const uint16_t* pC = Crow + (size_t)x * Dp;                                   // C of column x
         uint16_t* pck = ck + (size_t)((x - (ROW_K - 1) - r0) / ROW_K + 1) * Dp;       // checkpoint of the group that starts at x
@@ -229,7 +230,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS
     unsigned mr;
     sgm_reset<NR>(Lr, mr);
     auto stepb = [&](const int x, const int xs, const unsigned (&Cc)[NR]) {     // one <- step; L and C kept for the -> scan
-        sgm_step<LW, NR, PAD, DEEP>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
+        sgm_step<LW, NR, PAD, WR>(L, m, Cc, pm, gmask, gl, P1P1, P2mP1, quirkL, d0);
         const int pix = (x - xs) * RPW + rw;
         uint4* rec = Lw + pix * NCHP;
 #pragma unroll
@@ -247,7 +248,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS
             const uint4 t = Cb[((x - xs) * (NR / 4) + q) * LW + gl];
             Cc[4 * q] = t.x; Cc[4 * q + 1] = t.y; Cc[4 * q + 2] = t.z; Cc[4 * q + 3] = t.w;
         }
-        sgm_step<LW, NR, PAD, DEEP>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
+        sgm_step<LW, NR, PAD, WR>(Lr, mr, Cc, pm, gmask, gl, P1P1, P2mP1, 0, d0);
         const int pix = (x - xs) * RPW + rw;
         uint4* rec = Lw + pix * NCHP;
 #pragma unroll
@@ -451,7 +452,7 @@ __global__ void __launch_bounds__(ROWS_THREADS, (NR == 4 && LW >= 16) ? 2 : ROWS
     };
     auto start_from_ck = [&](const int xe) {
         if (xe < a.W1) {
-            m = group_min<LW, DEEP>(local_min2<NR>(L), gmask, gl);
+            m = group_min<LW, WR>(local_min2<NR>(L), gmask, gl);
         } else {
             sgm_reset<NR>(L, m);
         }
